@@ -1,0 +1,157 @@
+/*
+ * b200attn.h -- C ABI of libb200attn.so: the B200 (sm_100a) paged-attention decode backend.
+ *
+ * This is the drop-in boundary "b2" of SURVEY.md section 8(b).  The reference
+ * (ThakiCloud/vllm-backend-public) has no FFI for this path -- it launches an external vLLM
+ * server process (reference benchmark-vllm/vllm_manager.py:371-374,744-773) and never sees
+ * the kernels -- so every entry point below cites (a) the vLLM operation an engine behind that
+ * launch contract performs and (b) the reference symbol that parameterises it.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / pybind types.
+ *   - the caller owns every device and host buffer, including the workspace; the library
+ *     allocates nothing on the device and keeps no device-side state.
+ *   - every kernel entry point only enqueues work on `stream` (a cudaStream_t passed as void*)
+ *     and returns without synchronising.
+ *   - return value: 0 (B2_OK) or a negative B2_E* code; the message for the calling thread's last
+ *     failure is available from b2_last_error().  Nothing throws or aborts across this boundary.
+ *   - device pointers must be 16-byte aligned; head_dim must be 128 (Llama-3 geometry).
+ *
+ * Tensor layouts (element strides unless noted)
+ *   q, out        [B, Hq, d]                 bf16   (row b at q + b*q_stride)
+ *   k_new, v_new  [T, Hkv, d]                bf16   (token t at k_new + t*k_token_stride)
+ *   k_cache       [num_blocks, Hkv, bs, d]   bf16 or e4m3 bytes ("HND": one (block, head) tile of
+ *   v_cache                                  bs x d elements is contiguous)
+ *   block_tables  [B, max_nb] int32          physical block id of each logical block
+ *   seq_lens      [B] int32                  tokens that attend (including the one just written)
+ *   slot_mapping  [T] int64                  block_id*bs + offset, or < 0 to skip the token
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define B2_API __attribute__((visibility("default")))
+#else
+#define B2_API
+#endif
+
+/* error codes */
+#define B2_OK             0
+#define B2_EINVAL        -1   /* bad argument (null pointer, misalignment, non-positive size)   */
+#define B2_EUNSUPPORTED  -2   /* shape / dtype outside what the sm_100a kernels are built for     */
+#define B2_ECUDA         -3   /* CUDA runtime / driver error at launch or descriptor encoding     */
+#define B2_ENOMEM        -4   /* block pool exhausted (block manager) or workspace too small      */
+#define B2_ENOTFOUND     -5   /* unknown sequence id (block manager)                              */
+#define B2_EEXISTS       -6   /* sequence id already present (block manager)                      */
+
+/* KV-cache element types: VLLMConfig.dtype / additional_args["kv-cache-dtype"]
+ * (reference benchmark-vllm/models.py:14,23-28 -> vllm_templates.py:57,82-87). */
+#define B2_KV_BF16      0
+#define B2_KV_FP8_E4M3  1
+
+B2_API int         b2_version(void);          /* returns B2_ABI_VERSION */
+B2_API const char* b2_last_error(void);       /* thread-local, never NULL */
+
+/* ---------------------------------------------------------------------------------------------
+ * KV write.  Replaces vLLM `reshape_and_cache` (csrc/cache_kernels.cu) inside the engine the
+ * reference launches (vllm_manager.py:371-374); page size = VLLMConfig.block_size
+ * (benchmark-vllm/models.py:10 -> --block-size, vllm_templates.py:54).
+ *   for t in [0,T): s = slot_mapping[t]; if s < 0 skip;
+ *     k_cache[s / bs][h][s % bs][:] = k_new[t][h][:]   (same for v)
+ *   B2_KV_FP8_E4M3 stores sat_rne_e4m3(x / *k_scale): clamp to +-448, round to nearest even.
+ * k_scale / v_scale: DEVICE pointers to one float each (may be NULL for B2_KV_BF16).
+ * cache_block_stride / cache_head_stride are in elements of the cache dtype.
+ * ------------------------------------------------------------------------------------------- */
+B2_API int b2_reshape_and_cache(const void* k_new, const void* v_new,
+                         void* k_cache, void* v_cache,
+                         const int64_t* slot_mapping,
+                         int T, int Hkv, int d, int bs,
+                         int64_t k_token_stride, int64_t v_token_stride,
+                         int64_t cache_block_stride, int64_t cache_head_stride,
+                         int kv_dtype, const float* k_scale, const float* v_scale,
+                         void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Paged-attention decode.  Replaces vLLM `paged_attention_v1/_v2` (csrc/attention/) for the decode
+ * step of the engine behind the reference's launch contract; B <= VLLMConfig.max_num_seqs
+ * (models.py:9), max_nb = ceil(max_model_len / block_size) (models.py:15,10), Hq/Hkv are the
+ * per-GPU head counts after tensor_parallel_size sharding (models.py:11).
+ *   out[b][hq] = softmax_j(scale * <q[b][hq], K[b][j][hq / G]>) . V[b][j][hq / G],  j < seq_lens[b]
+ *   G = Hq / Hkv; fp32 softmax and accumulation; out rounded to bf16 once; seq_len 0 -> zeros.
+ * num_splits: 0 = choose automatically, 1 = single pass ("v1"), >1 = split-K over the KV length
+ * with a log-sum-exp merge ("v2").  The workspace (device memory, 16-byte aligned) must hold
+ * b2_paged_decode_workspace_bytes(...) bytes for the same B/Hq/d/max_nb/bs/num_splits; it is
+ * scratch (no state survives the call) and may be NULL when that size is 0.
+ * ------------------------------------------------------------------------------------------- */
+B2_API size_t b2_paged_decode_workspace_bytes(int B, int Hq, int Hkv, int d, int bs, int max_nb,
+                                       int num_splits);
+
+/* the split count b2_paged_decode will actually use for num_splits = 0 */
+B2_API int b2_paged_decode_auto_splits(int B, int Hq, int Hkv, int d, int bs, int max_nb, int kv_dtype);
+
+B2_API int b2_paged_decode(void* out, const void* q,
+                    const void* k_cache, const void* v_cache,
+                    const int32_t* block_tables, const int32_t* seq_lens,
+                    int B, int Hq, int Hkv, int d, int bs, int max_nb,
+                    int64_t num_blocks,
+                    int64_t q_stride, int64_t out_stride,
+                    int64_t cache_block_stride, int64_t cache_head_stride,
+                    float scale, int kv_dtype,
+                    const float* k_scale, const float* v_scale,
+                    void* workspace, size_t workspace_bytes, int num_splits,
+                    void* stream);
+
+/* Diagnostic / A-B variant kept for the ncu comparison DESIGN.md cites: the same contract as
+ * b2_paged_decode, computed by a plain CUDA-core kernel (no TMA, no tensor cores).  Not used by
+ * the engine. */
+B2_API int b2_paged_decode_simt(void* out, const void* q,
+                         const void* k_cache, const void* v_cache,
+                         const int32_t* block_tables, const int32_t* seq_lens,
+                         int B, int Hq, int Hkv, int d, int bs, int max_nb,
+                         int64_t q_stride, int64_t out_stride,
+                         int64_t cache_block_stride, int64_t cache_head_stride,
+                         float scale, int kv_dtype,
+                         const float* k_scale, const float* v_scale,
+                         void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Block manager (host only): the page allocator that produces block_tables / seq_lens /
+ * slot_mapping each step.  Pool size follows VLLMConfig.gpu_memory_utilization and block_size
+ * (models.py:8,10); per-sequence capacity follows max_model_len (models.py:15).
+ * A handle is single-writer (the scheduler thread).  All output pointers are HOST memory.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b2_block_manager b2_block_manager;
+
+B2_API b2_block_manager* b2_bm_create(int64_t num_blocks, int bs);          /* NULL on bad args */
+B2_API void    b2_bm_destroy(b2_block_manager* bm);
+B2_API int64_t b2_bm_num_free(const b2_block_manager* bm);
+B2_API int64_t b2_bm_num_seqs(const b2_block_manager* bm);
+B2_API int64_t b2_bm_seq_len(const b2_block_manager* bm, int64_t seq_id);   /* < 0: B2_ENOTFOUND */
+/* can `n_tokens` more tokens be appended to seq_id (or a new sequence if it is unknown)? */
+B2_API int     b2_bm_can_append(const b2_block_manager* bm, int64_t seq_id, int64_t n_tokens);
+/* register seq_id with room for n_tokens tokens, length 0 */
+B2_API int     b2_bm_alloc_seq(b2_block_manager* bm, int64_t seq_id, int64_t n_tokens);
+/* grow seq_id by n_new tokens; writes their n_new slots (block*bs + offset) to slots_out */
+B2_API int     b2_bm_append(b2_block_manager* bm, int64_t seq_id, int64_t n_new, int64_t* slots_out);
+B2_API int     b2_bm_free_seq(b2_block_manager* bm, int64_t seq_id);
+/* block_tables_out[B][max_nb] (unused entries 0) and seq_lens_out[B] for the given sequences */
+B2_API int     b2_bm_fill_tables(const b2_block_manager* bm, const int64_t* seq_ids, int B,
+                          int32_t* block_tables_out, int max_nb, int32_t* seq_lens_out);
+/* one decode step for a batch: append one token to every sequence, then fill the three arrays */
+B2_API int     b2_bm_plan_decode(b2_block_manager* bm, const int64_t* seq_ids, int B,
+                          int32_t* block_tables_out, int max_nb, int32_t* seq_lens_out,
+                          int64_t* slot_mapping_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

@@ -1,0 +1,298 @@
+"""GPU parity tests proper: the sm_100a kernels, called through the C ABI (ctypes ->
+libb200attn.so), against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star):
+  * reshape_and_cache: bit-exact.
+  * decode, bf16 KV: |delta| <= 2e-3 + 1e-2 * |ref|.
+  * decode, fp8 KV vs the oracle reading the *same quantised cache*: same bound; vs the
+    unquantised oracle the looser stated bound 5e-2 + 1e-1 * |ref| (quantisation error).
+At BASELINE.json's full sizes the oracle is run on a subset of sequences and the rest is covered
+by size-independent properties (split-count invariance, block-table permutation invariance,
+agreement of two independent kernels)."""
+import json
+from pathlib import Path
+
+import pytest
+import torch
+
+import b200attn
+import paged_attention_ref as R
+
+pytestmark = pytest.mark.gpu
+
+ATOL, RTOL = 2e-3, 1e-2
+GOLDEN = Path(__file__).parent / "golden"
+
+
+def assert_close(got, ref, atol=ATOL, rtol=RTOL, what=""):
+    got = got.float().cpu()
+    ref = ref.float().cpu()
+    assert torch.isfinite(got).all(), f"{what}: non-finite output"
+    err = (got - ref).abs()
+    bound = atol + rtol * ref.abs()
+    bad = err > bound
+    assert not bad.any(), (f"{what}: {int(bad.sum())}/{bad.numel()} outside {atol}+{rtol}|ref|; "
+                           f"max err {float(err.max()):.3e} at ref {float(ref.flatten()[err.argmax()]):.3e}")
+
+
+def build_caches(inp, dev, fp8=False, poison=False):
+    """Fill device caches through our reshape_and_cache and the CPU caches through the oracle."""
+    shape = (inp["num_blocks"], inp["Hkv"], inp["bs"], inp["d"])
+    if fp8:
+        ks = float(inp["k"].float().abs().max()) / 448.0
+        vs = float(inp["v"].float().abs().max()) / 448.0
+        kc_ref = torch.zeros(shape, dtype=torch.uint8)
+        vc_ref = torch.zeros(shape, dtype=torch.uint8)
+        R.reshape_and_cache_ref(inp["k"], inp["v"], kc_ref, vc_ref, inp["slot_mapping"], R.KV_FP8_E4M3, ks, vs)
+        kc = torch.zeros(shape, dtype=torch.uint8, device=dev)
+        vc = torch.zeros(shape, dtype=torch.uint8, device=dev)
+        ksd = torch.tensor([ks], dtype=torch.float32, device=dev)
+        vsd = torch.tensor([vs], dtype=torch.float32, device=dev)
+        b200attn.reshape_and_cache(inp["k"].to(dev), inp["v"].to(dev), kc, vc, inp["slot_mapping"].to(dev), ksd, vsd)
+        return kc, vc, kc_ref, vc_ref, (ks, vs, ksd, vsd)
+    fill = float("nan") if poison else 0.0
+    kc_ref = torch.full(shape, fill, dtype=torch.bfloat16)
+    vc_ref = torch.full(shape, fill, dtype=torch.bfloat16)
+    R.reshape_and_cache_ref(inp["k"], inp["v"], kc_ref, vc_ref, inp["slot_mapping"])
+    kc = torch.full(shape, fill, dtype=torch.bfloat16, device=dev)
+    vc = torch.full(shape, fill, dtype=torch.bfloat16, device=dev)
+    b200attn.reshape_and_cache(inp["k"].to(dev), inp["v"].to(dev), kc, vc, inp["slot_mapping"].to(dev))
+    return kc, vc, kc_ref, vc_ref, None
+
+
+def bits(t):
+    return t.contiguous().view(torch.uint8).cpu()
+
+
+# ------------------------------------------------------------------------------------------
+# a5 reshape_and_cache: bit-exact
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("bs", [8, 16, 32])
+def test_reshape_and_cache_bf16_bit_exact(cuda, bs):
+    inp = R.make_inputs(5, 8, 2, 128, bs, 70, seed=bs, ragged=True, slack_blocks=5)
+    slots = inp["slot_mapping"].clone()
+    slots[::7] = -1
+    inp["slot_mapping"] = slots
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    assert torch.equal(bits(kc), bits(kc_ref))
+    assert torch.equal(bits(vc), bits(vc_ref))
+
+
+def test_reshape_and_cache_token_stride_and_empty(cuda):
+    """k/v taken as slices of a fused QKV projection (token stride > Hkv*d); T = 0 is a no-op."""
+    Hq, Hkv, d, bs = 8, 2, 128, 16
+    inp = R.make_inputs(3, Hq, Hkv, d, bs, 40, seed=11, ragged=True)
+    T = inp["k"].shape[0]
+    g = torch.Generator().manual_seed(1)
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * d, generator=g).to(torch.bfloat16)
+    qkv[:, Hq * d:(Hq + Hkv) * d] = inp["k"].reshape(T, -1)
+    qkv[:, (Hq + Hkv) * d:] = inp["v"].reshape(T, -1)
+    qkv_d = qkv.to(cuda)
+    k_view = qkv_d[:, Hq * d:(Hq + Hkv) * d].unflatten(1, (Hkv, d))
+    v_view = qkv_d[:, (Hq + Hkv) * d:].unflatten(1, (Hkv, d))
+    shape = (inp["num_blocks"], Hkv, bs, d)
+    kc = torch.zeros(shape, dtype=torch.bfloat16, device=cuda)
+    vc = torch.zeros_like(kc)
+    b200attn.reshape_and_cache(k_view, v_view, kc, vc, inp["slot_mapping"].to(cuda))
+    kc_ref = torch.zeros(shape, dtype=torch.bfloat16)
+    vc_ref = torch.zeros_like(kc_ref)
+    R.reshape_and_cache_ref(inp["k"], inp["v"], kc_ref, vc_ref, inp["slot_mapping"])
+    assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref))
+    empty = torch.zeros(0, Hkv, d, dtype=torch.bfloat16, device=cuda)
+    b200attn.reshape_and_cache(empty, empty, kc, vc, torch.zeros(0, dtype=torch.int64, device=cuda))
+    assert torch.equal(bits(kc), bits(kc_ref))
+
+
+def test_reshape_and_cache_fp8_bit_exact(cuda):
+    inp = R.make_inputs(4, 8, 2, 128, 16, 90, seed=3, ragged=True)
+    # stretch the range so saturation, subnormals and zero all occur
+    inp["k"][::3] *= 40.0
+    inp["k"][1::3] *= 1e-3
+    inp["v"][::5] = 0.0
+    kc_shape = (inp["num_blocks"], 2, 16, 128)
+    ks, vs = 0.37, 0.0121
+    kc_ref = torch.zeros(kc_shape, dtype=torch.uint8)
+    vc_ref = torch.zeros_like(kc_ref)
+    R.reshape_and_cache_ref(inp["k"], inp["v"], kc_ref, vc_ref, inp["slot_mapping"], R.KV_FP8_E4M3, ks, vs)
+    kc = torch.zeros(kc_shape, dtype=torch.uint8, device=cuda)
+    vc = torch.zeros_like(kc)
+    b200attn.reshape_and_cache(inp["k"].to(cuda), inp["v"].to(cuda), kc, vc, inp["slot_mapping"].to(cuda),
+                               torch.tensor([ks], device=cuda), torch.tensor([vs], device=cuda))
+    assert torch.equal(kc.cpu(), kc_ref), f"{int((kc.cpu() != kc_ref).sum())} K bytes differ"
+    assert torch.equal(vc.cpu(), vc_ref), f"{int((vc.cpu() != vc_ref).sum())} V bytes differ"
+    assert int((kc_ref & 0x7F).max()) == 0x7E           # saturation was exercised
+
+
+# ------------------------------------------------------------------------------------------
+# a6/a7 decode, bf16 KV
+# ------------------------------------------------------------------------------------------
+def run_decode(inp, kc, vc, dev, **kw):
+    return b200attn.paged_decode(inp["q"].to(dev), kc, vc, inp["block_tables"].to(dev), inp["seq_lens"].to(dev), **kw)
+
+
+@pytest.mark.parametrize("impl,splits", [("tma", 1), ("tma", 2), ("tma", 0), ("tma", 7), ("simt", 1)])
+def test_decode_config1(cuda, impl, splits):
+    """BASELINE.json configs[0]: 8 q / 2 kv heads, d 128, bs 16, batch 4, ctx 512."""
+    inp = R.make_inputs(4, 8, 2, 128, 16, 512, seed=0)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    out = run_decode(inp, kc, vc, cuda, impl=impl, num_splits=splits)
+    assert_close(out, ref, what=f"config1 {impl} splits={splits}")
+
+
+def test_decode_config1_against_committed_golden(cuda):
+    meta = json.loads((GOLDEN / "config1.json").read_text())
+    inp = R.make_inputs(**meta["shape"], seed=meta["seed"])
+    kc, vc, _, _, _ = build_caches(inp, cuda)
+    out = run_decode(inp, kc, vc, cuda)
+    assert_close(out, torch.load(GOLDEN / "config1_out.pt"), what="golden config1")
+
+
+@pytest.mark.parametrize("Hq,Hkv", [(1, 1), (4, 4), (8, 2), (32, 8), (8, 1), (16, 1), (24, 2), (40, 2)])
+def test_decode_gqa_group_sizes(cuda, Hq, Hkv):
+    inp = R.make_inputs(3, Hq, Hkv, 128, 16, 200, seed=Hq, ragged=True)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    assert_close(run_decode(inp, kc, vc, cuda), ref, what=f"G={Hq // Hkv}")
+    assert_close(run_decode(inp, kc, vc, cuda, impl="simt"), ref, what=f"simt G={Hq // Hkv}")
+
+
+@pytest.mark.parametrize("bs", [8, 16, 32])
+@pytest.mark.parametrize("splits", [1, 3])
+def test_decode_block_sizes_and_edge_lengths(cuda, bs, splits):
+    """seq_len 0, 1, around block and stage (64-token) boundaries; untouched cache memory is NaN, so any
+    read past seq_len that reaches the arithmetic shows up as a non-finite output."""
+    lens = [0, 1, bs - 1, bs, bs + 1, 63, 64, 65, 127, 128, 129, 300]
+    B = len(lens)
+    inp = R.make_inputs(B, 8, 2, 128, bs, 320, seed=bs + splits)
+    sl = torch.tensor(lens, dtype=torch.int32)
+    # rebuild the token stream for the shortened sequences
+    keep = []
+    off = 0
+    for b in range(B):
+        keep.append(torch.arange(off, off + lens[b]))
+        off += 320
+    keep = torch.cat(keep)
+    inp["k"], inp["v"], inp["slot_mapping"] = inp["k"][keep], inp["v"][keep], inp["slot_mapping"][keep]
+    inp["seq_lens"] = sl
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda, poison=True)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], sl, return_f32=True)
+    out = run_decode(inp, kc, vc, cuda, num_splits=splits)
+    assert torch.all(out[0] == 0), "seq_len 0 must give a zero row"
+    assert_close(out, ref, what=f"bs={bs} splits={splits}")
+
+
+def test_decode_ragged_mixed_lengths(cuda):
+    inp = R.make_inputs(16, 32, 8, 128, 16, 1500, seed=5, ragged=True)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    for splits in (0, 1, 4):
+        assert_close(run_decode(inp, kc, vc, cuda, num_splits=splits), ref, what=f"ragged splits={splits}")
+
+
+def test_decode_q_and_out_strides(cuda):
+    """q as a slice of a fused QKV row and out as a slice of a wider buffer (strided batch axis)."""
+    inp = R.make_inputs(4, 8, 2, 128, 16, 100, seed=6)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    wide = torch.zeros(4, 12 * 128, dtype=torch.bfloat16, device=cuda)
+    wide[:, :8 * 128] = inp["q"].reshape(4, -1).to(cuda)
+    qv = wide[:, :8 * 128].unflatten(1, (8, 128))
+    obuf = torch.zeros(4, 10 * 128, dtype=torch.bfloat16, device=cuda)
+    ov = obuf[:, :8 * 128].unflatten(1, (8, 128))
+    b200attn.paged_decode(qv, kc, vc, inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda), out=ov, num_splits=2)
+    assert_close(ov, ref, what="strided q/out")
+    assert torch.all(obuf[:, 8 * 128:] == 0)
+
+
+def test_decode_large_magnitude_scores(cuda):
+    """Scores far from zero: the running-max rescale must keep everything finite."""
+    inp = R.make_inputs(2, 8, 2, 128, 16, 260, seed=8)
+    inp["q"] = (inp["q"].float() * 6).to(torch.bfloat16)
+    inp["k"] = (inp["k"].float() * 6).to(torch.bfloat16)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    assert_close(run_decode(inp, kc, vc, cuda, num_splits=1), ref, atol=4e-3, rtol=2e-2, what="peaked softmax")
+
+
+# ------------------------------------------------------------------------------------------
+# a8 decode, fp8 KV
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("Hq,Hkv,splits", [(8, 2, 1), (32, 8, 0), (16, 1, 2)])
+def test_decode_fp8(cuda, Hq, Hkv, splits):
+    inp = R.make_inputs(4, Hq, Hkv, 128, 16, 400, seed=21, ragged=True)
+    kc, vc, kc_ref, vc_ref, (ks, vs, ksd, vsd) = build_caches(inp, cuda, fp8=True)
+    assert torch.equal(kc.cpu(), kc_ref) and torch.equal(vc.cpu(), vc_ref)
+    ref_q = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"],
+                               kv_dtype=R.KV_FP8_E4M3, k_scale=ks, v_scale=vs, return_f32=True)
+    for impl in ("tma", "simt"):
+        out = run_decode(inp, kc, vc, cuda, k_scale=ksd, v_scale=vsd, num_splits=splits, impl=impl)
+        assert_close(out, ref_q, what=f"fp8 {impl} vs same-cache oracle")
+    # against the unquantised oracle: the stated looser bound
+    shape = kc.shape
+    kb = torch.zeros(shape, dtype=torch.bfloat16)
+    vb = torch.zeros_like(kb)
+    R.reshape_and_cache_ref(inp["k"], inp["v"], kb, vb, inp["slot_mapping"])
+    ref = R.paged_decode_ref(inp["q"], kb, vb, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    out = run_decode(inp, kc, vc, cuda, k_scale=ksd, v_scale=vsd)
+    assert_close(out, ref, atol=5e-2, rtol=1e-1, what="fp8 vs unquantised oracle")
+
+
+# ------------------------------------------------------------------------------------------
+# full-size configs: oracle on a subset + size-independent properties
+# ------------------------------------------------------------------------------------------
+def _full_size(cuda, B, Hq, Hkv, ctx, fp8, seed, n_oracle=2):
+    inp = R.make_inputs(B, Hq, Hkv, 128, 16, ctx, seed=seed)
+    dev_k, dev_v = inp["k"].to(cuda), inp["v"].to(cuda)
+    shape = (inp["num_blocks"], Hkv, 16, 128)
+    kw = {}
+    if fp8:
+        ks = float(inp["k"].float().abs().max()) / 448.0
+        vs = float(inp["v"].float().abs().max()) / 448.0
+        kw = dict(k_scale=torch.tensor([ks], device=cuda), v_scale=torch.tensor([vs], device=cuda))
+        kc = torch.zeros(shape, dtype=torch.uint8, device=cuda)
+    else:
+        kc = torch.zeros(shape, dtype=torch.bfloat16, device=cuda)
+    vc = torch.zeros_like(kc)
+    b200attn.reshape_and_cache(dev_k, dev_v, kc, vc, inp["slot_mapping"].to(cuda), kw.get("k_scale"), kw.get("v_scale"))
+    del dev_k, dev_v
+    q, bt, sl = inp["q"].to(cuda), inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda)
+    out_auto = b200attn.paged_decode(q, kc, vc, bt, sl, **kw)
+    out_one = b200attn.paged_decode(q, kc, vc, bt, sl, num_splits=1, **kw)
+    out_many = b200attn.paged_decode(q, kc, vc, bt, sl, num_splits=16, **kw)
+    # (1) split-count invariance: the merge is exact algebra, only bf16/fp32 rounding differs
+    assert_close(out_one, out_auto.float(), what="splits 1 vs auto")
+    assert_close(out_many, out_auto.float(), what="splits 16 vs auto")
+    # (2) two independent kernels agree on every row
+    out_simt = b200attn.paged_decode(q, kc, vc, bt, sl, impl="simt", **kw)
+    assert_close(out_auto, out_simt.float(), what="tma vs simt")
+    # (3) the oracle on the first n_oracle sequences (it reads the device-written cache, copied back)
+    sub = slice(0, n_oracle)
+    need = torch.unique(inp["block_tables"][sub].flatten()).long()
+    kc_ref = torch.zeros(shape, dtype=kc.dtype)
+    vc_ref = torch.zeros_like(kc_ref)
+    kc_ref[need] = kc[need.to(cuda)].cpu()
+    vc_ref[need] = vc[need.to(cuda)].cpu()
+    okw = dict(kv_dtype=R.KV_FP8_E4M3, k_scale=ks, v_scale=vs) if fp8 else {}
+    ref = R.paged_decode_ref(inp["q"][sub], kc_ref, vc_ref, inp["block_tables"][sub], inp["seq_lens"][sub],
+                             return_f32=True, **okw)
+    assert_close(out_auto[sub], ref, what="oracle subset")
+    # (4) permuting which sequence sits in which batch row permutes the output rows
+    perm = torch.randperm(B, generator=torch.Generator().manual_seed(1)).to(cuda)
+    out_p = b200attn.paged_decode(q[perm].contiguous(), kc, vc, bt[perm].contiguous(), sl[perm].contiguous(), **kw)
+    assert torch.equal(out_p, out_auto[perm])
+
+
+def test_full_size_config2_llama3_8b_b64_ctx4k(cuda):
+    """BASELINE.json configs[1]: 32 q / 8 kv heads, batch 64, ctx 4096, bf16 KV."""
+    _full_size(cuda, 64, 32, 8, 4096, fp8=False, seed=0)
+
+
+def test_full_size_config3_fp8_b128_ctx8k(cuda):
+    """BASELINE.json configs[2]: fp8 e4m3 KV, batch 128, ctx 8192."""
+    _full_size(cuda, 128, 32, 8, 8192, fp8=True, seed=1, n_oracle=1)
+
+
+def test_full_size_config4_per_gpu_shard_tp8(cuda):
+    """BASELINE.json configs[3] as seen by one of 8 ranks: 8 q / 1 kv head, batch 256, ctx 8192."""
+    _full_size(cuda, 256, 8, 1, 8192, fp8=False, seed=2, n_oracle=1)

@@ -1,0 +1,9 @@
+"""b200attn -- host side of the B200 paged-attention decode backend.
+
+`ops` are the two device ops (KV write, paged decode) over libb200attn.so;
+`BlockManager` is the C++ page allocator.  The CUDA extension is mandatory.
+"""
+from ._lib import B2Error, KV_BF16, KV_FP8_E4M3, LIB_PATH, load  # noqa: F401
+from .block_manager import BlockManager  # noqa: F401
+from .ops import (decode_auto_splits, decode_workspace_bytes, paged_decode,  # noqa: F401
+                  reshape_and_cache)

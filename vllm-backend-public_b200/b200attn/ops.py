@@ -1,0 +1,159 @@
+"""Torch-tensor front end of the C ABI: the two device ops on the hot path.
+
+Mirrors the call shape of vLLM's `ops.reshape_and_cache` / `ops.paged_attention_v1/v2` (the ops
+the engine launched by reference benchmark-vllm/vllm_manager.py:371-374 runs each decode step),
+but every argument is checked here and handed to libb200attn.so as raw pointers + sizes on the
+current CUDA stream.  CUDA tensors only: there is no CPU path.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import KV_BF16, KV_FP8_E4M3
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _need_cuda(**tensors) -> torch.device:
+    dev = None
+    for name, t in tensors.items():
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise ValueError(f"{name} must be a CUDA tensor (b200attn has no CPU path)")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise ValueError(f"{name} is on {t.device}, expected {dev}")
+    return dev
+
+
+def _stream(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _kv_dtype_of(cache: torch.Tensor) -> int:
+    if cache.dtype == torch.bfloat16:
+        return KV_BF16
+    if cache.dtype in (torch.uint8, torch.float8_e4m3fn):
+        return KV_FP8_E4M3
+    raise ValueError(f"KV cache dtype {cache.dtype} unsupported (bf16 or uint8/float8_e4m3fn)")
+
+
+def _check_cache(k_cache: torch.Tensor, v_cache: torch.Tensor):
+    if k_cache.dim() != 4 or k_cache.shape != v_cache.shape or k_cache.dtype != v_cache.dtype:
+        raise ValueError("k_cache / v_cache must both be [num_blocks, Hkv, bs, d] of one dtype")
+    if k_cache.stride() != v_cache.stride():
+        raise ValueError("k_cache / v_cache must share strides")
+    nb, Hkv, bs, d = k_cache.shape
+    s = k_cache.stride()
+    if s[3] != 1 or s[2] != d:
+        raise ValueError("each (block, head) tile of the KV cache must be contiguous [bs, d]")
+    return nb, Hkv, bs, d, s[0], s[1]
+
+
+def reshape_and_cache(k_new: torch.Tensor, v_new: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                      slot_mapping: torch.Tensor, k_scale: Optional[torch.Tensor] = None,
+                      v_scale: Optional[torch.Tensor] = None) -> None:
+    """k_cache[slot // bs, h, slot % bs, :] = k_new[t, h, :] (same for v); slot < 0 skips the token.
+
+    k_new / v_new: [T, Hkv, d] bf16 (the last two dims contiguous; a token stride is allowed so a
+    fused QKV projection can be written without a copy).  fp8 caches need 1-element fp32 device
+    tensors k_scale / v_scale."""
+    lib = _lib.load()
+    dev = _need_cuda(k_new=k_new, v_new=v_new, k_cache=k_cache, v_cache=v_cache, slot_mapping=slot_mapping,
+                     k_scale=k_scale, v_scale=v_scale)
+    nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+    kvd = _kv_dtype_of(k_cache)
+    if k_new.dtype != torch.bfloat16 or v_new.dtype != torch.bfloat16:
+        raise ValueError("k_new / v_new must be bf16")
+    if k_new.dim() != 3 or k_new.shape != v_new.shape or k_new.shape[1:] != (Hkv, d):
+        raise ValueError(f"k_new / v_new must be [T, {Hkv}, {d}]")
+    for t in (k_new, v_new):
+        if t.stride(2) != 1 or t.stride(1) != d:
+            raise ValueError("k_new / v_new: head and dim axes must be contiguous")
+    T = k_new.shape[0]
+    if slot_mapping.dtype != torch.int64 or slot_mapping.shape != (T,) or not slot_mapping.is_contiguous():
+        raise ValueError("slot_mapping must be a contiguous int64 [T]")
+    if kvd == KV_FP8_E4M3:
+        for s in (k_scale, v_scale):
+            if s is None or s.dtype != torch.float32 or s.numel() != 1:
+                raise ValueError("fp8 KV cache needs 1-element fp32 device tensors k_scale / v_scale")
+    _lib.check(lib.b2_reshape_and_cache(
+        _ptr(k_new), _ptr(v_new), _ptr(k_cache), _ptr(v_cache), _ptr(slot_mapping),
+        T, Hkv, d, bs, k_new.stride(0) if T else Hkv * d, v_new.stride(0) if T else Hkv * d,
+        bstride, hstride, kvd, _ptr(k_scale), _ptr(v_scale), _stream(dev)))
+
+
+def decode_workspace_bytes(B: int, Hq: int, Hkv: int, d: int, bs: int, max_nb: int, num_splits: int = 0) -> int:
+    return int(_lib.load().b2_paged_decode_workspace_bytes(B, Hq, Hkv, d, bs, max_nb, num_splits))
+
+
+def decode_auto_splits(B: int, Hq: int, Hkv: int, d: int, bs: int, max_nb: int, kv_dtype: int = KV_BF16) -> int:
+    return int(_lib.load().b2_paged_decode_auto_splits(B, Hq, Hkv, d, bs, max_nb, kv_dtype))
+
+
+def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_tables: torch.Tensor,
+                 seq_lens: torch.Tensor, scale: Optional[float] = None, k_scale: Optional[torch.Tensor] = None,
+                 v_scale: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                 workspace: Optional[torch.Tensor] = None, num_splits: int = 0, impl: str = "tma") -> torch.Tensor:
+    """out[b, hq] = softmax(scale * q[b, hq] . K[b, :seq_lens[b], hq // G]) . V[...]  -> bf16 [B, Hq, d].
+
+    `workspace` is a uint8 device tensor of at least decode_workspace_bytes(...) bytes; one is
+    allocated per call when omitted (the engine passes a persistent one).  impl="simt" selects
+    the CUDA-core A/B kernel."""
+    lib = _lib.load()
+    dev = _need_cuda(q=q, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables, seq_lens=seq_lens,
+                     k_scale=k_scale, v_scale=v_scale, out=out, workspace=workspace)
+    nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+    kvd = _kv_dtype_of(k_cache)
+    if q.dtype != torch.bfloat16 or q.dim() != 3 or q.shape[2] != d:
+        raise ValueError(f"q must be bf16 [B, Hq, {d}]")
+    B, Hq, _ = q.shape
+    if q.stride(2) != 1 or q.stride(1) != d:
+        raise ValueError("q: head and dim axes must be contiguous")
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B \
+            or not block_tables.is_contiguous():
+        raise ValueError("block_tables must be a contiguous int32 [B, max_nb]")
+    if seq_lens.dtype != torch.int32 or seq_lens.shape != (B,) or not seq_lens.is_contiguous():
+        raise ValueError("seq_lens must be a contiguous int32 [B]")
+    max_nb = block_tables.shape[1]
+    if out is None:
+        out = torch.empty(B, Hq, d, dtype=torch.bfloat16, device=dev)
+    elif out.dtype != torch.bfloat16 or out.shape != (B, Hq, d) or out.stride(2) != 1 or out.stride(1) != d:
+        raise ValueError("out must be bf16 [B, Hq, d] with contiguous head/dim axes")
+    if scale is None:
+        scale = 1.0 / math.sqrt(d)
+    if kvd == KV_FP8_E4M3:
+        for s in (k_scale, v_scale):
+            if s is None or s.dtype != torch.float32 or s.numel() != 1:
+                raise ValueError("fp8 KV cache needs 1-element fp32 device tensors k_scale / v_scale")
+    if B == 0:
+        return out
+    qs = q.stride(0) if B > 1 else Hq * d
+    os_ = out.stride(0) if B > 1 else Hq * d
+    if impl == "simt":
+        _lib.check(lib.b2_paged_decode_simt(
+            _ptr(out), _ptr(q), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(seq_lens),
+            B, Hq, Hkv, d, bs, max_nb, qs, os_, bstride, hstride, float(scale), kvd,
+            _ptr(k_scale), _ptr(v_scale), _stream(dev)))
+        return out
+    if impl != "tma":
+        raise ValueError(f"impl {impl!r}")
+    need = lib.b2_paged_decode_workspace_bytes(B, Hq, Hkv, d, bs, max_nb, num_splits)
+    if need and (workspace is None or workspace.numel() * workspace.element_size() < need):
+        if workspace is not None:
+            raise ValueError(f"workspace holds {workspace.numel() * workspace.element_size()} bytes, {need} required")
+        workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+    wbytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    _lib.check(lib.b2_paged_decode(
+        _ptr(out), _ptr(q), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(seq_lens),
+        B, Hq, Hkv, d, bs, max_nb, nb, qs, os_, bstride, hstride, float(scale), kvd,
+        _ptr(k_scale), _ptr(v_scale), _ptr(workspace), wbytes, num_splits, _stream(dev)))
+    return out

@@ -1,0 +1,123 @@
+// reshape_and_cache.cu -- KV write through slot_mapping.
+//
+// Contract: include/b200attn.h `b2_reshape_and_cache`.  Semantics follow vLLM's
+// `reshape_and_cache` (the op the engine launched by reference
+// benchmark-vllm/vllm_manager.py:371-374 runs after every QKV projection), on the HND cache
+// layout [num_blocks, Hkv, bs, d].
+//
+// HBM-bound byte mover: one CTA per token, one 16-byte vector (8 bf16) per thread per trip,
+// K and V handled by the same CTA.  Loads go through the non-allocating read-only path; the
+// scattered 256-byte row stores are full 32-byte sectors.  bf16 is a bit-exact copy; e4m3 is
+// `cvt.rn.satfinite.e4m3x2.f32(x / scale)`.
+#include "b2_common.cuh"
+
+namespace {
+
+template <bool FP8>
+__global__ void __launch_bounds__(256)
+reshape_and_cache_kernel(const __nv_bfloat16* __restrict__ k_new,
+                         const __nv_bfloat16* __restrict__ v_new,
+                         void* __restrict__ k_cache, void* __restrict__ v_cache,
+                         const int64_t* __restrict__ slot_mapping,
+                         int Hkv, int d, int bs,
+                         int64_t k_token_stride, int64_t v_token_stride,
+                         int64_t cache_block_stride, int64_t cache_head_stride,
+                         const float* __restrict__ k_scale, const float* __restrict__ v_scale) {
+    const int t = blockIdx.x;
+    const int64_t slot = slot_mapping[t];
+    if (slot < 0) return;  // padding token
+    const int64_t blk = slot / bs;
+    const int off = static_cast<int>(slot - blk * bs);
+    const int vec_per_head = d >> 3;
+    const int nvec = Hkv * vec_per_head;
+
+    float ks = 1.f, vs = 1.f;
+    if (FP8) {
+        ks = *k_scale;
+        vs = *v_scale;
+    }
+
+    for (int i = threadIdx.x; i < 2 * nvec; i += blockDim.x) {
+        const bool is_v = i >= nvec;
+        const int j = is_v ? i - nvec : i;
+        const int h = j / vec_per_head;
+        const int c = j - h * vec_per_head;
+        const __nv_bfloat16* src =
+            (is_v ? v_new + t * v_token_stride : k_new + t * k_token_stride) + h * d + c * 8;
+        const int4 val = b2::ld_nc_16(src);
+        const int64_t dst_elem =
+            blk * cache_block_stride + h * cache_head_stride + static_cast<int64_t>(off) * d + c * 8;
+        if (!FP8) {
+            __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(is_v ? v_cache : k_cache) + dst_elem;
+            *reinterpret_cast<int4*>(dst) = val;
+        } else {
+            const float s = is_v ? vs : ks;
+            const uint32_t w[4] = {static_cast<uint32_t>(val.x), static_cast<uint32_t>(val.y),
+                                   static_cast<uint32_t>(val.z), static_cast<uint32_t>(val.w)};
+            uint32_t packed[2];
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                uint32_t acc = 0;
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const uint32_t word = w[p * 2 + q];
+                    // bf16 -> f32 is a 16-bit shift; the division is IEEE (matches the oracle)
+                    const float lo = __fdiv_rn(__uint_as_float(word << 16), s);
+                    const float hi = __fdiv_rn(__uint_as_float(word & 0xffff0000u), s);
+                    const __nv_fp8x2_storage_t pr =
+                        __nv_cvt_float2_to_fp8x2(make_float2(lo, hi), __NV_SATFINITE, __NV_E4M3);
+                    acc |= static_cast<uint32_t>(pr) << (16 * q);
+                }
+                packed[p] = acc;
+            }
+            uint8_t* dst = static_cast<uint8_t*>(is_v ? v_cache : k_cache) + dst_elem;
+            *reinterpret_cast<uint2*>(dst) = make_uint2(packed[0], packed[1]);
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" int b2_reshape_and_cache(const void* k_new, const void* v_new, void* k_cache,
+                                    void* v_cache, const int64_t* slot_mapping, int T, int Hkv,
+                                    int d, int bs, int64_t k_token_stride, int64_t v_token_stride,
+                                    int64_t cache_block_stride, int64_t cache_head_stride,
+                                    int kv_dtype, const float* k_scale, const float* v_scale,
+                                    void* stream) {
+    B2_REQUIRE(T >= 0 && Hkv > 0 && d > 0 && bs > 0, B2_EINVAL,
+               "reshape_and_cache: bad sizes T=%d Hkv=%d d=%d bs=%d", T, Hkv, d, bs);
+    if (T == 0) return B2_OK;
+    B2_REQUIRE(k_new && v_new && k_cache && v_cache && slot_mapping, B2_EINVAL,
+               "reshape_and_cache: null pointer");
+    B2_REQUIRE(kv_dtype == B2_KV_BF16 || kv_dtype == B2_KV_FP8_E4M3, B2_EUNSUPPORTED,
+               "reshape_and_cache: kv_dtype %d", kv_dtype);
+    B2_REQUIRE(d % 8 == 0, B2_EUNSUPPORTED, "reshape_and_cache: d=%d must be a multiple of 8", d);
+    B2_REQUIRE(b2_aligned16(k_new) && b2_aligned16(v_new) && b2_aligned16(k_cache) &&
+                   b2_aligned16(v_cache),
+               B2_EINVAL, "reshape_and_cache: pointers must be 16-byte aligned");
+    B2_REQUIRE(k_token_stride % 8 == 0 && v_token_stride % 8 == 0 && cache_block_stride % 16 == 0 &&
+                   cache_head_stride % 16 == 0,
+               B2_EINVAL, "reshape_and_cache: strides must keep 16-byte alignment");
+    B2_REQUIRE(k_token_stride >= (int64_t)Hkv * d && v_token_stride >= (int64_t)Hkv * d &&
+                   cache_head_stride >= (int64_t)bs * d,
+               B2_EINVAL, "reshape_and_cache: strides overlap");
+    if (kv_dtype == B2_KV_FP8_E4M3)
+        B2_REQUIRE(k_scale && v_scale, B2_EINVAL, "reshape_and_cache: fp8 needs k_scale/v_scale");
+
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nvec2 = 2 * Hkv * (d / 8);
+    int threads = nvec2 < 256 ? ((nvec2 + 31) / 32) * 32 : 256;
+    const __nv_bfloat16* kn = static_cast<const __nv_bfloat16*>(k_new);
+    const __nv_bfloat16* vn = static_cast<const __nv_bfloat16*>(v_new);
+    if (kv_dtype == B2_KV_BF16) {
+        reshape_and_cache_kernel<false><<<T, threads, 0, st>>>(
+            kn, vn, k_cache, v_cache, slot_mapping, Hkv, d, bs, k_token_stride, v_token_stride,
+            cache_block_stride, cache_head_stride, nullptr, nullptr);
+    } else {
+        reshape_and_cache_kernel<true><<<T, threads, 0, st>>>(
+            kn, vn, k_cache, v_cache, slot_mapping, Hkv, d, bs, k_token_stride, v_token_stride,
+            cache_block_stride, cache_head_stride, k_scale, v_scale);
+    }
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}
