@@ -53,9 +53,11 @@ def test_argument_validation_without_gpu():
     rc = lib.b2_reshape_and_cache(16, 16, 16, 16, 16, 4, 2, 128, 16, 256, 256, 4096, 2048, 7, None, None, None)
     assert rc == _lib.B2_EUNSUPPORTED
     assert lib.b2_paged_decode_workspace_bytes(64, 32, 8, 128, 16, 256, 1) == 0
-    n = lib.b2_paged_decode_auto_splits(64, 32, 8, 128, 16, 256, 0)
-    assert n >= 1
-    assert lib.b2_paged_decode_workspace_bytes(64, 32, 8, 128, 16, 256, 0) == 64 * 32 * n * 129 * 4
+    assert lib.b2_paged_decode_auto_splits(64, 32, 8, 128, 16, 256, 0) == 0      # 0 = persistent schedule
+    assert lib.b2_paged_decode_workspace_bytes(64, 32, 8, 128, 16, 256, 4) == 64 * 32 * 4 * 129 * 4
+    # persistent schedule: two partial slots per CTA, independent of the batch size
+    w = lib.b2_paged_decode_workspace_bytes(64, 32, 8, 128, 16, 256, 0)
+    assert w == lib.b2_paged_decode_workspace_bytes(4, 32, 8, 128, 16, 256, 0) and w % (2 * 8 * 129 * 4) == 0
 
 
 def test_ops_refuse_cpu_tensors():

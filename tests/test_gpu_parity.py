@@ -280,7 +280,8 @@ def _full_size(cuda, B, Hq, Hkv, ctx, fp8, seed, n_oracle=2):
     # (4) permuting which sequence sits in which batch row permutes the output rows
     perm = torch.randperm(B, generator=torch.Generator().manual_seed(1)).to(cuda)
     out_p = b200attn.paged_decode(q[perm].contiguous(), kc, vc, bt[perm].contiguous(), sl[perm].contiguous(), **kw)
-    assert torch.equal(out_p, out_auto[perm])
+    # (the persistent schedule cuts segments by batch position, so rows agree to rounding, not bitwise)
+    assert_close(out_p, out_auto[perm].float(), what="batch-row permutation")
 
 
 def test_full_size_config2_llama3_8b_b64_ctx4k(cuda):

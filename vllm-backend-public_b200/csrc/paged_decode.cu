@@ -6,20 +6,29 @@
 // (reference benchmark-vllm/vllm_manager.py:371-374); block_size / max_num_seqs / max_model_len
 // come from reference benchmark-vllm/models.py:9,10,15.
 //
-// Design (HBM-bound gather; see DESIGN.md section 3):
-//   * grid = (split, kv_head x head_group, seq).  One CTA streams the K and V tiles of its
-//     (sequence, kv head, KV-length split) exactly once and serves all G = Hq/Hkv query heads
-//     that share that kv head, so KV bytes are read once per kv head, not once per q head.
+// Design (HBM-bound gather; DESIGN.md section 3):
+//   * Work unit = one KV block of one (sequence, kv head [, head group]) item.  The flattened unit
+//     space is cut into equal contiguous ranges, one per persistent CTA (2 CTAs per SM), so every
+//     CTA streams the same number of bytes regardless of batch size or ragged lengths ("stream-K"
+//     over the KV length).  A range is a list of segments (item, block range).
+//   * One CTA serves all G = Hq/Hkv query heads that share the kv head, so KV bytes are read once
+//     per kv head, not once per q head.
 //   * warp 4 is the producer: it walks the block table and issues one TMA tiled copy
 //     (cp.async.bulk.tensor.4d, 128-byte swizzle, L2 evict-first) per 16 x 64-element half tile
 //     into a ring of NSTAGE x 64-token stages; completion is counted in bytes on an mbarrier.
+//     The ring keeps running across segment boundaries.
 //   * warps 0-3 are consumers: each owns 16 tokens of every stage.  S^T = K.Q^T and
 //     O^T += V^T.P^T run on mma.sync m16n8k16 (tokens / head_dim on the M side, the <=8 grouped
 //     query heads on the N side, so no MMA row is wasted on padding tokens); ldmatrix(.trans)
 //     feeds the A operand straight from the swizzled stage; softmax is fp32 with warp shuffles;
 //     the P^T B-operand is produced from the S^T accumulator by movmatrix.
-//   * the four consumers merge their (m, l, O) in shared memory; with num_splits > 1 the CTA
-//     writes a normalised partial + log2-sum-exp and `merge_splits_kernel` combines them.
+//   * at a segment end the four consumers tree-merge their (m, l, O) through a small scratch
+//     area; a segment that covers its whole item writes bf16 output directly, otherwise a
+//     normalised partial + log2-sum-exp goes to one of the CTA's two workspace slots and
+//     `merge_boundary_kernel` (launched with programmatic dependent launch) combines the
+//     partials of the items that straddle a CTA boundary.
+//   * num_splits >= 1 selects the classic grid-split schedule (v1/v2 style, one CTA per
+//     (split, kv head, sequence)) built from the same producer/consumer code.
 #include "b2_common.cuh"
 
 namespace {
@@ -28,6 +37,7 @@ constexpr int D = 128;        // head_dim (Llama-3 geometry)
 constexpr int NCW = 4;        // consumer warps
 constexpr int TOK = NCW * 16; // tokens per pipeline stage
 constexpr int NTHREADS = (NCW + 1) * 32;
+constexpr int MIN_TOK_PER_CTA = 128;   // persistent schedule: do not cut work finer than this
 constexpr float LOG2E = 1.4426950408889634f;
 
 struct DecodeParams {
@@ -35,11 +45,11 @@ struct DecodeParams {
     const __nv_bfloat16* q;
     const int32_t* block_tables;
     const int32_t* seq_lens;
-    float* ws_o;     // [B, Hq, num_splits, D] normalised partial outputs
-    float* ws_lse;   // [B, Hq, num_splits]    log2-sum-exp of each partial
+    float* ws_o;     // grid-split: [B, Hq, num_splits, D]   persistent: [NC*2, HEADS, D]
+    float* ws_lse;   // grid-split: [B, Hq, num_splits]      persistent: [NC*2, HEADS]
     const float* k_scale;
     const float* v_scale;
-    int Hq, Hkv, G, HG, max_nb, num_splits, split_tokens;
+    int B, Hq, Hkv, G, HG, max_nb, num_splits, split_tokens;
     int64_t q_stride, out_stride;
     float scale_log2;  // softmax scale * log2(e)
 };
@@ -55,10 +65,13 @@ struct Cfg {
     static constexpr int BOX_BYTES = BS * 128;     // one TMA box
     static constexpr int HEADS = 8 * NT;           // q heads served per CTA
     static constexpr int RING_BYTES = NSTAGE * STAGE_BYTES;
-    static constexpr int MERGE_BYTES = NCW * (D * HEADS + 2 * HEADS) * 4;
-    static constexpr int SMEM_BYTES = 1024 + RING_BYTES + 2 * NSTAGE * 8;
+    static constexpr int BAR_BYTES = 2 * NSTAGE * 8 + 16;
+    static constexpr int SLOT_FLOATS = 32 * NT * 32 + 4 * NT * 4;   // O^T fragments + (m, l) of one warp
+    static constexpr int SCRATCH_BYTES = 2 * SLOT_FLOATS * 4;
+    static constexpr int SMEM_BYTES = RING_BYTES + BAR_BYTES + SCRATCH_BYTES;
     static_assert(TOK % BS == 0 && BS % 8 == 0, "block size must divide the stage and keep the swizzle phase");
-    static_assert(MERGE_BYTES <= RING_BYTES, "merge scratch reuses the ring");
+    static_assert(RING_BYTES % 1024 == 0, "stages must stay 1024-byte aligned");
+    static_assert(2 * (SMEM_BYTES + 1024) <= 233472, "two CTAs per SM must fit");
 };
 
 // fp8 (e4m3 x2, low 16 bits of `v`) -> f16x2, exact
@@ -80,28 +93,385 @@ __device__ __forceinline__ void mma_f16_16816(float (&c)[4], uint32_t a0, uint32
         : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
-
 template <bool FP8>
 __device__ __forceinline__ void mma_kv(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2,
                                        uint32_t a3, uint32_t b0, uint32_t b1) {
     if (FP8) mma_f16_16816(c, a0, a1, a2, a3, b0, b1);
     else b2::mma_bf16_16816(c, a0, a1, a2, a3, b0, b1);
 }
+__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(NCW * 32) : "memory"); }
 
-template <int BS, bool FP8, int NT, int NSTAGE, int MINB>
-__global__ void __launch_bounds__(NTHREADS, MINB)
-paged_decode_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                    const DecodeParams p) {
+// ---------------------------------------------------------------------------------------------
+// producer: stream the blocks [blk_begin, blk_begin + n_blk) of one (sequence, kv head) into the ring
+// ---------------------------------------------------------------------------------------------
+template <class C, int NSTAGE>
+__device__ __forceinline__ void produce_segment(const CUtensorMap* tmK, const CUtensorMap* tmV,
+                                                const int32_t* __restrict__ bt, int n_blk, int kvh,
+                                                uint32_t ring, uint32_t bar_full, uint32_t bar_empty,
+                                                uint32_t& it, int lane, uint64_t pol) {
+    const int n_stage = (n_blk + C::BLK_PER_STAGE - 1) / C::BLK_PER_STAGE;
+    int cur = (lane < n_blk) ? bt[lane] : 0;            // 32 table entries per batch
+    int nxt = (32 + lane < n_blk) ? bt[32 + lane] : 0;  // next batch, prefetched
+    for (int st = 0; st < n_stage; ++st, ++it) {
+        const uint32_t s = it % NSTAGE;
+        const uint32_t ph = (it / NSTAGE) & 1;
+        b2::mbar_wait(bar_empty + s * 8, ph ^ 1);
+        const int nb_stage = min(C::BLK_PER_STAGE, n_blk - st * C::BLK_PER_STAGE);
+        const uint32_t kdst = ring + s * C::STAGE_BYTES;
+        const uint32_t vdst = kdst + C::TILE_BYTES;
+        if (lane == 0)
+            b2::mbar_arrive_expect_tx(bar_full + s * 8, nb_stage * 2 * C::NHALF * C::BOX_BYTES);
+#pragma unroll
+        for (int j = 0; j < C::BLK_PER_STAGE; ++j) {
+            const int gi = st * C::BLK_PER_STAGE + j;
+            const int src = gi & 31;
+            const int blk = __shfl_sync(0xffffffffu, cur, src);
+            if (j < nb_stage && lane == 0) {
+#pragma unroll
+                for (int h = 0; h < C::NHALF; ++h) {
+                    const uint32_t off = h * (TOK * 128) + j * C::BOX_BYTES;
+                    b2::tma_load_4d(kdst + off, tmK, bar_full + s * 8, h * 64, 0, kvh, blk, pol);
+                    b2::tma_load_4d(vdst + off, tmV, bar_full + s * 8, h * 64, 0, kvh, blk, pol);
+                }
+            }
+            if (src == 31) {  // warp-uniform: this batch of 32 entries is used up
+                cur = nxt;
+                nxt = (gi + 33 + lane < n_blk) ? bt[gi + 33 + lane] : 0;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// consumer state: one warp's running softmax over its token slabs
+// ---------------------------------------------------------------------------------------------
+template <int NT>
+struct WarpAcc {
+    float o[NT][8][4];     // O^T fragments: [n-tile][d-tile][c0..c3]
+    float m[NT][2];        // running max (raw scores) of heads 2*t4, 2*t4+1
+    float l[NT][2];        // running sum (lane-local until reduce_l)
+    __device__ __forceinline__ void reset() {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            m[nt][0] = m[nt][1] = -INFINITY;
+            l[nt][0] = l[nt][1] = 0.f;
+#pragma unroll
+            for (int dt = 0; dt < 8; ++dt) o[nt][dt][0] = o[nt][dt][1] = o[nt][dt][2] = o[nt][dt][3] = 0.f;
+        }
+    }
+    // lane-local row sums -> sums over the 16 token rows (lanes differing in g)
+    __device__ __forceinline__ void reduce_l() {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                float v = l[nt][j];
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                l[nt][j] = v;
+            }
+    }
+    // fragment-layout dump / combine: partner lanes hold the same (d, head) positions
+    __device__ __forceinline__ void dump(float* slot, int lane) const {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int dt = 0; dt < 8; ++dt)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) slot[((nt * 8 + dt) * 4 + i) * 32 + lane] = o[nt][dt][i];
+        if (lane < 4) {
+            float* ml = slot + 32 * NT * 32 + lane * (4 * NT);
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                ml[nt * 4 + 0] = m[nt][0];
+                ml[nt * 4 + 1] = m[nt][1];
+                ml[nt * 4 + 2] = l[nt][0];
+                ml[nt * 4 + 3] = l[nt][1];
+            }
+        }
+    }
+    __device__ __forceinline__ void combine(const float* slot, int lane, float sl2) {
+        const float* ml = slot + 32 * NT * 32 + (lane & 3) * (4 * NT);
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            float wa[2], wb[2];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const float mb = ml[nt * 4 + j], lb = ml[nt * 4 + 2 + j];
+                const float M = fmaxf(m[nt][j], mb);
+                wa[j] = (m[nt][j] == -INFINITY) ? 0.f : b2::fast_exp2((m[nt][j] - M) * sl2);
+                wb[j] = (mb == -INFINITY) ? 0.f : b2::fast_exp2((mb - M) * sl2);
+                l[nt][j] = wa[j] * l[nt][j] + wb[j] * lb;
+                m[nt][j] = M;
+            }
+#pragma unroll
+            for (int dt = 0; dt < 8; ++dt)
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    o[nt][dt][i] = wa[i & 1] * o[nt][dt][i] + wb[i & 1] * slot[((nt * 8 + dt) * 4 + i) * 32 + lane];
+        }
+    }
+};
+
+// Q^T as the B operand of S^T = K.Q^T: b0 = Q[head g][k-pair], b1 = the +8 pair.
+// bf16: logical k == physical d.  fp8: ldmatrix hands each thread 4 consecutive fp8 of a 16-element
+// chunk, so logical k = 2*t4+{0,1} <-> d = 16kc + 4*t4 + {0,1} and the +8 pair <-> d = 16kc + 4*t4 + {2,3};
+// the contraction is permutation invariant.
+template <bool FP8, int NT>
+__device__ __forceinline__ void load_q_frags(uint32_t (&qf)[NT][8][2], const __nv_bfloat16* __restrict__ qbase,
+                                             int nheads, int lane) {
+    const int g = lane >> 2, t4 = lane & 3;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        const int hl = nt * 8 + g;
+        const bool valid = hl < nheads;
+        const uint32_t* qrow = reinterpret_cast<const uint32_t*>(qbase + (int64_t)(valid ? hl : 0) * D);
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            uint32_t w0, w1;
+            if (!FP8) {
+                w0 = qrow[kc * 8 + t4];
+                w1 = qrow[kc * 8 + 4 + t4];
+            } else {
+                w0 = qrow[kc * 8 + 2 * t4];
+                w1 = qrow[kc * 8 + 2 * t4 + 1];
+                // bf16x2 -> f16x2 (the fp8 path runs the f16 MMA; see DESIGN.md on range)
+                w0 = pack_f16x2(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u));
+                w1 = pack_f16x2(__uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
+            }
+            qf[nt][kc][0] = valid ? w0 : 0u;
+            qf[nt][kc][1] = valid ? w1 : 0u;
+        }
+    }
+}
+
+// One warp, one stage: 16 token rows [row_base, row_base+16) of which the first `nvalid` are real.
+template <class C, bool FP8, int NT>
+__device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&qf)[NT][8][2], uint32_t kbase,
+                                             uint32_t vbase, int row_base, int nvalid, float sl2, int lane) {
+    const int g = lane >> 2, t4 = lane & 3;
+    const int mi = lane >> 3, ri = lane & 7;   // ldmatrix: lane -> (matrix, row)
+
+    // ------------------------------ S^T = K . Q^T ------------------------------
+    float sacc[NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
+    if (!FP8) {
+        // matrices: 0 = rows 0-7 / chunk lo, 1 = rows 8-15 / lo, 2 = rows 0-7 / hi, 3 = rows 8-15 / hi
+        const int row = row_base + (mi & 1) * 8 + ri;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            const int chunk = 2 * kc + (mi >> 1);        // 16-byte chunk of the 256-byte row
+            const uint32_t addr = kbase + (chunk >> 3) * (TOK * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            uint32_t a0, a1, a2, a3;
+            b2::ldmatrix_x4(addr, a0, a1, a2, a3);
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) mma_kv<FP8>(sacc[nt], a0, a1, a2, a3, qf[nt][kc][0], qf[nt][kc][1]);
+        }
+    } else {
+        // fp8 rows are 128 bytes = 8 chunks of 16 elements; one ldmatrix.x4 covers two k-chunks:
+        // matrices: 0 = rows 0-7 / chunk c, 1 = rows 8-15 / c, 2 = rows 0-7 / c+1, 3 = rows 8-15 / c+1
+        const int row = row_base + (mi & 1) * 8 + ri;
+#pragma unroll
+        for (int kc2 = 0; kc2 < 4; ++kc2) {
+            const int chunk = 2 * kc2 + (mi >> 1);
+            const uint32_t addr = kbase + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            uint32_t r0, r1, r2, r3;
+            b2::ldmatrix_x4(addr, r0, r1, r2, r3);
+            const uint32_t a0 = e4m3x2_to_f16x2(r0), a1 = e4m3x2_to_f16x2(r1);
+            const uint32_t a2 = e4m3x2_to_f16x2(r0 >> 16), a3 = e4m3x2_to_f16x2(r1 >> 16);
+            const uint32_t c0 = e4m3x2_to_f16x2(r2), c1 = e4m3x2_to_f16x2(r3);
+            const uint32_t c2 = e4m3x2_to_f16x2(r2 >> 16), c3 = e4m3x2_to_f16x2(r3 >> 16);
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                mma_kv<FP8>(sacc[nt], a0, a1, a2, a3, qf[nt][2 * kc2][0], qf[nt][2 * kc2][1]);
+                mma_kv<FP8>(sacc[nt], c0, c1, c2, c3, qf[nt][2 * kc2 + 1][0], qf[nt][2 * kc2 + 1][1]);
+            }
+        }
+    }
+    // sacc[nt] = {S[tok g][head 2t4], S[tok g][2t4+1], S[tok g+8][2t4], S[tok g+8][2t4+1]}
+    if (nvalid < 16) {
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            if (g >= nvalid) sacc[nt][0] = sacc[nt][1] = -INFINITY;
+            if (g + 8 >= nvalid) sacc[nt][2] = sacc[nt][3] = -INFINITY;
+        }
+    }
+
+    // ------------------------------ online softmax ------------------------------
+    uint32_t pb[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        float pr[4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            float mx = fmaxf(sacc[nt][j], sacc[nt][j + 2]);
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+            const float m_new = fmaxf(acc.m[nt][j], mx);       // finite: the slab has a valid token
+            const float alpha = b2::fast_exp2((acc.m[nt][j] - m_new) * sl2);
+            const float ms = m_new * sl2;
+            pr[j] = b2::fast_exp2(fmaf(sacc[nt][j], sl2, -ms));
+            pr[j + 2] = b2::fast_exp2(fmaf(sacc[nt][j + 2], sl2, -ms));
+            acc.m[nt][j] = m_new;
+            acc.l[nt][j] = fmaf(acc.l[nt][j], alpha, pr[j] + pr[j + 2]);
+#pragma unroll
+            for (int dt = 0; dt < 8; ++dt) {
+                acc.o[nt][dt][j] *= alpha;
+                acc.o[nt][dt][j + 2] *= alpha;
+            }
+        }
+        // P^T as the B operand of O^T += V^T.P^T: transpose the 8x8 (token x head) tiles
+        const uint32_t x0 = FP8 ? pack_f16x2(pr[0], pr[1]) : b2::pack_bf16x2(pr[0], pr[1]);
+        const uint32_t x1 = FP8 ? pack_f16x2(pr[2], pr[3]) : b2::pack_bf16x2(pr[2], pr[3]);
+        pb[nt][0] = b2::movmatrix_trans(x0);   // (tokens 2t4,2t4+1 ; head g)
+        pb[nt][1] = b2::movmatrix_trans(x1);   // (tokens 8+2t4,.. ; head g)
+    }
+
+    // ------------------------------ O^T += V^T . P^T -----------------------------
+    // V garbage beyond seq_len must not reach the MMA (0 * NaN): zero those token columns.
+    uint32_t mk_lo = 0xffffffffu, mk_hi = 0xffffffffu;
+    if (nvalid < 16) {
+        mk_lo = (2 * t4 < nvalid ? 0x0000ffffu : 0u) | (2 * t4 + 1 < nvalid ? 0xffff0000u : 0u);
+        mk_hi = (8 + 2 * t4 < nvalid ? 0x0000ffffu : 0u) | (9 + 2 * t4 < nvalid ? 0xffff0000u : 0u);
+    }
+    if (!FP8) {
+        // .trans matrices: 0 = tokens 0-7 / d lo, 1 = tokens 0-7 / d hi, 2 = tokens 8-15 / lo, 3 = tokens 8-15 / hi
+        const int row = row_base + (mi >> 1) * 8 + ri;
+#pragma unroll
+        for (int dt = 0; dt < 8; ++dt) {
+            const int chunk = 2 * dt + (mi & 1);
+            const uint32_t addr = vbase + (chunk >> 3) * (TOK * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            uint32_t a0, a1, a2, a3;
+            b2::ldmatrix_x4_trans(addr, a0, a1, a2, a3);
+            a0 &= mk_lo; a1 &= mk_lo; a2 &= mk_hi; a3 &= mk_hi;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) mma_kv<FP8>(acc.o[nt][dt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
+        }
+    } else {
+        // A 16-byte fp8 chunk holds 16 d values, so the b16 transpose moves (d 2g, d 2g+1) pairs: a thread
+        // receives {tok 2t4: d 2g, d 2g+1 ; tok 2t4+1: d 2g, d 2g+1}.  PRMT regroups it to {d 2g: tok pair ;
+        // d 2g+1: tok pair}; MMA row g <-> d = 16c + 2g, row g+8 <-> d = 16c + 2g + 1.
+        // .trans matrices: 0 = tokens 0-7 / chunk c, 1 = tokens 8-15 / c, 2 = tokens 0-7 / c+1, 3 = tokens 8-15 / c+1
+        const int row = row_base + (mi & 1) * 8 + ri;
+#pragma unroll
+        for (int dt2 = 0; dt2 < 4; ++dt2) {
+            const int chunk = 2 * dt2 + (mi >> 1);
+            const uint32_t addr = vbase + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            uint32_t r0, r1, r2, r3;
+            b2::ldmatrix_x4_trans(addr, r0, r1, r2, r3);
+            r0 = __byte_perm(r0, 0, 0x3120); r1 = __byte_perm(r1, 0, 0x3120);
+            r2 = __byte_perm(r2, 0, 0x3120); r3 = __byte_perm(r3, 0, 0x3120);
+            const uint32_t a0 = e4m3x2_to_f16x2(r0) & mk_lo, a1 = e4m3x2_to_f16x2(r0 >> 16) & mk_lo;
+            const uint32_t a2 = e4m3x2_to_f16x2(r1) & mk_hi, a3 = e4m3x2_to_f16x2(r1 >> 16) & mk_hi;
+            const uint32_t c0 = e4m3x2_to_f16x2(r2) & mk_lo, c1 = e4m3x2_to_f16x2(r2 >> 16) & mk_lo;
+            const uint32_t c2 = e4m3x2_to_f16x2(r3) & mk_hi, c3 = e4m3x2_to_f16x2(r3 >> 16) & mk_hi;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                mma_kv<FP8>(acc.o[nt][2 * dt2], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
+                mma_kv<FP8>(acc.o[nt][2 * dt2 + 1], c0, c1, c2, c3, pb[nt][0], pb[nt][1]);
+            }
+        }
+    }
+}
+
+// Consume the stages of one segment (n_tok tokens starting at a block boundary).
+template <class C, bool FP8, int NT, int NSTAGE>
+__device__ __forceinline__ void consume_segment(WarpAcc<NT>& acc, const uint32_t (&qf)[NT][8][2], int n_tok,
+                                                uint32_t ring, uint32_t bar_full, uint32_t bar_empty,
+                                                uint32_t& it, float sl2, int warp, int lane) {
+    const int n_stage = (n_tok + TOK - 1) / TOK;
+    const int row_base = warp * 16;
+    for (int st = 0; st < n_stage; ++st, ++it) {
+        const uint32_t s = it % NSTAGE;
+        const uint32_t ph = (it / NSTAGE) & 1;
+        b2::mbar_wait(bar_full + s * 8, ph);
+        const int nvalid = n_tok - (st * TOK + row_base);   // valid tokens in this warp's slab
+        if (nvalid > 0) {
+            const uint32_t kbase = ring + s * C::STAGE_BYTES;
+            consume_slab<C, FP8, NT>(acc, qf, kbase, kbase + C::TILE_BYTES, row_base, nvalid, sl2, lane);
+        }
+        __syncwarp();
+        if (lane == 0) b2::mbar_arrive(bar_empty + s * 8);   // stage may be overwritten
+    }
+}
+
+// Tree merge of the four consumer warps; the result lands in warp 0's accumulator.
+template <int NT>
+__device__ __forceinline__ void merge_warps(WarpAcc<NT>& acc, float* scratch, int slot_floats, float sl2,
+                                            int warp, int lane) {
+    acc.reduce_l();
+    if (warp >= 2) acc.dump(scratch + (warp - 2) * slot_floats, lane);
+    consumer_bar();
+    if (warp < 2) acc.combine(scratch + warp * slot_floats, lane, sl2);
+    consumer_bar();
+    if (warp == 1) acc.dump(scratch, lane);
+    consumer_bar();
+    if (warp == 0) acc.combine(scratch, lane, sl2);
+    consumer_bar();   // scratch is free for the next segment
+}
+
+// Warp 0 writes the merged result: final bf16 rows, or a normalised fp32 partial + log2-sum-exp.
+// MMA row r of d-tile dt <-> d = 16dt + r (bf16) or rows g / g+8 <-> d = 16dt + 2g / 2g+1 (fp8).
+template <bool FP8, int NT>
+__device__ __forceinline__ void write_result(const WarpAcc<NT>& acc, int nheads, float vs, float sl2,
+                                             __nv_bfloat16* out_rows /* [head][D] or null */,
+                                             float* part_o /* [head][D] */, float* part_lse /* [head] */,
+                                             int lane) {
+    const int g = lane >> 2, t4 = lane & 3;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int h = nt * 8 + 2 * t4 + j;
+            if (h >= nheads) continue;
+            const float L = acc.l[nt][j];
+            const float inv = L > 0.f ? vs / L : 0.f;
+#pragma unroll
+            for (int dt = 0; dt < 8; ++dt) {
+                const int d_lo = FP8 ? 16 * dt + 2 * g : 16 * dt + g;
+                const int d_hi = FP8 ? d_lo + 1 : d_lo + 8;
+                const float v_lo = acc.o[nt][dt][j] * inv, v_hi = acc.o[nt][dt][j + 2] * inv;
+                if (out_rows) {
+                    out_rows[h * D + d_lo] = __float2bfloat16(v_lo);
+                    out_rows[h * D + d_hi] = __float2bfloat16(v_hi);
+                } else {
+                    part_o[h * D + d_lo] = v_lo;
+                    part_o[h * D + d_hi] = v_hi;
+                }
+            }
+            if (!out_rows && g == 0) part_lse[h] = L > 0.f ? fmaf(acc.m[nt][j], sl2, log2f(L)) : -INFINITY;
+        }
+}
+
+__device__ __forceinline__ void init_pipeline(uint32_t bar_full, uint32_t bar_empty, int nstage, int tid) {
+    if (tid == 0) {
+        for (int s = 0; s < nstage; ++s) {
+            b2::mbar_init(bar_full + s * 8, 1);       // producer's arrive.expect_tx
+            b2::mbar_init(bar_empty + s * 8, NCW);    // one arrive per consumer warp
+        }
+        b2::fence_mbar_init();
+    }
+    __syncthreads();
+}
+
+// =============================================================================================
+// schedule A: classic grid split, one CTA per (split, kv head x head group, sequence)
+// =============================================================================================
+template <int BS, bool FP8, int NT, int NSTAGE>
+__global__ void __launch_bounds__(NTHREADS, 2)
+paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                          const DecodeParams p) {
     using C = Cfg<BS, FP8, NT, NSTAGE>;
-    extern __shared__ uint8_t smem_raw[];
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
 
     const int split = blockIdx.x;
     const int kvh = blockIdx.y / p.HG;
     const int hg = blockIdx.y - kvh * p.HG;
     const int b = blockIdx.z;
-    const int tid = threadIdx.x;
-    const int warp = tid >> 5;
-    const int lane = tid & 31;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     const int seq_len = p.seq_lens[b];
     const int t_begin = split * p.split_tokens;
@@ -110,343 +480,66 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_consta
 
     if (t_begin >= seq_len) {
         // empty split: nothing to read.  Single-pass mode must still define the output row.
-        if (p.num_splits == 1) {
+        if (p.num_splits == 1)
             for (int i = tid; i < nheads * D; i += NTHREADS)
-                p.out[b * p.out_stride + (int64_t)(head0 + i / D) * D + (i % D)] = __float2bfloat16(0.f);
-        }
+                p.out[b * p.out_stride + (int64_t)head0 * D + i] = __float2bfloat16(0.f);
         return;
     }
-    const int t_end = min(seq_len, t_begin + p.split_tokens);
-    const int n_tok = t_end - t_begin;
-    const int n_stage = (n_tok + TOK - 1) / TOK;
-    const int n_blk = (n_tok + BS - 1) / BS;
-    const int blk0 = t_begin / BS;
+    const int n_tok = min(seq_len, t_begin + p.split_tokens) - t_begin;
 
-    const uint32_t base = (b2::smem_u32(smem_raw) + 1023u) & ~1023u;   // swizzle phase = address bits
-    const uint32_t bar_full = base + C::RING_BYTES;
+    const uint32_t ring = b2::smem_u32(smem_raw);
+    if (ring & 1023u) __trap();   // swizzle phase is derived from address bits
+    const uint32_t bar_full = ring + C::RING_BYTES;
     const uint32_t bar_empty = bar_full + NSTAGE * 8;
+    float* scratch = reinterpret_cast<float*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
+    init_pipeline(bar_full, bar_empty, NSTAGE, tid);
 
-    if (tid == 0) {
-        for (int s = 0; s < NSTAGE; ++s) {
-            b2::mbar_init(bar_full + s * 8, 1);       // producer's arrive.expect_tx
-            b2::mbar_init(bar_empty + s * 8, NCW);    // one arrive per consumer warp
-        }
-        b2::fence_mbar_init();
-    }
-    __syncthreads();
-
+    uint32_t it = 0;
     if (warp == NCW) {
-        // ================================ producer warp =====================================
         if (lane == 0) {
             b2::tma_prefetch_desc(&tmK);
             b2::tma_prefetch_desc(&tmV);
         }
         const uint64_t pol = b2::policy_evict_first();
-        const int32_t* bt = p.block_tables + (int64_t)b * p.max_nb + blk0;
-        int cur = (lane < n_blk) ? bt[lane] : 0;            // 32 table entries per batch
-        int nxt = (32 + lane < n_blk) ? bt[32 + lane] : 0;  // next batch, prefetched
-        for (int it = 0; it < n_stage; ++it) {
-            const int s = it % NSTAGE;
-            const uint32_t ph = (it / NSTAGE) & 1;
-            b2::mbar_wait(bar_empty + s * 8, ph ^ 1);
-            const int nb_stage = min(C::BLK_PER_STAGE, n_blk - it * C::BLK_PER_STAGE);
-            const uint32_t kdst = base + s * C::STAGE_BYTES;
-            const uint32_t vdst = kdst + C::TILE_BYTES;
-            if (lane == 0)
-                b2::mbar_arrive_expect_tx(bar_full + s * 8, nb_stage * 2 * C::NHALF * C::BOX_BYTES);
-#pragma unroll
-            for (int j = 0; j < C::BLK_PER_STAGE; ++j) {
-                const int gi = it * C::BLK_PER_STAGE + j;
-                const int src = gi & 31;
-                const int blk = __shfl_sync(0xffffffffu, cur, src);
-                if (j < nb_stage && lane == 0) {
-#pragma unroll
-                    for (int h = 0; h < C::NHALF; ++h) {
-                        const uint32_t off = h * (TOK * 128) + j * C::BOX_BYTES;
-                        b2::tma_load_4d(kdst + off, &tmK, bar_full + s * 8, h * 64, 0, kvh, blk, pol);
-                        b2::tma_load_4d(vdst + off, &tmV, bar_full + s * 8, h * 64, 0, kvh, blk, pol);
-                    }
-                }
-                if (src == 31) {  // warp-uniform: this batch of 32 entries is used up
-                    cur = nxt;
-                    nxt = (gi + 33 + lane < n_blk) ? bt[gi + 33 + lane] : 0;
-                }
-            }
-        }
+        produce_segment<C, NSTAGE>(&tmK, &tmV, p.block_tables + (int64_t)b * p.max_nb + t_begin / BS,
+                                   (n_tok + BS - 1) / BS, kvh, ring, bar_full, bar_empty, it, lane, pol);
     } else {
-        // ================================ consumer warps ====================================
-        const int g = lane >> 2;   // mma "group id": row of A/C, column of B
-        const int t4 = lane & 3;   // thread in group
-        float sl2 = p.scale_log2;
-        if (FP8) sl2 *= *p.k_scale;   // K dequant scale folds into the softmax scale
-
-        // ---- Q^T as the B operand of S^T = K.Q^T: b0 = Q[head g][k-pair], b1 = the +8 pair.
-        // bf16: logical k == physical d.  fp8: ldmatrix hands each thread 4 consecutive fp8 of a
-        // 16-element chunk, so logical k = 2*t4+{0,1} <-> d = 16kc + 4*t4 + {0,1} and the +8 pair
-        // <-> d = 16kc + 4*t4 + {2,3}; the contraction is permutation invariant.
+        float sl2 = p.scale_log2, vs = 1.f;
+        if (FP8) {
+            sl2 *= *p.k_scale;   // K dequant scale folds into the softmax scale
+            vs = *p.v_scale;     // V dequant scale folds into the epilogue
+        }
         uint32_t qf[NT][8][2];
+        load_q_frags<FP8, NT>(qf, p.q + b * p.q_stride + (int64_t)head0 * D, nheads, lane);
+        WarpAcc<NT> acc;
+        acc.reset();
+        consume_segment<C, FP8, NT, NSTAGE>(acc, qf, n_tok, ring, bar_full, bar_empty, it, sl2, warp, lane);
+        merge_warps<NT>(acc, scratch, C::SLOT_FLOATS, sl2, warp, lane);
+        if (warp == 0) {
+            if (p.num_splits == 1) {
+                write_result<FP8, NT>(acc, nheads, vs, sl2, p.out + b * p.out_stride + (int64_t)head0 * D, nullptr,
+                                      nullptr, lane);
+            } else {
+                // partial of q head (head0 + h) lives at ((b*Hq + head0 + h)*num_splits + split)
+                const int g = lane >> 2, t4 = lane & 3;
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            const int hl = nt * 8 + g;
-            const bool valid = hl < nheads;
-            const uint32_t* qrow =
-                reinterpret_cast<const uint32_t*>(p.q + b * p.q_stride + (int64_t)(head0 + (valid ? hl : 0)) * D);
-#pragma unroll
-            for (int kc = 0; kc < 8; ++kc) {
-                uint32_t w0, w1;
-                if (!FP8) {
-                    w0 = qrow[kc * 8 + t4];
-                    w1 = qrow[kc * 8 + 4 + t4];
-                } else {
-                    w0 = qrow[kc * 8 + 2 * t4];
-                    w1 = qrow[kc * 8 + 2 * t4 + 1];
-                    // bf16x2 -> f16x2 (the fp8 path runs the f16 MMA; see DESIGN.md on range)
-                    w0 = pack_f16x2(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u));
-                    w1 = pack_f16x2(__uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
-                }
-                qf[nt][kc][0] = valid ? w0 : 0u;
-                qf[nt][kc][1] = valid ? w1 : 0u;
-            }
-        }
-
-        float o[NT][8][4];
-        float m_run[NT][2], l_run[NT][2];
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            m_run[nt][0] = m_run[nt][1] = -INFINITY;
-            l_run[nt][0] = l_run[nt][1] = 0.f;
-#pragma unroll
-            for (int dt = 0; dt < 8; ++dt) o[nt][dt][0] = o[nt][dt][1] = o[nt][dt][2] = o[nt][dt][3] = 0.f;
-        }
-
-        // per-lane ldmatrix geometry: lane -> (matrix mi, row ri)
-        const int mi = lane >> 3, ri = lane & 7;
-        const int row_base = warp * 16;
-
-        for (int it = 0; it < n_stage; ++it) {
-            const int s = it % NSTAGE;
-            const uint32_t ph = (it / NSTAGE) & 1;
-            b2::mbar_wait(bar_full + s * 8, ph);
-            const int nvalid = n_tok - (it * TOK + row_base);   // valid tokens in this warp's slab
-            if (nvalid > 0) {
-                const uint32_t kbase = base + s * C::STAGE_BYTES;
-                const uint32_t vbase = kbase + C::TILE_BYTES;
-
-                // ------------------------------ S^T = K . Q^T ------------------------------
-                float sacc[NT][4];
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
-                if (!FP8) {
-                    // matrices: 0 = rows 0-7 / chunk lo, 1 = rows 8-15 / lo, 2 = rows 0-7 / hi, 3 = rows 8-15 / hi
-                    const int row = row_base + (mi & 1) * 8 + ri;
-#pragma unroll
-                    for (int kc = 0; kc < 8; ++kc) {
-                        const int chunk = 2 * kc + (mi >> 1);        // 16-byte chunk of the 256-byte row
-                        const uint32_t addr = kbase + (chunk >> 3) * (TOK * 128) + row * 128 +
-                                              (((chunk & 7) ^ (row & 7)) << 4);
-                        uint32_t a0, a1, a2, a3;
-                        b2::ldmatrix_x4(addr, a0, a1, a2, a3);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt)
-                            mma_kv<FP8>(sacc[nt], a0, a1, a2, a3, qf[nt][kc][0], qf[nt][kc][1]);
-                    }
-                } else {
-                    // fp8 rows are 128 bytes = 8 chunks of 16 elements; one ldmatrix.x4 covers two k-chunks:
-                    // matrices: 0 = rows 0-7 / chunk c, 1 = rows 8-15 / c, 2 = rows 0-7 / c+1, 3 = rows 8-15 / c+1
-                    const int row = row_base + (mi & 1) * 8 + ri;
-#pragma unroll
-                    for (int kc2 = 0; kc2 < 4; ++kc2) {
-                        const int chunk = 2 * kc2 + (mi >> 1);
-                        const uint32_t addr = kbase + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
-                        uint32_t r0, r1, r2, r3;
-                        b2::ldmatrix_x4(addr, r0, r1, r2, r3);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt) {
-                            mma_kv<FP8>(sacc[nt], e4m3x2_to_f16x2(r0), e4m3x2_to_f16x2(r1),
-                                        e4m3x2_to_f16x2(r0 >> 16), e4m3x2_to_f16x2(r1 >> 16),
-                                        qf[nt][2 * kc2][0], qf[nt][2 * kc2][1]);
-                            mma_kv<FP8>(sacc[nt], e4m3x2_to_f16x2(r2), e4m3x2_to_f16x2(r3),
-                                        e4m3x2_to_f16x2(r2 >> 16), e4m3x2_to_f16x2(r3 >> 16),
-                                        qf[nt][2 * kc2 + 1][0], qf[nt][2 * kc2 + 1][1]);
-                        }
-                    }
-                }
-                // sacc[nt] = {S[tok g][head 2t4], S[tok g][2t4+1], S[tok g+8][2t4], S[tok g+8][2t4+1]}
-                if (nvalid < 16) {
-#pragma unroll
-                    for (int nt = 0; nt < NT; ++nt) {
-                        if (g >= nvalid) sacc[nt][0] = sacc[nt][1] = -INFINITY;
-                        if (g + 8 >= nvalid) sacc[nt][2] = sacc[nt][3] = -INFINITY;
-                    }
-                }
-
-                // ------------------------------ online softmax ------------------------------
-                uint32_t pb[NT][2];
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    float pr[4];
+                for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
                     for (int j = 0; j < 2; ++j) {
-                        float mx = fmaxf(sacc[nt][j], sacc[nt][j + 2]);
-                        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
-                        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-                        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-                        const float m_new = fmaxf(m_run[nt][j], mx);       // finite: slab has a valid token
-                        const float alpha = b2::fast_exp2((m_run[nt][j] - m_new) * sl2);
-                        const float ms = m_new * sl2;
-                        pr[j] = b2::fast_exp2(fmaf(sacc[nt][j], sl2, -ms));
-                        pr[j + 2] = b2::fast_exp2(fmaf(sacc[nt][j + 2], sl2, -ms));
-                        m_run[nt][j] = m_new;
-                        l_run[nt][j] = fmaf(l_run[nt][j], alpha, pr[j] + pr[j + 2]);
+                        const int h = nt * 8 + 2 * t4 + j;
+                        if (h >= nheads) continue;
+                        const int64_t pi = ((int64_t)b * p.Hq + head0 + h) * p.num_splits + split;
+                        const float L = acc.l[nt][j];
+                        const float inv = vs / L;   // L > 0: the split holds at least one valid token
 #pragma unroll
                         for (int dt = 0; dt < 8; ++dt) {
-                            o[nt][dt][j] *= alpha;
-                            o[nt][dt][j + 2] *= alpha;
+                            const int d_lo = FP8 ? 16 * dt + 2 * g : 16 * dt + g;
+                            const int d_hi = FP8 ? d_lo + 1 : d_lo + 8;
+                            p.ws_o[pi * D + d_lo] = acc.o[nt][dt][j] * inv;
+                            p.ws_o[pi * D + d_hi] = acc.o[nt][dt][j + 2] * inv;
                         }
+                        if (g == 0) p.ws_lse[pi] = fmaf(acc.m[nt][j], sl2, log2f(L));
                     }
-                    // P^T as the B operand of O^T += V^T.P^T: transpose the 8x8 (token x head) tiles
-                    const uint32_t x0 = FP8 ? pack_f16x2(pr[0], pr[1]) : b2::pack_bf16x2(pr[0], pr[1]);
-                    const uint32_t x1 = FP8 ? pack_f16x2(pr[2], pr[3]) : b2::pack_bf16x2(pr[2], pr[3]);
-                    pb[nt][0] = b2::movmatrix_trans(x0);   // (tokens 2t4,2t4+1 ; head g)
-                    pb[nt][1] = b2::movmatrix_trans(x1);   // (tokens 8+2t4,.. ; head g)
-                }
-
-                // ------------------------------ O^T += V^T . P^T -----------------------------
-                // V garbage beyond seq_len must not reach the MMA (0 * NaN): zero those token columns.
-                uint32_t mk_lo = 0xffffffffu, mk_hi = 0xffffffffu;
-                if (nvalid < 16) {
-                    mk_lo = (2 * t4 < nvalid ? 0x0000ffffu : 0u) | (2 * t4 + 1 < nvalid ? 0xffff0000u : 0u);
-                    mk_hi = (8 + 2 * t4 < nvalid ? 0x0000ffffu : 0u) | (9 + 2 * t4 < nvalid ? 0xffff0000u : 0u);
-                }
-                if (!FP8) {
-                    // .trans matrices: 0 = tokens 0-7 / d lo, 1 = tokens 0-7 / d hi, 2 = tokens 8-15 / lo, 3 = tokens 8-15 / hi
-                    const int row = row_base + (mi >> 1) * 8 + ri;
-#pragma unroll
-                    for (int dt = 0; dt < 8; ++dt) {
-                        const int chunk = 2 * dt + (mi & 1);
-                        const uint32_t addr = vbase + (chunk >> 3) * (TOK * 128) + row * 128 +
-                                              (((chunk & 7) ^ (row & 7)) << 4);
-                        uint32_t a0, a1, a2, a3;
-                        b2::ldmatrix_x4_trans(addr, a0, a1, a2, a3);
-                        a0 &= mk_lo; a1 &= mk_lo; a2 &= mk_hi; a3 &= mk_hi;
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt)
-                            mma_kv<FP8>(o[nt][dt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
-                    }
-                } else {
-                    // A 16-byte fp8 chunk holds 16 d values, so the b16 transpose moves (d 2g, d 2g+1) pairs:
-                    // a thread receives {tok 2t4: d 2g, d 2g+1 ; tok 2t4+1: d 2g, d 2g+1}.  PRMT regroups it to
-                    // {d 2g: tok pair ; d 2g+1: tok pair}; MMA row g <-> d = 16c + 2g, row g+8 <-> d = 16c + 2g + 1.
-                    // .trans matrices: 0 = tokens 0-7 / chunk c, 1 = tokens 8-15 / c, 2 = tokens 0-7 / c+1, 3 = tokens 8-15 / c+1
-                    const int row = row_base + (mi & 1) * 8 + ri;
-#pragma unroll
-                    for (int dt2 = 0; dt2 < 4; ++dt2) {
-                        const int chunk = 2 * dt2 + (mi >> 1);
-                        const uint32_t addr = vbase + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
-                        uint32_t r0, r1, r2, r3;
-                        b2::ldmatrix_x4_trans(addr, r0, r1, r2, r3);
-                        r0 = __byte_perm(r0, 0, 0x3120); r1 = __byte_perm(r1, 0, 0x3120);
-                        r2 = __byte_perm(r2, 0, 0x3120); r3 = __byte_perm(r3, 0, 0x3120);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt) {
-                            mma_kv<FP8>(o[nt][2 * dt2], e4m3x2_to_f16x2(r0) & mk_lo, e4m3x2_to_f16x2(r0 >> 16) & mk_lo,
-                                        e4m3x2_to_f16x2(r1) & mk_hi, e4m3x2_to_f16x2(r1 >> 16) & mk_hi,
-                                        pb[nt][0], pb[nt][1]);
-                            mma_kv<FP8>(o[nt][2 * dt2 + 1], e4m3x2_to_f16x2(r2) & mk_lo, e4m3x2_to_f16x2(r2 >> 16) & mk_lo,
-                                        e4m3x2_to_f16x2(r3) & mk_hi, e4m3x2_to_f16x2(r3 >> 16) & mk_hi,
-                                        pb[nt][0], pb[nt][1]);
-                        }
-                    }
-                }
-            }
-            __syncwarp();
-            if (lane == 0) b2::mbar_arrive(bar_empty + s * 8);   // stage may be overwritten
-        }
-
-        // lane-local row sums -> full sums over the slab's 16 token rows (lanes differing in g)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                float l = l_run[nt][j];
-                l += __shfl_xor_sync(0xffffffffu, l, 4);
-                l += __shfl_xor_sync(0xffffffffu, l, 8);
-                l += __shfl_xor_sync(0xffffffffu, l, 16);
-                l_run[nt][j] = l;
-            }
-
-        // Every stage this CTA armed has been consumed by all four warps once they pass this
-        // named barrier, so the ring can be reused as merge scratch.
-        asm volatile("bar.sync 1, %0;" ::"n"(NCW * 32));
-
-        // ---- publish (m, l, O^T) of this warp: sc_o[warp][d][head], sc_m/sc_l[warp][head]
-        float* sc = reinterpret_cast<float*>(smem_raw + (base - b2::smem_u32(smem_raw)));
-        float* sc_o = sc + warp * (D * C::HEADS);
-        float* sc_m = sc + NCW * (D * C::HEADS) + warp * C::HEADS;
-        float* sc_l = sc_m + NCW * C::HEADS;
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-#pragma unroll
-            for (int dt = 0; dt < 8; ++dt) {
-                // bf16: MMA row r <-> d = 16dt + r.  fp8: row g <-> d = 16dt + 2g, row g+8 <-> d = 16dt + 2g + 1.
-                const int d_lo = FP8 ? 16 * dt + 2 * g : 16 * dt + g;
-                const int d_hi = FP8 ? d_lo + 1 : d_lo + 8;
-                *reinterpret_cast<float2*>(sc_o + d_lo * C::HEADS + nt * 8 + 2 * t4) =
-                    make_float2(o[nt][dt][0], o[nt][dt][1]);
-                *reinterpret_cast<float2*>(sc_o + d_hi * C::HEADS + nt * 8 + 2 * t4) =
-                    make_float2(o[nt][dt][2], o[nt][dt][3]);
-            }
-            if (g == 0) {
-                sc_m[nt * 8 + 2 * t4] = m_run[nt][0];
-                sc_m[nt * 8 + 2 * t4 + 1] = m_run[nt][1];
-                sc_l[nt * 8 + 2 * t4] = l_run[nt][0];
-                sc_l[nt * 8 + 2 * t4 + 1] = l_run[nt][1];
-            }
-        }
-        asm volatile("bar.sync 1, %0;" ::"n"(NCW * 32));
-
-        // ---- merge the four slabs; thread -> (head h, 8*NT... d values), bank-conflict-free reads
-        float vs = 1.f;
-        if (FP8) vs = *p.v_scale;
-        const float* sc_all = sc;
-        const float* sm_all = sc + NCW * (D * C::HEADS);
-        const float* sl_all = sm_all + NCW * C::HEADS;
-        constexpr int DG = (NCW * 32) / C::HEADS;        // d-groups covered per pass
-        const int h = tid % C::HEADS;
-        const int dg = tid / C::HEADS;
-        if (h < nheads) {
-            float mw[NCW], M = -INFINITY;
-#pragma unroll
-            for (int w = 0; w < NCW; ++w) {
-                mw[w] = sm_all[w * C::HEADS + h];
-                M = fmaxf(M, mw[w]);
-            }
-            float wgt[NCW], L = 0.f;
-#pragma unroll
-            for (int w = 0; w < NCW; ++w) {
-                wgt[w] = (mw[w] == -INFINITY) ? 0.f : b2::fast_exp2((mw[w] - M) * sl2);
-                L = fmaf(wgt[w], sl_all[w * C::HEADS + h], L);
-            }
-            const float inv = vs / L;   // L > 0: the split holds at least one valid token
-            const int hq = head0 + h;
-            if (p.num_splits == 1) {
-                __nv_bfloat16* orow = p.out + b * p.out_stride + (int64_t)hq * D;
-                for (int d = dg; d < D; d += DG) {
-                    float acc = 0.f;
-#pragma unroll
-                    for (int w = 0; w < NCW; ++w) acc = fmaf(wgt[w], sc_all[w * (D * C::HEADS) + d * C::HEADS + h], acc);
-                    orow[d] = __float2bfloat16(acc * inv);
-                }
-            } else {
-                const int64_t pi = ((int64_t)b * p.Hq + hq) * p.num_splits + split;
-                float* orow = p.ws_o + pi * D;
-                for (int d = dg; d < D; d += DG) {
-                    float acc = 0.f;
-#pragma unroll
-                    for (int w = 0; w < NCW; ++w) acc = fmaf(wgt[w], sc_all[w * (D * C::HEADS) + d * C::HEADS + h], acc);
-                    orow[d] = acc * inv;
-                }
-                if (dg == 0) p.ws_lse[pi] = fmaf(M, sl2, log2f(L));
             }
         }
     }
@@ -476,6 +569,279 @@ merge_splits_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ w
         den += w;
     }
     *o = __float2bfloat16(num / den);
+}
+
+// =============================================================================================
+// schedule B (default): persistent CTAs over an equal partition of the flattened block space
+// =============================================================================================
+// Unit u of the flattened space: sequences in order, within a sequence the IPB = Hkv*HG items in order,
+// within an item its ceil(seq_len/BS) blocks in order.  CTA c of NC owns [c*U/NC, (c+1)*U/NC).
+struct Cursor {
+    int b;        // sequence
+    int j;        // item within the sequence (kvh*HG + hg)
+    int blk;      // block within the item
+};
+
+// Block-cooperative: total unit count U and, for `n_targets` unit indices given by target(U), their cursors.
+// Every thread returns the same values.  `part` is NT_+2 words of shared memory.
+template <int BS, int NT_>
+__device__ __forceinline__ uint32_t count_units(const int32_t* __restrict__ seq_lens, int B, int IPB,
+                                                uint32_t* part, uint32_t& my_local, uint32_t& my_pre, int& chunk) {
+    const int tid = threadIdx.x;
+    chunk = (B + NT_ - 1) / NT_;
+    uint32_t local = 0;
+    const int b0 = tid * chunk, b1 = min(B, b0 + chunk);
+    for (int b = b0; b < b1; ++b) local += (uint32_t)((seq_lens[b] + BS - 1) / BS) * IPB;
+    part[tid] = local;
+    __syncthreads();
+    if (tid < 32) {   // exclusive scan of NT_ partials, ceil(NT_/32) per lane
+        constexpr int PER = (NT_ + 31) / 32;
+        uint32_t v[PER], s = 0;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            const int idx = tid * PER + i;
+            v[i] = idx < NT_ ? part[idx] : 0;
+            s += v[i];
+        }
+        uint32_t incl = s;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (tid >= off) incl += t;
+        }
+        uint32_t run = incl - s;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            const int idx = tid * PER + i;
+            if (idx < NT_) part[idx] = run;
+            run += v[i];
+        }
+        if (tid == 31) part[NT_] = incl;
+    }
+    __syncthreads();
+    my_local = local;
+    my_pre = part[tid];
+    return part[NT_];
+}
+
+// The thread whose chunk contains unit u walks it and publishes the cursor through `res` (3 ints).
+template <int BS>
+__device__ __forceinline__ void locate_unit(uint32_t u, const int32_t* __restrict__ seq_lens, int B, int IPB,
+                                            uint32_t my_local, uint32_t my_pre, int chunk, int* res) {
+    if (u >= my_pre && u < my_pre + my_local) {
+        uint32_t acc = my_pre;
+        const int b0 = threadIdx.x * chunk, b1 = min(B, b0 + chunk);
+        for (int b = b0; b < b1; ++b) {
+            const uint32_t nb = (uint32_t)((seq_lens[b] + BS - 1) / BS);
+            const uint32_t span = nb * IPB;
+            if (u < acc + span) {
+                const uint32_t r = u - acc;
+                res[0] = b;
+                res[1] = (int)(r / nb);
+                res[2] = (int)(r % nb);
+                break;
+            }
+            acc += span;
+        }
+    }
+}
+
+__device__ __forceinline__ uint32_t range_begin(uint32_t c, uint32_t U, uint32_t NC) {
+    return (uint32_t)(((uint64_t)c * U) / NC);
+}
+__device__ __forceinline__ uint32_t effective_ctas(uint32_t U, uint32_t grid, int min_units) {
+    const uint32_t want = (U + min_units - 1) / min_units;
+    return want < grid ? (want ? want : 1u) : grid;
+}
+
+template <int BS, bool FP8, int NT, int NSTAGE>
+__global__ void __launch_bounds__(NTHREADS, 2)
+paged_decode_persistent_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                               const DecodeParams p) {
+    using C = Cfg<BS, FP8, NT, NSTAGE>;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // the unit search borrows the (not yet used) merge scratch: no static shared memory, so the
+    // dynamic region keeps its 1024-byte alignment without padding
+    uint32_t* s_part = reinterpret_cast<uint32_t*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
+    int* s_cur = reinterpret_cast<int*>(s_part + NTHREADS + 2);
+    static_assert((NTHREADS + 2 + 3) * 4 <= C::SCRATCH_BYTES, "unit search scratch");
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int c = blockIdx.x;
+    const int IPB = p.Hkv * p.HG;
+    // let the boundary-merge kernel (programmatic dependent launch) get resident and run its own
+    // unit search while this grid streams; it blocks in griddepcontrol.wait until we are done
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    // rows of empty sequences are defined here (no unit ever visits them)
+    for (int b = c; b < p.B; b += gridDim.x)
+        if (p.seq_lens[b] <= 0)
+            for (int i = tid; i < p.Hq * D; i += NTHREADS) p.out[b * p.out_stride + i] = __float2bfloat16(0.f);
+
+    uint32_t my_local, my_pre;
+    int chunk;
+    const uint32_t U = count_units<BS, NTHREADS>(p.seq_lens, p.B, IPB, s_part, my_local, my_pre, chunk);
+    const uint32_t NC = effective_ctas(U, gridDim.x, MIN_TOK_PER_CTA / BS);
+    if (U == 0 || (uint32_t)c >= NC) return;
+    const uint32_t u0 = range_begin(c, U, NC), u1 = range_begin(c + 1, U, NC);
+    if (u0 == u1) return;
+    locate_unit<BS>(u0, p.seq_lens, p.B, IPB, my_local, my_pre, chunk, s_cur);
+
+    const uint32_t ring = b2::smem_u32(smem_raw);
+    if (ring & 1023u) __trap();
+    const uint32_t bar_full = ring + C::RING_BYTES;
+    const uint32_t bar_empty = bar_full + NSTAGE * 8;
+    float* scratch = reinterpret_cast<float*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
+    init_pipeline(bar_full, bar_empty, NSTAGE, tid);   // also publishes s_cur
+
+    Cursor cur{s_cur[0], s_cur[1], s_cur[2]};
+    uint32_t remaining = u1 - u0;
+    uint32_t it = 0;
+
+    if (warp == NCW) {
+        // ================================ producer warp =====================================
+        if (lane == 0) {
+            b2::tma_prefetch_desc(&tmK);
+            b2::tma_prefetch_desc(&tmV);
+        }
+        const uint64_t pol = b2::policy_evict_first();
+        while (remaining) {
+            const int nb = (p.seq_lens[cur.b] + BS - 1) / BS;
+            if (nb == 0) { ++cur.b; cur.j = 0; cur.blk = 0; continue; }
+            const int take = min((uint32_t)(nb - cur.blk), remaining);
+            produce_segment<C, NSTAGE>(&tmK, &tmV, p.block_tables + (int64_t)cur.b * p.max_nb + cur.blk, take,
+                                       cur.j / p.HG, ring, bar_full, bar_empty, it, lane, pol);
+            remaining -= take;
+            cur.blk += take;
+            if (cur.blk == nb) { cur.blk = 0; if (++cur.j == IPB) { cur.j = 0; ++cur.b; } }
+        }
+    } else {
+        // ================================ consumer warps ====================================
+        float sl2 = p.scale_log2, vs = 1.f;
+        if (FP8) {
+            sl2 *= *p.k_scale;
+            vs = *p.v_scale;
+        }
+        WarpAcc<NT> acc;
+        bool first = true;
+        while (remaining) {
+            const int seq_len = p.seq_lens[cur.b];
+            const int nb = (seq_len + BS - 1) / BS;
+            if (nb == 0) { ++cur.b; cur.j = 0; cur.blk = 0; continue; }
+            const int take = min((uint32_t)(nb - cur.blk), remaining);
+            const int kvh = cur.j / p.HG, hg = cur.j - kvh * p.HG;
+            const int head0 = kvh * p.G + hg * C::HEADS;
+            const int nheads = min(C::HEADS, p.G - hg * C::HEADS);
+            const int n_tok = min(seq_len, (cur.blk + take) * BS) - cur.blk * BS;
+
+            uint32_t qf[NT][8][2];
+            load_q_frags<FP8, NT>(qf, p.q + cur.b * p.q_stride + (int64_t)head0 * D, nheads, lane);
+            acc.reset();
+            consume_segment<C, FP8, NT, NSTAGE>(acc, qf, n_tok, ring, bar_full, bar_empty, it, sl2, warp, lane);
+            merge_warps<NT>(acc, scratch, C::SLOT_FLOATS, sl2, warp, lane);
+            if (warp == 0) {
+                const bool whole = cur.blk == 0 && take == nb;
+                if (whole) {
+                    write_result<FP8, NT>(acc, nheads, vs, sl2, p.out + cur.b * p.out_stride + (int64_t)head0 * D,
+                                          nullptr, nullptr, lane);
+                } else {
+                    // a partial segment is either the first or the last segment of this CTA
+                    const int64_t slot = (int64_t)c * 2 + (first ? 0 : 1);
+                    write_result<FP8, NT>(acc, nheads, vs, sl2, nullptr, p.ws_o + slot * (C::HEADS * D),
+                                          p.ws_lse + slot * C::HEADS, lane);
+                }
+            }
+            first = false;
+            remaining -= take;
+            cur.blk += take;
+            if (cur.blk == nb) { cur.blk = 0; if (++cur.j == IPB) { cur.j = 0; ++cur.b; } }
+        }
+    }
+}
+
+// Items that straddle a CTA boundary: block c (one per boundary c | c+1) merges the item that crosses its
+// boundary if that item did not already cross the previous one (then an earlier block owns it).
+template <int BS, int HEADS>
+__global__ void __launch_bounds__(128)
+merge_boundary_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ ws_o,
+                      const float* __restrict__ ws_lse, const int32_t* __restrict__ seq_lens, int B, int Hkv, int G,
+                      int HG, int64_t out_stride, uint32_t grid_main) {
+    __shared__ uint32_t s_part[128 + 2];
+    __shared__ int s_cur[3];
+    const int tid = threadIdx.x;
+    const uint32_t c = blockIdx.x;
+    const int IPB = Hkv * HG;
+    uint32_t my_local, my_pre;
+    int chunk;
+    const uint32_t U = count_units<BS, 128>(seq_lens, B, IPB, s_part, my_local, my_pre, chunk);
+    const uint32_t NC = effective_ctas(U, grid_main, MIN_TOK_PER_CTA / BS);
+    if (U == 0 || c + 1 >= NC) return;
+    const uint32_t ub = range_begin(c + 1, U, NC);       // the boundary between CTA c and c+1
+    if (ub == 0 || ub >= U) return;
+    locate_unit<BS>(ub, seq_lens, B, IPB, my_local, my_pre, chunk, s_cur);
+    __syncthreads();
+    const int b = s_cur[0], j = s_cur[1], blk = s_cur[2];
+    if (blk == 0) return;                                // the boundary falls between two items
+    const int nb = (seq_lens[b] + BS - 1) / BS;
+    const uint32_t s_i = ub - blk, e_i = s_i + nb;       // the item's unit range
+    if (s_i < range_begin(c, U, NC)) return;             // it also crossed c-1 | c: block c_first owns it
+    // wait for the decode kernel's partials (programmatic dependent launch)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const uint32_t c_last = (uint32_t)((((uint64_t)e_i * NC) - 1) / U);
+    const int kvh = j / HG, hg = j - kvh * HG;
+    const int head0 = kvh * G + hg * HEADS;
+    const int nheads = min(HEADS, G - hg * HEADS);
+    // thread -> (head tid/16 [+8], 8 consecutive d); every load of a pass is independent, so the whole
+    // merge costs about one L2 round trip.  Partials are combined online, MAXC CTAs at a time.
+    constexpr int MAXC = 4;
+    const int dc = (tid & 15) * 8;
+    for (int h = tid >> 4; h < nheads; h += 8) {
+        float m_run = -INFINITY, den = 0.f, num[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) num[i] = 0.f;
+        for (uint32_t cb = c; cb <= c_last; cb += MAXC) {
+            float lse[MAXC];
+            float4 o0[MAXC], o1[MAXC];
+#pragma unroll
+            for (int i = 0; i < MAXC; ++i) {
+                const uint32_t cc = cb + i;
+                lse[i] = -INFINITY;
+                o0[i] = o1[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (cc <= c_last) {
+                    const int64_t slot = (int64_t)cc * 2 + (range_begin(cc, U, NC) >= s_i ? 0 : 1);
+                    lse[i] = ws_lse[slot * HEADS + h];
+                    const float4* po = reinterpret_cast<const float4*>(ws_o + (slot * HEADS + h) * D + dc);
+                    o0[i] = po[0];
+                    o1[i] = po[1];
+                }
+            }
+            float mx = m_run;
+#pragma unroll
+            for (int i = 0; i < MAXC; ++i) mx = fmaxf(mx, lse[i]);
+            if (mx == -INFINITY) continue;
+            const float a = m_run == -INFINITY ? 0.f : exp2f(m_run - mx);
+            den *= a;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) num[i] *= a;
+#pragma unroll
+            for (int i = 0; i < MAXC; ++i) {
+                const float w = lse[i] == -INFINITY ? 0.f : exp2f(lse[i] - mx);
+                den += w;
+                num[0] = fmaf(w, o0[i].x, num[0]); num[1] = fmaf(w, o0[i].y, num[1]);
+                num[2] = fmaf(w, o0[i].z, num[2]); num[3] = fmaf(w, o0[i].w, num[3]);
+                num[4] = fmaf(w, o1[i].x, num[4]); num[5] = fmaf(w, o1[i].y, num[5]);
+                num[6] = fmaf(w, o1[i].z, num[6]); num[7] = fmaf(w, o1[i].w, num[7]);
+            }
+            m_run = mx;
+        }
+        const float inv = den > 0.f ? 1.f / den : 0.f;
+        uint4 pk;
+        pk.x = b2::pack_bf16x2(num[0] * inv, num[1] * inv);
+        pk.y = b2::pack_bf16x2(num[2] * inv, num[3] * inv);
+        pk.z = b2::pack_bf16x2(num[4] * inv, num[5] * inv);
+        pk.w = b2::pack_bf16x2(num[6] * inv, num[7] * inv);
+        *reinterpret_cast<uint4*>(out + b * out_stride + (int64_t)(head0 + h) * D + dc) = pk;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -516,88 +882,115 @@ int make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t nu
     return B2_OK;
 }
 
-constexpr int kNumSMs = 148;
+int persistent_grid() {
+    static int n = []() {
+        int dev = 0, sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        return 2 * sms;   // two resident CTAs per SM (shared-memory bound)
+    }();
+    return n;
+}
 
 struct Plan {
     int nt;            // n-tiles of 8 q heads per CTA
     int hg;            // head groups per kv head
-    int num_splits;
+    int num_splits;    // 0 = persistent schedule
     int split_tokens;
 };
 
-int heads_per_cta(int G) { return G <= 8 ? 8 : 16; }
-
-// Split heuristic: enough CTAs for >= 8 waves over 148 SMs x 2 resident CTAs so the tail wave is
-// small, but never splits shorter than 256 tokens (merge traffic stays < 2 % of KV bytes).
-int auto_splits(int B, int Hkv, int G, int bs, int max_nb) {
-    const int hpc = heads_per_cta(G);
-    const int64_t items = (int64_t)B * Hkv * ((G + hpc - 1) / hpc);
-    const int64_t max_ctx = (int64_t)max_nb * bs;
-    const int64_t target = 8LL * kNumSMs * 2;
-    int64_t want = (target + items - 1) / items;
-    int64_t cap = max_ctx / 256;
-    if (cap < 1) cap = 1;
-    if (want > cap) want = cap;
-    if (want < 1) want = 1;
-    if (want > 64) want = 64;
-    return (int)want;
-}
-
-int make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_splits) {
+void make_plan(Plan* pl, int G, int bs, int max_nb, int num_splits) {
     pl->nt = G <= 8 ? 1 : 2;
     const int hpc = 8 * pl->nt;
     pl->hg = (G + hpc - 1) / hpc;
-    if (num_splits <= 0) num_splits = auto_splits(B, Hkv, G, bs, max_nb);
+    pl->num_splits = 0;
+    pl->split_tokens = 0;
+    if (num_splits <= 0) return;
     const int64_t max_ctx = (int64_t)max_nb * bs;
     int64_t st = (max_ctx + num_splits - 1) / num_splits;
     st = ((st + TOK - 1) / TOK) * TOK;   // whole stages, hence whole blocks
     pl->split_tokens = (int)st;
     pl->num_splits = (int)((max_ctx + st - 1) / st);
     if (pl->num_splits < 1) pl->num_splits = 1;
-    return B2_OK;
+}
+
+size_t plan_workspace(const Plan& pl, int B, int Hq) {
+    if (pl.num_splits == 0) return (size_t)persistent_grid() * 2 * (8 * pl.nt) * (D + 1) * sizeof(float);
+    if (pl.num_splits == 1) return 0;
+    return (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
 }
 
 template <int BS, bool FP8, int NT>
-int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, int B, cudaStream_t st) {
-    constexpr int NSTAGE = FP8 ? 4 : 3;
-    constexpr int MINB = 2;
+int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, const Plan& pl,
+                  cudaStream_t st) {
+    constexpr int NSTAGE = FP8 ? 6 : 3;
     using C = Cfg<BS, FP8, NT, NSTAGE>;
-    auto kern = paged_decode_kernel<BS, FP8, NT, NSTAGE, MINB>;
-    static bool attr_set = false;   // per instantiation; idempotent, so a race is harmless
-    if (!attr_set) {
-        B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-        attr_set = true;
+    if (pl.num_splits == 0) {
+        auto kern = paged_decode_persistent_kernel<BS, FP8, NT, NSTAGE>;
+        static bool attr_set = false;   // per instantiation; idempotent, so a race is harmless
+        if (!attr_set) {
+            B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+            attr_set = true;
+        }
+        const int grid = persistent_grid();
+        kern<<<grid, NTHREADS, C::SMEM_BYTES, st>>>(tmK, tmV, p);
+        B2_CUDA_OK(cudaGetLastError());
+        // boundary merge, launched early (PDL): its unit search overlaps the decode kernel's tail
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(128);
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        B2_CUDA_OK(cudaLaunchKernelEx(&cfg, merge_boundary_kernel<BS, 8 * NT>, p.out, (const float*)p.ws_o,
+                                      (const float*)p.ws_lse, p.seq_lens, p.B, p.Hkv, p.G, p.HG, p.out_stride,
+                                      (uint32_t)grid));
+        return B2_OK;
     }
-    dim3 grid(p.num_splits, p.Hkv * p.HG, B);
+    auto kern = paged_decode_split_kernel<BS, FP8, NT, NSTAGE>;
+    static bool attr_set2 = false;
+    if (!attr_set2) {
+        B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+        attr_set2 = true;
+    }
+    dim3 grid(p.num_splits, p.Hkv * p.HG, p.B);
     kern<<<grid, NTHREADS, C::SMEM_BYTES, st>>>(tmK, tmV, p);
     B2_CUDA_OK(cudaGetLastError());
+    if (pl.num_splits > 1) {
+        merge_splits_kernel<<<dim3(p.Hq, p.B), D, 0, st>>>(p.out, p.ws_o, p.ws_lse, p.seq_lens, p.Hq, p.num_splits,
+                                                           p.split_tokens, p.out_stride);
+        B2_CUDA_OK(cudaGetLastError());
+    }
     return B2_OK;
 }
 
 template <int BS>
-int dispatch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, int B, int nt,
-                    bool fp8, cudaStream_t st) {
-    if (!fp8) return nt == 1 ? launch_decode<BS, false, 1>(tmK, tmV, p, B, st) : launch_decode<BS, false, 2>(tmK, tmV, p, B, st);
-    return nt == 1 ? launch_decode<BS, true, 1>(tmK, tmV, p, B, st) : launch_decode<BS, true, 2>(tmK, tmV, p, B, st);
+int dispatch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, const Plan& pl, bool fp8,
+                    cudaStream_t st) {
+    if (!fp8) return pl.nt == 1 ? launch_decode<BS, false, 1>(tmK, tmV, p, pl, st) : launch_decode<BS, false, 2>(tmK, tmV, p, pl, st);
+    return pl.nt == 1 ? launch_decode<BS, true, 1>(tmK, tmV, p, pl, st) : launch_decode<BS, true, 2>(tmK, tmV, p, pl, st);
+}
+
+bool shape_ok(int B, int Hq, int Hkv, int d, int bs, int max_nb) {
+    return B > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && bs > 0 && max_nb > 0 && d == D;
 }
 
 }  // namespace
 
 extern "C" int b2_paged_decode_auto_splits(int B, int Hq, int Hkv, int d, int bs, int max_nb, int kv_dtype) {
-    (void)d; (void)kv_dtype;
-    if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv != 0 || bs <= 0 || max_nb <= 0) return B2_EINVAL;
-    Plan pl;
-    make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, 0);
-    return pl.num_splits;
+    (void)kv_dtype;
+    if (!shape_ok(B, Hq, Hkv, d, bs, max_nb)) return B2_EINVAL;
+    return 0;   // num_splits = 0 selects the persistent schedule: no fixed split count
 }
 
 extern "C" size_t b2_paged_decode_workspace_bytes(int B, int Hq, int Hkv, int d, int bs, int max_nb,
                                                   int num_splits) {
-    if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv != 0 || bs <= 0 || max_nb <= 0 || d != D) return 0;
+    if (!shape_ok(B, Hq, Hkv, d, bs, max_nb)) return 0;
     Plan pl;
-    make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits);
-    if (pl.num_splits == 1) return 0;
-    return (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
+    make_plan(&pl, Hq / Hkv, bs, max_nb, num_splits);
+    return plan_workspace(pl, B, Hq);
 }
 
 extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, const void* v_cache,
@@ -623,12 +1016,15 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
     B2_REQUIRE(cache_block_stride % 16 == 0 && cache_head_stride % 16 == 0 && cache_head_stride >= (int64_t)bs * D,
                B2_EINVAL, "paged_decode: cache strides must keep 16-byte alignment");
     B2_REQUIRE(scale > 0.f, B2_EINVAL, "paged_decode: scale must be positive");
+    B2_REQUIRE(num_splits >= 0, B2_EINVAL, "paged_decode: num_splits must be >= 0");
     if (kv_dtype == B2_KV_FP8_E4M3) B2_REQUIRE(k_scale && v_scale, B2_EINVAL, "paged_decode: fp8 needs k_scale/v_scale");
     B2_REQUIRE((int64_t)Hkv * ((Hq / Hkv + 15) / 16) <= 65535 && B <= 65535, B2_EUNSUPPORTED, "paged_decode: grid too large");
+    B2_REQUIRE((int64_t)B * max_nb * Hkv * ((Hq / Hkv + 7) / 8) < (1LL << 31), B2_EUNSUPPORTED,
+               "paged_decode: more than 2^31 block units");
 
     const int G = Hq / Hkv;
     Plan pl;
-    make_plan(&pl, B, Hkv, G, bs, max_nb, num_splits);
+    make_plan(&pl, G, bs, max_nb, num_splits);
 
     DecodeParams p;
     p.out = static_cast<__nv_bfloat16*>(out);
@@ -637,17 +1033,17 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
     p.seq_lens = seq_lens;
     p.k_scale = k_scale;
     p.v_scale = v_scale;
-    p.Hq = Hq; p.Hkv = Hkv; p.G = G; p.HG = pl.hg; p.max_nb = max_nb;
+    p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.G = G; p.HG = pl.hg; p.max_nb = max_nb;
     p.num_splits = pl.num_splits; p.split_tokens = pl.split_tokens;
     p.q_stride = q_stride; p.out_stride = out_stride;
     p.scale_log2 = scale * LOG2E;
     p.ws_o = nullptr; p.ws_lse = nullptr;
-    if (pl.num_splits > 1) {
-        const size_t need = (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
+    const size_t need = plan_workspace(pl, B, Hq);
+    if (need) {
         B2_REQUIRE(workspace && workspace_bytes >= need && b2_aligned16(workspace), B2_ENOMEM,
                    "paged_decode: workspace %zu bytes < required %zu", workspace_bytes, need);
         p.ws_o = static_cast<float*>(workspace);
-        p.ws_lse = p.ws_o + (size_t)B * Hq * pl.num_splits * D;
+        p.ws_lse = p.ws_o + need / sizeof(float) / (D + 1) * D;
     }
 
     CUtensorMap tmK, tmV;
@@ -658,15 +1054,7 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool fp8 = kv_dtype == B2_KV_FP8_E4M3;
-    if (bs == 8) rc = dispatch_decode<8>(tmK, tmV, p, B, pl.nt, fp8, st);
-    else if (bs == 16) rc = dispatch_decode<16>(tmK, tmV, p, B, pl.nt, fp8, st);
-    else rc = dispatch_decode<32>(tmK, tmV, p, B, pl.nt, fp8, st);
-    if (rc != B2_OK) return rc;
-
-    if (pl.num_splits > 1) {
-        merge_splits_kernel<<<dim3(Hq, B), D, 0, st>>>(p.out, p.ws_o, p.ws_lse, seq_lens, Hq, pl.num_splits,
-                                                       pl.split_tokens, out_stride);
-        B2_CUDA_OK(cudaGetLastError());
-    }
-    return B2_OK;
+    if (bs == 8) return dispatch_decode<8>(tmK, tmV, p, pl, fp8, st);
+    if (bs == 16) return dispatch_decode<16>(tmK, tmV, p, pl, fp8, st);
+    return dispatch_decode<32>(tmK, tmV, p, pl, fp8, st);
 }
