@@ -98,6 +98,13 @@ B2_API size_t b2_paged_decode_workspace_bytes(int B, int Hq, int Hkv, int d, int
 /* the split count b2_paged_decode will actually use for num_splits = 0 */
 B2_API int b2_paged_decode_auto_splits(int B, int Hq, int Hkv, int d, int bs, int max_nb, int kv_dtype);
 
+/* Host-side schedule choice for callers that hold seq_lens on the host (the scheduler always does; it is the
+ * role `max_seq_len` plays for vLLM's paged_attention_v1/v2 choice).  Returns the num_splits to pass to
+ * b2_paged_decode: 1 when the single-pass grid (one CTA per (sequence, kv head)) keeps the machine balanced
+ * for these lengths, 0 (dynamic persistent schedule) otherwise; negative on bad arguments.  Pure host code. */
+B2_API int b2_paged_decode_plan_splits(const int32_t* seq_lens_host, int B, int Hq, int Hkv, int d, int bs,
+                                int kv_dtype);
+
 B2_API int b2_paged_decode(void* out, const void* q,
                     const void* k_cache, const void* v_cache,
                     const int32_t* block_tables, const int32_t* seq_lens,

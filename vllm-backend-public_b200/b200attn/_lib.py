@@ -36,6 +36,7 @@ SIGNATURES = {
     "b2_reshape_and_cache": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i32, vp, vp, vp]),
     "b2_paged_decode_workspace_bytes": (sz, [i32, i32, i32, i32, i32, i32, i32]),
     "b2_paged_decode_auto_splits": (i32, [i32, i32, i32, i32, i32, i32, i32]),
+    "b2_paged_decode_plan_splits": (i32, [vp, i32, i32, i32, i32, i32, i32]),
     "b2_paged_decode": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
                               f32, i32, vp, vp, vp, sz, i32, vp]),
     "b2_paged_decode_simt": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64,

@@ -99,6 +99,18 @@ def decode_auto_splits(B: int, Hq: int, Hkv: int, d: int, bs: int, max_nb: int, 
     return int(_lib.load().b2_paged_decode_auto_splits(B, Hq, Hkv, d, bs, max_nb, kv_dtype))
 
 
+def plan_num_splits(seq_lens_host: torch.Tensor, Hq: int, Hkv: int, d: int = 128, bs: int = 16,
+                    kv_dtype: int = KV_BF16) -> int:
+    """Schedule choice from the scheduler's HOST copy of seq_lens (int32 CPU tensor): 1 = single-pass grid,
+    0 = dynamic persistent schedule.  Pure host arithmetic (b2_paged_decode_plan_splits)."""
+    if seq_lens_host.is_cuda or seq_lens_host.dtype != torch.int32 or not seq_lens_host.is_contiguous():
+        raise ValueError("seq_lens_host must be a contiguous int32 CPU tensor")
+    rc = _lib.load().b2_paged_decode_plan_splits(seq_lens_host.data_ptr(), seq_lens_host.numel(), Hq, Hkv, d, bs, kv_dtype)
+    if rc < 0:
+        _lib.check(rc)
+    return int(rc)
+
+
 def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_tables: torch.Tensor,
                  seq_lens: torch.Tensor, scale: Optional[float] = None, k_scale: Optional[torch.Tensor] = None,
                  v_scale: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,

@@ -31,6 +31,10 @@
 //     (split, kv head, sequence)) built from the same producer/consumer code.
 #include "b2_common.cuh"
 
+#include <stdlib.h>
+#include <algorithm>
+#include <vector>
+
 namespace {
 
 constexpr int D = 128;        // head_dim (Llama-3 geometry)
@@ -39,6 +43,21 @@ constexpr int TOK = NCW * 16; // tokens per pipeline stage
 constexpr int NTHREADS = (NCW + 1) * 32;
 constexpr int MIN_TOK_PER_CTA = 128;   // persistent schedule: do not cut work finer than this
 constexpr float LOG2E = 1.4426950408889634f;
+
+// Optional per-CTA timeline (make trace -> lib/libb200attn_trace.so; scripts/trace_schedule.py reads it).
+#ifdef B2_TRACE
+__device__ unsigned long long g_trace[2048 * 8];
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define B2_TRACE_AT(cta, k) do { if ((threadIdx.x & 31) == 0 && (cta) < 2048) g_trace[(cta) * 8 + (k)] = gtime(); } while (0)
+#define B2_TRACE_VAL(cta, k, v) do { if ((threadIdx.x & 31) == 0 && (cta) < 2048) g_trace[(cta) * 8 + (k)] = (v); } while (0)
+#else
+#define B2_TRACE_AT(cta, k) do { } while (0)
+#define B2_TRACE_VAL(cta, k, v) do { } while (0)
+#endif
 
 struct DecodeParams {
     __nv_bfloat16* out;
@@ -50,6 +69,8 @@ struct DecodeParams {
     const float* k_scale;
     const float* v_scale;
     int B, Hq, Hkv, G, HG, max_nb, num_splits, split_tokens;
+    int chunk_tokens, static_pct;   // dynamic schedule: claim granularity, share of chunks dealt statically
+    uint32_t* counter;              // dynamic schedule: claim counter (workspace header)
     int64_t q_stride, out_stride;
     float scale_log2;  // softmax scale * log2(e)
 };
@@ -58,17 +79,26 @@ template <int BS, bool FP8, int NT, int NSTAGE>
 struct Cfg {
     static constexpr int ESZ = FP8 ? 1 : 2;
     static constexpr int ROWB = D * ESZ;           // bytes per token row
-    static constexpr int NHALF = ROWB / 128;       // 128-byte swizzle spans per row
     static constexpr int TILE_BYTES = TOK * ROWB;  // one K (or V) stage tile
     static constexpr int STAGE_BYTES = 2 * TILE_BYTES;
     static constexpr int BLK_PER_STAGE = TOK / BS;
-    static constexpr int BOX_BYTES = BS * 128;     // one TMA box
+    static constexpr int BOX_BYTES = BS * ROWB;    // one TMA box = one contiguous (block, head) tile: 4 KiB bf16 / 2 KiB fp8
     static constexpr int HEADS = 8 * NT;           // q heads served per CTA
     static constexpr int RING_BYTES = NSTAGE * STAGE_BYTES;
     static constexpr int BAR_BYTES = 2 * NSTAGE * 8 + 16;
     static constexpr int SLOT_FLOATS = 32 * NT * 32 + 4 * NT * 4;   // O^T fragments + (m, l) of one warp
     static constexpr int SCRATCH_BYTES = 2 * SLOT_FLOATS * 4;
     static constexpr int SMEM_BYTES = RING_BYTES + BAR_BYTES + SCRATCH_BYTES;
+    // dynamic schedule: per-stage descriptors + the chunk prefix over (groups of) sequences
+    static constexpr int META_BYTES = NSTAGE * 16;
+    static constexpr int PMAX = NT == 1 ? 512 : 128;
+    static constexpr int PRE_BYTES = (PMAX + 1 + 3) / 4 * 16;
+    // dynamic schedule, NT == 1: the run's q rows travel with its first stage (bulk copy, same full-barrier),
+    // so a run boundary never waits on a global load.  One q buffer per stage slot.
+    static constexpr bool QSMEM = NT == 1;
+    static constexpr int QROW_BYTES = D * 2;
+    static constexpr int QBUF_BYTES = QSMEM ? HEADS * QROW_BYTES : 0;
+    static constexpr int DYN_SMEM_BYTES = SMEM_BYTES + META_BYTES + PRE_BYTES + NSTAGE * QBUF_BYTES;
     static_assert(TOK % BS == 0 && BS % 8 == 0, "block size must divide the stage and keep the swizzle phase");
     static_assert(RING_BYTES % 1024 == 0, "stages must stay 1024-byte aligned");
     static_assert(2 * (SMEM_BYTES + 1024) <= 233472, "two CTAs per SM must fit");
@@ -101,6 +131,28 @@ __device__ __forceinline__ void mma_kv(float (&c)[4], uint32_t a0, uint32_t a1, 
 }
 __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(NCW * 32) : "memory"); }
 
+// One KV block of one kv head -> stage slot j.  The (block, head) tile is bs x d contiguous in HBM and is fetched
+// by ONE box per tensor: bf16 rows are 256 B = two 128-byte swizzle lines, so the tile is viewed as
+// [row][half][64 elements] (5-D map) and lands as 2*bs consecutive lines; fp8 rows are one line (4-D map).
+template <class C, bool FP8>
+__device__ __forceinline__ void issue_block(const CUtensorMap* tmK, const CUtensorMap* tmV, uint32_t kdst, uint32_t vdst,
+                                            int j, uint32_t bar, int kvh, int blk, uint64_t pol) {
+    const uint32_t off = j * C::BOX_BYTES;
+    if (FP8) {
+        b2::tma_load_4d(kdst + off, tmK, bar, 0, 0, kvh, blk, pol);
+        b2::tma_load_4d(vdst + off, tmV, bar, 0, 0, kvh, blk, pol);
+    } else {
+        b2::tma_load_5d(kdst + off, tmK, bar, 0, 0, 0, kvh, blk, pol);
+        b2::tma_load_5d(vdst + off, tmV, bar, 0, 0, 0, kvh, blk, pol);
+    }
+}
+// shared-memory address of 16-byte chunk `chunk` (0..15 bf16, 0..7 fp8) of token row `row` inside a K or V stage tile
+template <bool FP8>
+__device__ __forceinline__ uint32_t tile_addr(uint32_t base, int row, int chunk) {
+    const int line = FP8 ? row : 2 * row + (chunk >> 3);           // 128-byte swizzle line
+    return base + line * 128 + (((chunk & 7) ^ (line & 7)) << 4);
+}
+
 // ---------------------------------------------------------------------------------------------
 // producer: stream the blocks [blk_begin, blk_begin + n_blk) of one (sequence, kv head) into the ring
 // ---------------------------------------------------------------------------------------------
@@ -120,20 +172,14 @@ __device__ __forceinline__ void produce_segment(const CUtensorMap* tmK, const CU
         const uint32_t kdst = ring + s * C::STAGE_BYTES;
         const uint32_t vdst = kdst + C::TILE_BYTES;
         if (lane == 0)
-            b2::mbar_arrive_expect_tx(bar_full + s * 8, nb_stage * 2 * C::NHALF * C::BOX_BYTES);
+            b2::mbar_arrive_expect_tx(bar_full + s * 8, nb_stage * 2 * C::BOX_BYTES);
 #pragma unroll
         for (int j = 0; j < C::BLK_PER_STAGE; ++j) {
             const int gi = st * C::BLK_PER_STAGE + j;
             const int src = gi & 31;
             const int blk = __shfl_sync(0xffffffffu, cur, src);
-            if (j < nb_stage && lane == 0) {
-#pragma unroll
-                for (int h = 0; h < C::NHALF; ++h) {
-                    const uint32_t off = h * (TOK * 128) + j * C::BOX_BYTES;
-                    b2::tma_load_4d(kdst + off, tmK, bar_full + s * 8, h * 64, 0, kvh, blk, pol);
-                    b2::tma_load_4d(vdst + off, tmV, bar_full + s * 8, h * 64, 0, kvh, blk, pol);
-                }
-            }
+            if (j < nb_stage && lane == 0)
+                issue_block<C, C::ESZ == 1>(tmK, tmV, kdst, vdst, j, bar_full + s * 8, kvh, blk, pol);
             if (src == 31) {  // warp-uniform: this batch of 32 entries is used up
                 cur = nxt;
                 nxt = (gi + 33 + lane < n_blk) ? bt[gi + 33 + lane] : 0;
@@ -246,6 +292,35 @@ __device__ __forceinline__ void load_q_frags(uint32_t (&qf)[NT][8][2], const __n
     }
 }
 
+// same fragments, read from the q rows staged in shared memory ([head][D] bf16, heads >= nheads are garbage)
+template <bool FP8, int NT>
+__device__ __forceinline__ void load_q_frags_smem(uint32_t (&qf)[NT][8][2], const uint32_t* qsm, int nheads, int lane) {
+    const int g = lane >> 2, t4 = lane & 3;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+        const int hl = nt * 8 + g;
+        const bool valid = hl < nheads;
+        const uint32_t* qrow = qsm + hl * (D / 2);
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            uint32_t w0 = 0u, w1 = 0u;
+            if (valid) {
+                if (!FP8) {
+                    w0 = qrow[kc * 8 + t4];
+                    w1 = qrow[kc * 8 + 4 + t4];
+                } else {
+                    w0 = qrow[kc * 8 + 2 * t4];
+                    w1 = qrow[kc * 8 + 2 * t4 + 1];
+                    w0 = pack_f16x2(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u));
+                    w1 = pack_f16x2(__uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
+                }
+            }
+            qf[nt][kc][0] = w0;
+            qf[nt][kc][1] = w1;
+        }
+    }
+}
+
 // One warp, one stage: 16 token rows [row_base, row_base+16) of which the first `nvalid` are real.
 template <class C, bool FP8, int NT>
 __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&qf)[NT][8][2], uint32_t kbase,
@@ -263,7 +338,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
 #pragma unroll
         for (int kc = 0; kc < 8; ++kc) {
             const int chunk = 2 * kc + (mi >> 1);        // 16-byte chunk of the 256-byte row
-            const uint32_t addr = kbase + (chunk >> 3) * (TOK * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            const uint32_t addr = tile_addr<false>(kbase, row, chunk);
             uint32_t a0, a1, a2, a3;
             b2::ldmatrix_x4(addr, a0, a1, a2, a3);
 #pragma unroll
@@ -276,7 +351,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
 #pragma unroll
         for (int kc2 = 0; kc2 < 4; ++kc2) {
             const int chunk = 2 * kc2 + (mi >> 1);
-            const uint32_t addr = kbase + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            const uint32_t addr = tile_addr<true>(kbase, row, chunk);
             uint32_t r0, r1, r2, r3;
             b2::ldmatrix_x4(addr, r0, r1, r2, r3);
             const uint32_t a0 = e4m3x2_to_f16x2(r0), a1 = e4m3x2_to_f16x2(r1);
@@ -343,7 +418,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
 #pragma unroll
         for (int dt = 0; dt < 8; ++dt) {
             const int chunk = 2 * dt + (mi & 1);
-            const uint32_t addr = vbase + (chunk >> 3) * (TOK * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            const uint32_t addr = tile_addr<false>(vbase, row, chunk);
             uint32_t a0, a1, a2, a3;
             b2::ldmatrix_x4_trans(addr, a0, a1, a2, a3);
             a0 &= mk_lo; a1 &= mk_lo; a2 &= mk_hi; a3 &= mk_hi;
@@ -359,7 +434,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
 #pragma unroll
         for (int dt2 = 0; dt2 < 4; ++dt2) {
             const int chunk = 2 * dt2 + (mi >> 1);
-            const uint32_t addr = vbase + row * 128 + (((chunk & 7) ^ (row & 7)) << 4);
+            const uint32_t addr = tile_addr<true>(vbase, row, chunk);
             uint32_t r0, r1, r2, r3;
             b2::ldmatrix_x4_trans(addr, r0, r1, r2, r3);
             r0 = __byte_perm(r0, 0, 0x3120); r1 = __byte_perm(r1, 0, 0x3120);
@@ -473,6 +548,8 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
     const int b = blockIdx.z;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
+    const int cta_lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (tid == 0) B2_TRACE_AT(cta_lin, 0);
     const int seq_len = p.seq_lens[b];
     const int t_begin = split * p.split_tokens;
     const int head0 = kvh * p.G + hg * C::HEADS;                 // first q head of this CTA
@@ -503,7 +580,9 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         const uint64_t pol = b2::policy_evict_first();
         produce_segment<C, NSTAGE>(&tmK, &tmV, p.block_tables + (int64_t)b * p.max_nb + t_begin / BS,
                                    (n_tok + BS - 1) / BS, kvh, ring, bar_full, bar_empty, it, lane, pol);
+        B2_TRACE_AT(cta_lin, 4);
     } else {
+        if (warp == 0) B2_TRACE_AT(cta_lin, 1);
         float sl2 = p.scale_log2, vs = 1.f;
         if (FP8) {
             sl2 *= *p.k_scale;   // K dequant scale folds into the softmax scale
@@ -514,6 +593,7 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         WarpAcc<NT> acc;
         acc.reset();
         consume_segment<C, FP8, NT, NSTAGE>(acc, qf, n_tok, ring, bar_full, bar_empty, it, sl2, warp, lane);
+        if (warp == 0) B2_TRACE_AT(cta_lin, 3);
         merge_warps<NT>(acc, scratch, C::SLOT_FLOATS, sl2, warp, lane);
         if (warp == 0) {
             if (p.num_splits == 1) {
@@ -669,6 +749,7 @@ paged_decode_persistent_kernel(const __grid_constant__ CUtensorMap tmK, const __
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int c = blockIdx.x;
     const int IPB = p.Hkv * p.HG;
+    if (tid == 0) B2_TRACE_AT(c, 0);
     // let the boundary-merge kernel (programmatic dependent launch) get resident and run its own
     // unit search while this grid streams; it blocks in griddepcontrol.wait until we are done
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -697,6 +778,7 @@ paged_decode_persistent_kernel(const __grid_constant__ CUtensorMap tmK, const __
     Cursor cur{s_cur[0], s_cur[1], s_cur[2]};
     uint32_t remaining = u1 - u0;
     uint32_t it = 0;
+    if (tid == 0) B2_TRACE_AT(c, 1);
 
     if (warp == NCW) {
         // ================================ producer warp =====================================
@@ -756,6 +838,7 @@ paged_decode_persistent_kernel(const __grid_constant__ CUtensorMap tmK, const __
             cur.blk += take;
             if (cur.blk == nb) { cur.blk = 0; if (++cur.j == IPB) { cur.j = 0; ++cur.b; } }
         }
+        if (warp == 0) B2_TRACE_AT(c, 3);
     }
 }
 
@@ -844,6 +927,428 @@ merge_boundary_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__
     }
 }
 
+// =============================================================================================
+// schedule C (default, num_splits = 0): persistent CTAs, a static head + dynamically claimed chunks
+// =============================================================================================
+// Work is cut on a fixed grid: item (b, j) has nck(b) = ceil(seq_len / CT) chunks of CT tokens (CT a
+// multiple of the 64-token stage).  Chunk ids are flattened sequence-major, then item, then chunk.
+// CTA x first streams the contiguous ids [x*S, (x+1)*S), S = floor(pct% * Ctot / NC); the remaining
+// ids are claimed one at a time from an atomic counter, so CTAs that stream faster (SM / L2-slice
+// placement differs by ~10 %) take more of the tail and the grid drains together.  Consecutive
+// static chunks of one item are accumulated in registers (a "run"); every dynamic chunk is its own
+// run.  A run that covers its item writes bf16 output, any other run writes a normalised fp32
+// partial + log2-sum-exp to a slot that whoever merges the item can compute from (Ctot, S, NC) alone:
+//     run starts  : k == 0, or c >= NC*S, or c % S == 0
+//     slot(c)     : c >= NC*S -> 2*NC + c - NC*S ;  c % S == 0 -> 2*(c/S) ;  else 2*(c/S) + 1
+// The producer warp owns the schedule and hands each 64-token stage to the consumers together
+// with a 16-byte descriptor {sequence, item, valid tokens, flags | slot << 4} in shared memory
+// (ordered by the stage's full-barrier), so the consumer warps are a plain loop over stages.
+constexpr int META_FIRST = 1, META_LAST = 2, META_END = 4, META_DIRECT = 8;
+
+__device__ __forceinline__ uint32_t dyn_static_chunks(uint32_t Ctot, uint32_t NC, int pct) {
+    return (uint32_t)(((uint64_t)Ctot * (uint32_t)pct / 100u) / NC);
+}
+__device__ __forceinline__ bool dyn_is_start(uint32_t c, uint32_t k, uint32_t S, uint32_t stat_total) {
+    return k == 0 || c >= stat_total || (c % S) == 0;   // S > 0 whenever c < stat_total
+}
+__device__ __forceinline__ uint32_t dyn_slot(uint32_t c, uint32_t S, uint32_t stat_total, uint32_t NC) {
+    if (c >= stat_total) return 2 * NC + (c - stat_total);
+    const uint32_t x = c / S;
+    return (c % S) == 0 ? 2 * x : 2 * x + 1;
+}
+__device__ __forceinline__ uint32_t chunks_of(int seq_len, int ct) {
+    return seq_len > 0 ? (uint32_t)((seq_len + ct - 1) / ct) : 0u;
+}
+
+// pre[e], e in [0, E]: chunks before sequence group e (gs sequences per group).  Returns Ctot = pre[E].
+template <int NT_>
+__device__ __forceinline__ uint32_t build_chunk_prefix(const int32_t* __restrict__ seq_lens, int B, int IPB, int ct,
+                                                       int gs, int E, uint32_t* pre) {
+    const int tid = threadIdx.x;
+    for (int e = tid; e < E; e += NT_) {
+        uint32_t s = 0;
+        const int b1 = min(B, (e + 1) * gs);
+        for (int b = e * gs; b < b1; ++b) s += chunks_of(seq_lens[b], ct) * IPB;
+        pre[e + 1] = s;
+    }
+    if (tid == 0) pre[0] = 0;
+    __syncthreads();
+    if (tid < 32) {   // in-place inclusive scan of pre[1..E], one contiguous strip per lane
+        const int per = (E + 31) / 32;
+        const int i0 = 1 + tid * per, i1 = min(E + 1, i0 + per);
+        uint32_t s = 0;
+        for (int i = i0; i < i1; ++i) s += pre[i];
+        uint32_t incl = s;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (tid >= off) incl += t;
+        }
+        uint32_t run = incl - s;
+        for (int i = i0; i < i1; ++i) {
+            run += pre[i];
+            pre[i] = run;
+        }
+    }
+    __syncthreads();
+    return pre[E];
+}
+
+struct ChunkPos {
+    int b, j, k, nck, seq_len;
+};
+// warp-uniform: every lane computes the same position
+__device__ __forceinline__ ChunkPos locate_chunk(uint32_t c, const uint32_t* pre, int E, int gs,
+                                                 const int32_t* __restrict__ seq_lens, int B, int IPB, int ct) {
+    int lo = 0, hi = E;   // largest e with pre[e] <= c  (pre[E] = Ctot > c)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (pre[mid] <= c) lo = mid; else hi = mid;
+    }
+    uint32_t acc = pre[lo];
+    ChunkPos r{0, 0, 0, 1, 0};
+    const int b1 = min(B, (lo + 1) * gs);
+    for (int b = lo * gs; b < b1; ++b) {
+        const int L = seq_lens[b];
+        const uint32_t nck = chunks_of(L, ct), span = nck * IPB;
+        if (c < acc + span) {
+            const uint32_t rr = c - acc;
+            r.b = b; r.j = (int)(rr / nck); r.k = (int)(rr % nck); r.nck = (int)nck; r.seq_len = L;
+            return r;
+        }
+        acc += span;
+    }
+    return r;   // not reached for c < Ctot
+}
+
+// Number of runs item [ci0, ci0 + nck) was cut into.
+__device__ __forceinline__ uint32_t dyn_runs_of_item(uint32_t ci0, uint32_t nck, uint32_t S, uint32_t stat_total) {
+    uint32_t n = 1;
+    for (uint32_t c = ci0 + 1; c < ci0 + nck; ++c) n += dyn_is_start(c, c - ci0, S, stat_total) ? 1u : 0u;
+    return n;
+}
+
+// The four consumer warps (tid128 = 0..127) combine the partial runs of one item into bf16 output rows.
+// thread -> (head tid128/16 [+8], 8 consecutive d); partials were written by other CTAs: read through L2 (ld.cg).
+template <int HEADS>
+__device__ __forceinline__ void merge_item(__nv_bfloat16* __restrict__ out_rows, const float* ws_o, const float* ws_lse,
+                                           uint32_t ci0, uint32_t nck, uint32_t S, uint32_t stat_total, uint32_t NC,
+                                           int nheads, int tid128) {
+    constexpr int MAXC = 4;
+    const uint32_t cend = ci0 + nck;
+    const int dc = (tid128 & 15) * 8;
+    for (int h = tid128 >> 4; h < nheads; h += 8) {
+        float m_run = -INFINITY, den = 0.f, num[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) num[i] = 0.f;
+        uint32_t c = ci0;
+        while (c < cend) {
+            float lse[MAXC];
+            float4 o0[MAXC], o1[MAXC];
+#pragma unroll
+            for (int i = 0; i < MAXC; ++i) {
+                while (c < cend && !dyn_is_start(c, c - ci0, S, stat_total)) ++c;
+                lse[i] = -INFINITY;
+                o0[i] = o1[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (c < cend) {
+                    const int64_t slot = dyn_slot(c, S, stat_total, NC);
+                    lse[i] = __ldcg(ws_lse + slot * HEADS + h);
+                    const float4* po = reinterpret_cast<const float4*>(ws_o + (slot * HEADS + h) * D + dc);
+                    o0[i] = __ldcg(po);
+                    o1[i] = __ldcg(po + 1);
+                    ++c;
+                }
+            }
+            float mx = m_run;
+#pragma unroll
+            for (int i = 0; i < MAXC; ++i) mx = fmaxf(mx, lse[i]);
+            if (mx == -INFINITY) continue;
+            const float a = m_run == -INFINITY ? 0.f : exp2f(m_run - mx);
+            den *= a;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) num[i] *= a;
+#pragma unroll
+            for (int i = 0; i < MAXC; ++i) {
+                const float w = lse[i] == -INFINITY ? 0.f : exp2f(lse[i] - mx);
+                den += w;
+                num[0] = fmaf(w, o0[i].x, num[0]); num[1] = fmaf(w, o0[i].y, num[1]);
+                num[2] = fmaf(w, o0[i].z, num[2]); num[3] = fmaf(w, o0[i].w, num[3]);
+                num[4] = fmaf(w, o1[i].x, num[4]); num[5] = fmaf(w, o1[i].y, num[5]);
+                num[6] = fmaf(w, o1[i].z, num[6]); num[7] = fmaf(w, o1[i].w, num[7]);
+            }
+            m_run = mx;
+        }
+        const float inv = den > 0.f ? 1.f / den : 0.f;
+        uint4 pk;
+        pk.x = b2::pack_bf16x2(num[0] * inv, num[1] * inv);
+        pk.y = b2::pack_bf16x2(num[2] * inv, num[3] * inv);
+        pk.z = b2::pack_bf16x2(num[4] * inv, num[5] * inv);
+        pk.w = b2::pack_bf16x2(num[6] * inv, num[7] * inv);
+        *reinterpret_cast<uint4*>(out_rows + (int64_t)h * D + dc) = pk;
+    }
+}
+
+template <int BS, bool FP8, int NT, int NSTAGE>
+__global__ void __launch_bounds__(NTHREADS, 2)
+paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                            const DecodeParams p) {
+    using C = Cfg<BS, FP8, NT, NSTAGE>;
+    static_assert(2 * (C::DYN_SMEM_BYTES + 1024) <= 233472, "two CTAs per SM must fit (dynamic schedule)");
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    int4* s_meta = reinterpret_cast<int4*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
+    float* scratch = reinterpret_cast<float*>(smem_raw + C::RING_BYTES + C::BAR_BYTES + C::META_BYTES);
+    uint32_t* s_pre =
+        reinterpret_cast<uint32_t*>(smem_raw + C::RING_BYTES + C::BAR_BYTES + C::META_BYTES + C::SCRATCH_BYTES);
+    uint8_t* s_q = smem_raw + C::RING_BYTES + C::BAR_BYTES + C::META_BYTES + C::SCRATCH_BYTES + C::PRE_BYTES;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t x = blockIdx.x, NC = gridDim.x;
+    const int IPB = p.Hkv * p.HG;
+    const int ct = p.chunk_tokens;
+    // the merge kernel may become resident now; it waits (griddepcontrol.wait) until this grid is done
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    // rows of empty sequences are defined here (no chunk ever visits them)
+    for (int b = x; b < p.B; b += NC)
+        if (p.seq_lens[b] <= 0)
+            for (int i = tid; i < p.Hq * D; i += NTHREADS) p.out[b * p.out_stride + i] = __float2bfloat16(0.f);
+
+    if (tid == 0) B2_TRACE_AT(x, 0);
+    const int gs = (p.B + C::PMAX - 1) / C::PMAX, E = (p.B + gs - 1) / gs;
+    const uint32_t Ctot = build_chunk_prefix<NTHREADS>(p.seq_lens, p.B, IPB, ct, gs, E, s_pre);
+    // The claim counter is zeroed by the preceding (tiny) kernel of this call.  Only the producer warp touches
+    // it, and only after its static share, so it orders itself after that kernel (griddepcontrol.wait) right
+    // before its first claim -- and at the latest before it exits, which keeps "this grid finished" =>
+    // "that grid finished" for whatever follows in the stream.
+    if (Ctot == 0) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        return;
+    }
+    const uint32_t S = dyn_static_chunks(Ctot, NC, p.static_pct);
+    const uint32_t stat_total = S * NC;
+
+    const uint32_t ring = b2::smem_u32(smem_raw);
+    if (ring & 1023u) __trap();
+    const uint32_t bar_full = ring + C::RING_BYTES;
+    const uint32_t bar_empty = bar_full + NSTAGE * 8;
+    init_pipeline(bar_full, bar_empty, NSTAGE, tid);
+    uint32_t it = 0;
+    if (tid == 0) B2_TRACE_AT(x, 1);
+
+    if (warp == NCW) {
+        // ================================ producer warp =====================================
+        if (lane == 0) {
+            b2::tma_prefetch_desc(&tmK);
+            b2::tma_prefetch_desc(&tmV);
+        }
+        const uint64_t pol = b2::policy_evict_first();
+        const int CB = ct / BS;                         // <= 32: a chunk's block ids fit one register per lane
+        uint32_t stat_cur = x * S;
+        const uint32_t stat_end = stat_cur + S;
+        uint32_t cid;
+        bool cur_static;
+        bool ordered = false;                           // griddepcontrol.wait executed
+        if (stat_cur < stat_end) {
+            cid = stat_cur++;
+            cur_static = true;
+        } else {
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            ordered = true;
+            uint32_t v = 0;
+            if (lane == 0) v = atomicAdd(p.counter, 1u);
+            cid = stat_total + __shfl_sync(0xffffffffu, v, 0);
+            cur_static = false;
+        }
+        bool run_first = true, cont_prev = false;
+        uint32_t run_c0 = 0;
+        int run_k0 = 0;
+        ChunkPos cp{0, 0, 0, 1, 0};
+        while (cid < Ctot) {
+            if (cont_prev) ++cp.k;                      // next chunk of the same item
+            else cp = locate_chunk(cid, s_pre, E, gs, p.seq_lens, p.B, IPB, ct);
+            if (run_first) {
+                run_c0 = cid;
+                run_k0 = cp.k;
+            }
+            const int nb = (cp.seq_len + BS - 1) / BS;
+            const int blk0 = cp.k * CB;
+            const int nblk = min(CB, nb - blk0);
+            const int tbl = lane < nblk ? p.block_tables[(int64_t)cp.b * p.max_nb + blk0 + lane] : 0;
+            // the id after this one: static ids are known, a dynamic one is claimed now and read late
+            const bool next_static = cur_static && stat_cur < stat_end;
+            uint32_t pend = 0;
+            if (!next_static) {
+                if (!ordered) {
+                    asm volatile("griddepcontrol.wait;" ::: "memory");
+                    ordered = true;
+                }
+                if (lane == 0) pend = atomicAdd(p.counter, 1u);
+            }
+            const bool cont = next_static && (cp.k + 1 < cp.nck);
+            const int ntok = min(ct, cp.seq_len - cp.k * ct);
+            const int n_stage = (ntok + TOK - 1) / TOK;
+            const int kvh = cp.j / p.HG;
+            for (int st = 0; st < n_stage; ++st, ++it) {
+                const uint32_t s = it % NSTAGE;
+                const uint32_t ph = (it / NSTAGE) & 1;
+                b2::mbar_wait(bar_empty + s * 8, ph ^ 1);
+                const int nb_stage = min(C::BLK_PER_STAGE, nblk - st * C::BLK_PER_STAGE);
+                const uint32_t kdst = ring + s * C::STAGE_BYTES;
+                const uint32_t vdst = kdst + C::TILE_BYTES;
+                if (lane == 0) {
+                    int flags = 0;
+                    if (st == 0 && run_first) flags |= META_FIRST;
+                    if (st == n_stage - 1 && !cont) {
+                        flags |= META_LAST;
+                        if (run_k0 == 0 && cp.k == cp.nck - 1) flags |= META_DIRECT;
+                        else flags |= (int)(dyn_slot(run_c0, S, stat_total, NC) << 4);
+                    }
+                    s_meta[s] = make_int4(cp.b, cp.j, min(TOK, ntok - st * TOK), flags);
+                    uint32_t tx = nb_stage * 2 * C::BOX_BYTES;
+                    if (C::QSMEM && (flags & META_FIRST)) {
+                        const int hg = cp.j - kvh * p.HG;
+                        const int head0 = kvh * p.G + hg * C::HEADS;
+                        const uint32_t qbytes = min(C::HEADS, p.G - hg * C::HEADS) * C::QROW_BYTES;
+                        tx += qbytes;
+                        b2::mbar_arrive_expect_tx(bar_full + s * 8, tx);
+                        b2::bulk_load(b2::smem_u32(s_q + s * C::QBUF_BYTES),
+                                      p.q + cp.b * p.q_stride + (int64_t)head0 * D, qbytes, bar_full + s * 8);
+                    } else {
+                        b2::mbar_arrive_expect_tx(bar_full + s * 8, tx);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < C::BLK_PER_STAGE; ++j) {
+                    const int blk = __shfl_sync(0xffffffffu, tbl, (st * C::BLK_PER_STAGE + j) & 31);
+                    if (j < nb_stage && lane == 0)
+                        issue_block<C, FP8>(&tmK, &tmV, kdst, vdst, j, bar_full + s * 8, kvh, blk, pol);
+                }
+            }
+            run_first = !cont;
+            cont_prev = cont;
+            if (next_static) cid = stat_cur++;
+            else cid = stat_total + __shfl_sync(0xffffffffu, pend, 0);
+            cur_static = next_static;
+        }
+        if (!ordered) asm volatile("griddepcontrol.wait;" ::: "memory");
+        // end-of-work sentinel: a stage with no bytes
+        const uint32_t s = it % NSTAGE;
+        b2::mbar_wait(bar_empty + s * 8, ((it / NSTAGE) & 1) ^ 1);
+        if (lane == 0) {
+            s_meta[s] = make_int4(0, 0, 0, META_END);
+            b2::mbar_arrive(bar_full + s * 8);
+        }
+    } else {
+        // ================================ consumer warps ====================================
+        float sl2 = p.scale_log2, vs = 1.f;
+        if (FP8) {
+            sl2 *= *p.k_scale;
+            vs = *p.v_scale;
+        }
+        WarpAcc<NT> acc;
+        acc.reset();
+        uint32_t qf[NT][8][2];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int kc = 0; kc < 8; ++kc) qf[nt][kc][0] = qf[nt][kc][1] = 0u;
+        int cb = 0, head0 = 0, nheads = 0;
+        const int row_base = warp * 16;
+        for (;; ++it) {
+            const uint32_t s = it % NSTAGE;
+            b2::mbar_wait(bar_full + s * 8, (it / NSTAGE) & 1);
+            const int4 m = s_meta[s];
+            if (m.w & META_END) {
+                if (warp == 0) {
+                    B2_TRACE_AT(x, 3);
+                    B2_TRACE_VAL(x, 5, (unsigned long long)it);
+                }
+                break;
+            }
+            if (m.w & META_FIRST) {
+                cb = m.x;
+                const int kvh = m.y / p.HG, hg = m.y - kvh * p.HG;
+                head0 = kvh * p.G + hg * C::HEADS;
+                nheads = min(C::HEADS, p.G - hg * C::HEADS);
+                if (C::QSMEM)
+                    load_q_frags_smem<FP8, NT>(qf, reinterpret_cast<const uint32_t*>(s_q + s * C::QBUF_BYTES), nheads, lane);
+                else
+                    load_q_frags<FP8, NT>(qf, p.q + cb * p.q_stride + (int64_t)head0 * D, nheads, lane);
+                acc.reset();
+            }
+            const int nvalid = m.z - row_base;
+            if (nvalid > 0) {
+                const uint32_t kbase = ring + s * C::STAGE_BYTES;
+                consume_slab<C, FP8, NT>(acc, qf, kbase, kbase + C::TILE_BYTES, row_base, nvalid, sl2, lane);
+            }
+            __syncwarp();
+            if (lane == 0) b2::mbar_arrive(bar_empty + s * 8);   // the stage and its descriptor may be reused
+            if (m.w & META_LAST) {
+                merge_warps<NT>(acc, scratch, C::SLOT_FLOATS, sl2, warp, lane);
+                if (warp == 0) {
+                    if (m.w & META_DIRECT) {
+                        write_result<FP8, NT>(acc, nheads, vs, sl2, p.out + cb * p.out_stride + (int64_t)head0 * D,
+                                              nullptr, nullptr, lane);
+                    } else {
+                        const int64_t slot = (int64_t)((uint32_t)m.w >> 4);
+                        write_result<FP8, NT>(acc, nheads, vs, sl2, nullptr, p.ws_o + slot * (C::HEADS * D),
+                                              p.ws_lse + slot * C::HEADS, lane);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// first kernel of a dynamic-schedule call: zero the claim counter
+__global__ void zero_counter_kernel(uint32_t* counter) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the decode grid may start its static share
+    if (threadIdx.x == 0) *counter = 0u;
+}
+
+// One block per item (sequence b = blockIdx.y, item j = blockIdx.x): combine its partial runs unless one
+// run covered it.  Which chunks start a run, and where their partials live, follows from (Ctot, S, NC)
+// -- the same arithmetic as the main kernel, no flags in memory.
+template <int HEADS>
+__global__ void __launch_bounds__(128)
+merge_chunks_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ ws_o,
+                    const float* __restrict__ ws_lse, const int32_t* __restrict__ seq_lens, int B, int Hkv, int G,
+                    int HG, int64_t out_stride, int ct, int static_pct, uint32_t NC) {
+    __shared__ uint32_t s_red[2][4];
+    const int tid = threadIdx.x, b = blockIdx.y, j = blockIdx.x;
+    const int IPB = Hkv * HG;
+    uint32_t before = 0, total = 0;
+    for (int i = tid; i < B; i += 128) {
+        const uint32_t n = chunks_of(seq_lens[i], ct) * IPB;
+        total += n;
+        if (i < b) before += n;
+    }
+#pragma unroll
+    for (int off = 16; off; off >>= 1) {
+        before += __shfl_xor_sync(0xffffffffu, before, off);
+        total += __shfl_xor_sync(0xffffffffu, total, off);
+    }
+    if ((tid & 31) == 0) {
+        s_red[0][tid >> 5] = before;
+        s_red[1][tid >> 5] = total;
+    }
+    __syncthreads();
+    before = s_red[0][0] + s_red[0][1] + s_red[0][2] + s_red[0][3];
+    total = s_red[1][0] + s_red[1][1] + s_red[1][2] + s_red[1][3];
+    // every block waits for the decode grid, so "merge finished" implies "decode finished" for later work
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const uint32_t nck = chunks_of(seq_lens[b], ct);
+    if (nck <= 1) return;                                 // a single chunk is always written directly
+    const uint32_t S = dyn_static_chunks(total, NC, static_pct);
+    const uint32_t stat_total = S * NC;
+    const uint32_t ci0 = before + (uint32_t)j * nck;
+    if (dyn_runs_of_item(ci0, nck, S, stat_total) == 1) return;   // one run covered the item: already in `out`
+    const int kvh = j / HG, hg = j - kvh * HG;
+    const int head0 = kvh * G + hg * HEADS;
+    merge_item<HEADS>(out + b * out_stride + (int64_t)head0 * D, ws_o, ws_lse, ci0, nck, S, stat_total, NC,
+                      min(HEADS, G - hg * HEADS), tid);
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -864,20 +1369,30 @@ EncodeTiledFn get_encode_tiled() {
     return fn;
 }
 
-// cache viewed as [num_blocks][Hkv][bs][128 elements]; one box = bs rows x 128 bytes
+// fp8: cache viewed as [num_blocks][Hkv][bs][128 B]; bf16: [num_blocks][Hkv][bs][2 halves][64 elements].
+// One box = one whole (block, head) tile, contiguous in HBM.
 int make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t num_blocks, int Hkv,
                     int bs, int64_t block_stride, int64_t head_stride) {
     EncodeTiledFn enc = get_encode_tiled();
     B2_REQUIRE(enc != nullptr, B2_ECUDA, "cuTensorMapEncodeTiled entry point not available");
-    const int esz = kv_dtype == B2_KV_FP8_E4M3 ? 1 : 2;
-    cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)bs, (cuuint64_t)Hkv, (cuuint64_t)num_blocks};
-    cuuint64_t strides[3] = {(cuuint64_t)D * esz, (cuuint64_t)head_stride * esz, (cuuint64_t)block_stride * esz};
-    cuuint32_t box[4] = {(cuuint32_t)(128 / esz), (cuuint32_t)bs, 1, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    const CUresult r = enc(tm, esz == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
-                           const_cast<void*>(cache), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r;
+    if (kv_dtype == B2_KV_FP8_E4M3) {
+        cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)bs, (cuuint64_t)Hkv, (cuuint64_t)num_blocks};
+        cuuint64_t strides[3] = {(cuuint64_t)D, (cuuint64_t)head_stride, (cuuint64_t)block_stride};
+        cuuint32_t box[4] = {128, (cuuint32_t)bs, 1, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(cache), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        cuuint64_t dims[5] = {64, 2, (cuuint64_t)bs, (cuuint64_t)Hkv, (cuuint64_t)num_blocks};
+        cuuint64_t strides[4] = {128, (cuuint64_t)D * 2, (cuuint64_t)head_stride * 2, (cuuint64_t)block_stride * 2};
+        cuuint32_t box[5] = {64, 2, (cuuint32_t)bs, 1, 1};
+        cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+        r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(cache), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
     B2_REQUIRE(r == CUDA_SUCCESS, B2_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return B2_OK;
 }
@@ -896,16 +1411,55 @@ struct Plan {
     int hg;            // head groups per kv head
     int num_splits;    // 0 = persistent schedule
     int split_tokens;
+    bool dynamic;      // persistent: dynamic claims (default) or the static equal split (B2_SCHEDULE=static)
+    int chunk_tokens;  // dynamic: claim granularity
+    int static_pct;    // dynamic: share of the chunks dealt out statically
+    int64_t slots;     // dynamic: partial slots in the workspace
+    int ipb;           // items per sequence = Hkv * hg
 };
 
-void make_plan(Plan* pl, int G, int bs, int max_nb, int num_splits) {
+// dynamic schedule: workspace header (claim counter)
+size_t ws_header_bytes(int, int) { return 256; }
+
+int env_int(const char* name, int dflt) {
+    const char* s = getenv(name);
+    return (s && *s) ? atoi(s) : dflt;
+}
+
+void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_splits) {
     pl->nt = G <= 8 ? 1 : 2;
     const int hpc = 8 * pl->nt;
     pl->hg = (G + hpc - 1) / hpc;
     pl->num_splits = 0;
     pl->split_tokens = 0;
-    if (num_splits <= 0) return;
+    pl->dynamic = false;
+    pl->chunk_tokens = 0;
+    pl->static_pct = 0;
+    pl->slots = 0;
+    pl->ipb = Hkv * pl->hg;
     const int64_t max_ctx = (int64_t)max_nb * bs;
+    if (num_splits <= 0) {
+        // diagnostic overrides, read once per call (cheap): B2_SCHEDULE=static|dynamic, B2_CHUNK_TOKENS, B2_STATIC_PCT
+        const char* sch = getenv("B2_SCHEDULE");
+        pl->dynamic = !(sch && sch[0] == 's');
+        if (!pl->dynamic) return;
+        const int NC = persistent_grid();
+        const int ipb = Hkv * pl->hg;
+        const int ct_max = bs * 32 < 512 ? bs * 32 : 512;   // <= 32 blocks per chunk
+        // aim for >= 8 chunks per CTA (run boundaries cost more than a slightly longer tail), within [64, ct_max] tokens
+        const int64_t total_tok = (int64_t)B * ipb * max_ctx;
+        int ct = TOK;
+        while (ct * 2 <= ct_max && total_tok / (ct * 2) >= (int64_t)8 * NC) ct *= 2;
+        const int ect = env_int("B2_CHUNK_TOKENS", 0);
+        if (ect >= TOK && ect <= ct_max && ect % TOK == 0 && ect % bs == 0) ct = ect;
+        int pct = env_int("B2_STATIC_PCT", 85);
+        pct = pct < 0 ? 0 : (pct > 100 ? 100 : pct);
+        pl->chunk_tokens = ct;
+        pl->static_pct = pct;
+        const int64_t ctot_max = (int64_t)B * ipb * ((max_ctx + ct - 1) / ct);
+        pl->slots = 2 * (int64_t)NC + ctot_max * (100 - pct) / 100 + NC + 2;
+        return;
+    }
     int64_t st = (max_ctx + num_splits - 1) / num_splits;
     st = ((st + TOK - 1) / TOK) * TOK;   // whole stages, hence whole blocks
     pl->split_tokens = (int)st;
@@ -914,7 +1468,10 @@ void make_plan(Plan* pl, int G, int bs, int max_nb, int num_splits) {
 }
 
 size_t plan_workspace(const Plan& pl, int B, int Hq) {
-    if (pl.num_splits == 0) return (size_t)persistent_grid() * 2 * (8 * pl.nt) * (D + 1) * sizeof(float);
+    if (pl.num_splits == 0) {
+        if (pl.dynamic) return ws_header_bytes(B, pl.ipb) + (size_t)pl.slots * (8 * pl.nt) * (D + 1) * sizeof(float);
+        return (size_t)persistent_grid() * 2 * (8 * pl.nt) * (D + 1) * sizeof(float);
+    }
     if (pl.num_splits == 1) return 0;
     return (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
 }
@@ -924,6 +1481,40 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
                   cudaStream_t st) {
     constexpr int NSTAGE = FP8 ? 6 : 3;
     using C = Cfg<BS, FP8, NT, NSTAGE>;
+    if (pl.num_splits == 0 && pl.dynamic) {
+        constexpr int NSTAGE_D = FP8 ? 5 : 3;   // fp8: one 16 KiB stage gives way to the per-stage q buffers
+        using C = Cfg<BS, FP8, NT, NSTAGE_D>;
+        auto kern = paged_decode_dynamic_kernel<BS, FP8, NT, NSTAGE_D>;
+        static bool attr_set3 = false;   // per instantiation; idempotent, so a race is harmless
+        if (!attr_set3) {
+            B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::DYN_SMEM_BYTES));
+            attr_set3 = true;
+        }
+        const int grid = persistent_grid();
+        zero_counter_kernel<<<1, 32, 0, st>>>(p.counter);
+        B2_CUDA_OK(cudaGetLastError());
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(NTHREADS);
+        cfg.dynamicSmemBytes = C::DYN_SMEM_BYTES;
+        cfg.stream = st;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        B2_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmK, tmV, p));
+        cudaLaunchConfig_t cfg2 = {};
+        cfg2.gridDim = dim3(p.Hkv * p.HG, p.B);
+        cfg2.blockDim = dim3(128);
+        cfg2.stream = st;
+        cfg2.attrs = at;
+        cfg2.numAttrs = 1;
+        B2_CUDA_OK(cudaLaunchKernelEx(&cfg2, merge_chunks_kernel<8 * NT>, p.out, (const float*)p.ws_o,
+                                      (const float*)p.ws_lse, p.seq_lens, p.B, p.Hkv, p.G, p.HG, p.out_stride,
+                                      p.chunk_tokens, p.static_pct, (uint32_t)grid));
+        return B2_OK;
+    }
     if (pl.num_splits == 0) {
         auto kern = paged_decode_persistent_kernel<BS, FP8, NT, NSTAGE>;
         static bool attr_set = false;   // per instantiation; idempotent, so a race is harmless
@@ -985,11 +1576,46 @@ extern "C" int b2_paged_decode_auto_splits(int B, int Hq, int Hkv, int d, int bs
     return 0;   // num_splits = 0 selects the persistent schedule: no fixed split count
 }
 
+// Host-side schedule choice from the scheduler's own (host) copy of seq_lens -- the same role max_seq_len plays
+// for vLLM's v1/v2 choice.  Model: CTAs of the single-pass grid (one per item, launched in grid order onto
+// 2 x SMs slots, greedily) each stream `len + overhead` tokens; HBM saturates with ~3/4 of the slots busy, so a
+// slot can run up to 1.37x its fair share.  If that makespan stays within 2 % of the ideal (total / slots), the
+// single-pass grid wins (no workspace, no merge, no schedule prologue); otherwise the dynamic schedule does.
+extern "C" int b2_paged_decode_plan_splits(const int32_t* seq_lens_host, int B, int Hq, int Hkv, int d, int bs,
+                                           int kv_dtype) {
+    (void)kv_dtype;
+    if (!seq_lens_host || !shape_ok(B, Hq, Hkv, d, bs, 1)) return B2_EINVAL;
+    const int G = Hq / Hkv;
+    const int hpc = G <= 8 ? 8 : 16;
+    const int ipb = Hkv * ((G + hpc - 1) / hpc);
+    const int NC = persistent_grid();
+    const int64_t items = (int64_t)B * ipb;
+    if (items < NC) return 0;
+    constexpr int64_t OVERHEAD_TOK = 128;   // CTA launch + pipeline fill, in streamed-token equivalents
+    std::vector<int64_t> slot((size_t)NC, 0);   // min-heap of slot finish times
+    auto cmp = [](int64_t a, int64_t b) { return a > b; };
+    int64_t total = 0, makespan = 0;
+    for (int b = 0; b < B; ++b) {
+        const int64_t L = seq_lens_host[b] > 0 ? seq_lens_host[b] : 0;
+        for (int j = 0; j < ipb; ++j) {
+            std::pop_heap(slot.begin(), slot.end(), cmp);
+            int64_t& t = slot.back();
+            t += L + OVERHEAD_TOK;
+            if (t > makespan) makespan = t;
+            std::push_heap(slot.begin(), slot.end(), cmp);
+            total += L + OVERHEAD_TOK;
+        }
+    }
+    const double ideal = (double)total / NC;
+    const double est = std::max(ideal, (double)makespan / 1.37);
+    return est <= 1.02 * ideal ? 1 : 0;
+}
+
 extern "C" size_t b2_paged_decode_workspace_bytes(int B, int Hq, int Hkv, int d, int bs, int max_nb,
                                                   int num_splits) {
     if (!shape_ok(B, Hq, Hkv, d, bs, max_nb)) return 0;
     Plan pl;
-    make_plan(&pl, Hq / Hkv, bs, max_nb, num_splits);
+    make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits);
     return plan_workspace(pl, B, Hq);
 }
 
@@ -1024,7 +1650,7 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
 
     const int G = Hq / Hkv;
     Plan pl;
-    make_plan(&pl, G, bs, max_nb, num_splits);
+    make_plan(&pl, B, Hkv, G, bs, max_nb, num_splits);
 
     DecodeParams p;
     p.out = static_cast<__nv_bfloat16*>(out);
@@ -1039,11 +1665,22 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
     p.scale_log2 = scale * LOG2E;
     p.ws_o = nullptr; p.ws_lse = nullptr;
     const size_t need = plan_workspace(pl, B, Hq);
+    p.counter = nullptr;
+    p.chunk_tokens = pl.chunk_tokens;
+    p.static_pct = pl.static_pct;
     if (need) {
         B2_REQUIRE(workspace && workspace_bytes >= need && b2_aligned16(workspace), B2_ENOMEM,
                    "paged_decode: workspace %zu bytes < required %zu", workspace_bytes, need);
-        p.ws_o = static_cast<float*>(workspace);
-        p.ws_lse = p.ws_o + need / sizeof(float) / (D + 1) * D;
+        size_t body = need;
+        char* base = static_cast<char*>(workspace);
+        if (pl.num_splits == 0 && pl.dynamic) {
+            B2_REQUIRE(pl.slots < (1LL << 27), B2_EUNSUPPORTED, "paged_decode: %lld partial slots", (long long)pl.slots);
+            p.counter = reinterpret_cast<uint32_t*>(base);
+            base += ws_header_bytes(B, pl.ipb);
+            body -= ws_header_bytes(B, pl.ipb);
+        }
+        p.ws_o = reinterpret_cast<float*>(base);
+        p.ws_lse = p.ws_o + body / sizeof(float) / (D + 1) * D;
     }
 
     CUtensorMap tmK, tmV;
@@ -1058,3 +1695,14 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
     if (bs == 16) return dispatch_decode<16>(tmK, tmV, p, pl, fp8, st);
     return dispatch_decode<32>(tmK, tmV, p, pl, fp8, st);
 }
+
+#ifdef B2_TRACE
+extern "C" B2_API int b2_debug_read_trace(unsigned long long* dst, int n_words) {
+    if (n_words > 2048 * 8) n_words = 2048 * 8;
+    return cudaMemcpyFromSymbol(dst, g_trace, (size_t)n_words * 8) == cudaSuccess ? 0 : B2_ECUDA;
+}
+extern "C" B2_API int b2_debug_clear_trace(void) {
+    static unsigned long long zeros[2048 * 8];
+    return cudaMemcpyToSymbol(g_trace, zeros, sizeof zeros) == cudaSuccess ? 0 : B2_ECUDA;
+}
+#endif
