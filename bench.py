@@ -270,12 +270,25 @@ def run_ours(args, wl_name, wl):
     sl_d = prob["seq_lens"].to(dev)
     slot_d = prob["slot_new"].to(dev)
     ks, vs = prob["scales"] or (None, None)
-    num_splits = args.splits
-    used_splits = b200attn.decode_auto_splits(B, Hq_l, Hkv_l, D, BS, prob["max_nb"]) if num_splits == 0 else num_splits
+    # schedule: the engine's scheduler holds seq_lens on the host and picks the schedule from them (--splits -1)
+    if args.splits < 0:
+        num_splits = b200attn.plan_num_splits(prob["seq_lens"], Hq_l, Hkv_l, D, BS)
+        schedule_src = "host planner (b2_paged_decode_plan_splits on host seq_lens)"
+    else:
+        num_splits = args.splits
+        schedule_src = "--splits"
+    used_splits = num_splits
+    schedule = {0: "dynamic persistent (zero + decode + merge kernels)", 1: "single-pass grid"}.get(
+        num_splits, f"grid split x{num_splits} + merge")
     ws_bytes = b200attn.decode_workspace_bytes(B, Hq_l, Hkv_l, D, BS, prob["max_nb"], num_splits)
     ws = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=dev)
     out = torch.empty(B, Hq_l, D, dtype=torch.bfloat16, device=dev)
-    launches_per_step = 2 + (1 if used_splits != 1 else 0)   # reshape + decode (+ merge)
+    if num_splits == 1:
+        launches_per_step = 2                                  # reshape + decode
+    elif num_splits == 0:
+        launches_per_step = 4                                  # reshape + zero-counter + decode + merge
+    else:
+        launches_per_step = 3                                  # reshape + decode + merge
 
     def step_resident():
         b200attn.reshape_and_cache(prob["k_new"], prob["v_new"], prob["k_cache"], prob["v_cache"], slot_d, ks, vs)
@@ -316,34 +329,28 @@ def run_ours(args, wl_name, wl):
     value = bytes_rank * world / (ms_per_step * 1e-3) / 1e9
 
     # ---------------- end to end through the public API with HOST buffers: `e2e` ----------------
-    pin = lambda x: x.cpu().pin_memory()  # noqa: E731
-    h_q, h_k, h_v = pin(prob["q"]), pin(prob["k_new"]), pin(prob["v_new"])
-    h_bt, h_sl, h_slot = pin(prob["block_tables"]), pin(prob["seq_lens"]), pin(prob["slot_new"])
-    h_out = torch.empty(B, Hq_l, D, dtype=torch.bfloat16).pin_memory()
-    d_q, d_k, d_v = torch.empty_like(prob["q"]), torch.empty_like(prob["k_new"]), torch.empty_like(prob["v_new"])
-    d_bt, d_sl, d_slot = torch.empty_like(bt_d), torch.empty_like(sl_d), torch.empty_like(slot_d)
-    h2d = sum(x.numel() * x.element_size() for x in (h_q, h_k, h_v, h_bt, h_sl, h_slot))
-    d2h = h_out.numel() * h_out.element_size()
-
-    def step_e2e():
-        d_q.copy_(h_q, non_blocking=True)
-        d_k.copy_(h_k, non_blocking=True)
-        d_v.copy_(h_v, non_blocking=True)
-        d_bt.copy_(h_bt, non_blocking=True)
-        d_sl.copy_(h_sl, non_blocking=True)
-        d_slot.copy_(h_slot, non_blocking=True)
-        b200attn.reshape_and_cache(d_k, d_v, prob["k_cache"], prob["v_cache"], d_slot, ks, vs)
-        b200attn.paged_decode(d_q, prob["k_cache"], prob["v_cache"], d_bt, d_sl, k_scale=ks, v_scale=vs,
-                              out=out, workspace=ws, num_splits=num_splits)
-        h_out.copy_(out, non_blocking=True)
-        stream.synchronize()      # the caller reads the step's result before planning the next step
-
+    # b200attn.DecodeStep: pinned q|k|v and block_tables|seq_lens|slots -> 2 H2D copies, both kernels, result rows
+    # stored by the kernels straight into pinned host memory, stream sync; replayed as one CUDA graph per step.
+    step = b200attn.DecodeStep(prob["k_cache"], prob["v_cache"], max_batch=B, Hq=Hq_l, max_nb=prob["max_nb"],
+                               k_scale=ks, v_scale=vs)
+    step.h_qkv[:, :Hq_l].copy_(prob["q"].cpu())
+    step.h_qkv[:, Hq_l:Hq_l + Hkv_l].copy_(prob["k_new"].cpu())
+    step.h_qkv[:, Hq_l + Hkv_l:].copy_(prob["v_new"].cpu())
+    step.h_block_tables.copy_(prob["block_tables"])
+    step.h_seq_lens.copy_(prob["seq_lens"])
+    step.h_slots.copy_(prob["slot_new"])
+    h2d, d2h = step.h2d_bytes, step.d2h_bytes
+    e2e_splits = None if args.splits < 0 else args.splits      # None: planned on the host inside every step
     for _ in range(max(3, args.warmup // 4)):
-        step_e2e()
+        h_res = step.run(B, e2e_splits)
+    if not torch.equal(h_res.view(torch.int16), out.cpu().view(torch.int16)) and rank == 0:
+        diff = (h_res.float() - out.cpu().float()).abs().max().item()
+        if not diff < 2e-2:
+            raise SystemExit(f"e2e result differs from the device-resident result (max abs diff {diff})")
     barrier()
     t0 = time.perf_counter()
     for _ in range(K):
-        step_e2e()
+        step.run(B, e2e_splits)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / K
     t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
@@ -370,17 +377,21 @@ def run_ours(args, wl_name, wl):
                        "block_size": BS, "kv_dtype": "fp8_e4m3" if fp8 else "bf16",
                        "parallelism": f"kv-head-shard tp{tp}" if tp > 1 else "1 GPU",
                        "per_gpu": {"B": B, "Hq": Hq_l, "Hkv": Hkv_l}, "num_splits": used_splits,
+                       "schedule": schedule, "schedule_chosen_by": schedule_src,
                        "step": "reshape_and_cache(1 new token/seq) + paged_decode, one layer",
                        "algorithmic_bytes_per_step_per_gpu": bytes_rank,
                        "l2": "KV working set per GPU >> 126 MB L2, every step streams it from HBM; no flush needed"},
             "pct_of_8TBps": round(100.0 * value / world / NOMINAL_HBM_GBS, 2),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
                          "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "b2_paged_decode (decode kernel + its merge kernel)",
+                         "kernel": "b2_paged_decode (every kernel the call launches)",
                          "kernel_ms": round(dec_mean_ms, 5), "kernel_ms_min": round(min(dec_ms), 5),
                          "frac_of_8TBps": round(achieved / NOMINAL_HBM_GBS, 4)},
             "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": round(e2e_ms, 5)},
+                    "ms_per_step": round(e2e_ms, 5),
+                    "path": "b200attn.DecodeStep: 2 H2D copies from pinned memory, reshape_and_cache + paged_decode, "
+                            "result rows stored by the kernels into pinned host memory (the D2H leg), stream sync; "
+                            "one CUDA-graph replay per step, schedule planned on the host per step"},
             "gpu_launches": launches_per_step * K,
             "clocks": clk.summary(),
         }
@@ -404,7 +415,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="llama3-8b_b64_ctx4k_bf16kv")
-    ap.add_argument("--splits", type=int, default=0, help="num_splits passed to b2_paged_decode (0 = auto)")
+    ap.add_argument("--splits", type=int, default=-1,
+                    help="num_splits for b2_paged_decode: -1 = host planner (default), 0 = dynamic persistent, 1 = single pass")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--batch", type=int, default=0, help="override the workload batch size (experiments only)")
     args = ap.parse_args()

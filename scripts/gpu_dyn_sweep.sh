@@ -15,7 +15,7 @@ except Exception as e:
 PY
 }
 B="timeout 300 python bench.py --steps 300 --warmup 20 --no-cpu"
-run "c2 static      " B2_SCHEDULE=static $B
+
 run "c2 splits1     " X=1 $B --splits 1
 for pct in 0 50 70 85; do for ct in 128 256 512; do
 run "c2 dyn pct$pct ct$ct" B2_STATIC_PCT=$pct B2_CHUNK_TOKENS=$ct $B

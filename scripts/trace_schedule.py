@@ -2,7 +2,7 @@
 
     B200ATTN_LIB=vllm-backend-public_b200/lib/libb200attn_trace.so python scripts/trace_schedule.py [workload]
 
-For each schedule (static persistent, grid split 1, dynamic) it runs one traced launch on the headline config
+For each schedule (grid split 1, dynamic with several chunk sizes / static shares) it runs one traced launch on the headline config
 and prints: kernel span, distribution of CTA start / first-data / end times, per-CTA busy time, idle tail.
 """
 import ctypes as C
@@ -34,7 +34,7 @@ def pct(a, q):
 
 
 def run(label, splits, env):
-    for k in ("B2_SCHEDULE", "B2_CHUNK_TOKENS", "B2_STATIC_PCT"):
+    for k in ("B2_CHUNK_TOKENS", "B2_STATIC_PCT"):
         os.environ.pop(k, None)
     os.environ.update(env)
     ws = torch.zeros(max(16, b200attn.decode_workspace_bytes(wl["B"], wl["Hq"], wl["Hkv"], 128, 16, prob["max_nb"], splits)),
@@ -77,9 +77,8 @@ def run(label, splits, env):
     print("   alive CTAs every 10 us:", alive)
 
 
-run("static persistent", 0, {"B2_SCHEDULE": "static"})
 run("grid split, num_splits=1", 1, {})
 run("dynamic pct85 ct512", 0, {"B2_STATIC_PCT": "85", "B2_CHUNK_TOKENS": "512"})
 run("dynamic pct85 ct256", 0, {"B2_STATIC_PCT": "85", "B2_CHUNK_TOKENS": "256"})
-run("dynamic pct70 ct256 (default)", 0, {})
+run("dynamic default", 0, {})
 run("dynamic pct0 ct128", 0, {"B2_STATIC_PCT": "0", "B2_CHUNK_TOKENS": "128"})

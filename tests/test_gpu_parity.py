@@ -297,3 +297,62 @@ def test_full_size_config3_fp8_b128_ctx8k(cuda):
 def test_full_size_config4_per_gpu_shard_tp8(cuda):
     """BASELINE.json configs[3] as seen by one of 8 ranks: 8 q / 1 kv head, batch 256, ctx 8192."""
     _full_size(cuda, 256, 8, 1, 8192, fp8=False, seed=2, n_oracle=1)
+
+
+# ------------------------------------------------------------------------------------------
+# schedules of the persistent kernel: every (chunk size, static share) must give the same answer
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("env", [{}, {"B2_STATIC_PCT": "0", "B2_CHUNK_TOKENS": "64"},
+                                 {"B2_STATIC_PCT": "50", "B2_CHUNK_TOKENS": "128"}, {"B2_STATIC_PCT": "100"},
+                                 {"B2_STATIC_PCT": "85", "B2_CHUNK_TOKENS": "512"}])
+def test_decode_schedule_variants_ragged(cuda, env, monkeypatch):
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    inp = R.make_inputs(37, 16, 4, 128, 16, 1500, seed=11, ragged=True)
+    inp["seq_lens"][3] = 0
+    inp["seq_lens"][5] = 1          # (lengths may only shrink: the block tables were dealt for the original ones)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda, poison=True)
+    ref = R.paged_decode_ref(inp["q"], torch.nan_to_num(kc_ref), torch.nan_to_num(vc_ref), inp["block_tables"],
+                             inp["seq_lens"], return_f32=True)
+    out = b200attn.paged_decode(inp["q"].to(cuda), kc, vc, inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda),
+                                num_splits=0)
+    assert_close(out, ref, what=f"schedule {env}")
+    assert float(out[3].float().abs().max()) == 0.0
+
+
+def test_decode_many_sequences_grouped_prefix(cuda):
+    """More sequences than the kernel's shared-memory prefix holds entries (512): grouped prefix + walk."""
+    inp = R.make_inputs(700, 4, 1, 128, 16, 96, seed=12, ragged=True)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    out = b200attn.paged_decode(inp["q"].to(cuda), kc, vc, inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda))
+    assert_close(out, ref, what="B=700")
+
+
+# ------------------------------------------------------------------------------------------
+# the engine-facing step: host buffers in, host rows out (CUDA graph, output stored to pinned memory)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_decode_step_from_host_buffers(cuda, use_graph):
+    B, Hq, Hkv, ctx = 6, 8, 2, 300
+    inp = R.make_inputs(B, Hq, Hkv, 128, 16, ctx, seed=21, ragged=True)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    step = b200attn.DecodeStep(kc, vc, max_batch=8, Hq=Hq, max_nb=inp["max_nb"], use_graph=use_graph)
+    g = torch.Generator().manual_seed(5)
+    for it in range(3):    # three decode steps: each rewrites the last token of every sequence, then attends
+        k_new = torch.randn(B, Hkv, 128, generator=g).to(torch.bfloat16)
+        v_new = torch.randn(B, Hkv, 128, generator=g).to(torch.bfloat16)
+        q = torch.randn(B, Hq, 128, generator=g).to(torch.bfloat16)
+        last = inp["seq_lens"].long() - 1
+        slots = inp["block_tables"][torch.arange(B), last // 16].long() * 16 + last % 16
+        step.h_qkv[:B, :Hq] = q
+        step.h_qkv[:B, Hq:Hq + Hkv] = k_new
+        step.h_qkv[:B, Hq + Hkv:] = v_new
+        step.h_block_tables[:B] = inp["block_tables"]
+        step.h_seq_lens[:B] = inp["seq_lens"]
+        step.h_slots[:B] = slots
+        out = step.run(B).clone()
+        R.reshape_and_cache_ref(k_new, v_new, kc_ref, vc_ref, slots)
+        ref = R.paged_decode_ref(q, kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+        assert_close(out, ref, what=f"DecodeStep graph={use_graph} step {it}")
+    assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref))

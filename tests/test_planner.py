@@ -1,0 +1,29 @@
+"""Host-side schedule planner (b2_paged_decode_plan_splits): pure host arithmetic, no GPU."""
+import torch
+
+import b200attn
+
+
+def plan(lens, Hq=32, Hkv=8):
+    return b200attn.plan_num_splits(torch.tensor(lens, dtype=torch.int32), Hq, Hkv)
+
+
+def test_uniform_large_batches_take_the_single_pass_grid():
+    assert plan([4096] * 64) == 1                 # BASELINE configs[1]: 512 items on 296 CTA slots
+    assert plan([8192] * 128) == 1                # configs[2]
+    assert plan([8192] * 256, 64, 8) == 1         # configs[3], tp = 1
+
+
+def test_small_or_skewed_batches_take_the_dynamic_schedule():
+    assert plan([512] * 4, 8, 2) == 0             # configs[0]: 8 items
+    assert plan([8192] * 256, 8, 1) == 0          # configs[3] at tp = 8: 256 items < 296 slots
+    assert plan([32768] + [200] * 63) == 0        # one long prompt among short ones
+    assert plan(list(range(100, 6500, 100))) == 0
+
+
+def test_bad_arguments():
+    import pytest
+    with pytest.raises(ValueError):
+        b200attn.plan_num_splits(torch.tensor([1, 2], dtype=torch.int64), 8, 2)
+    with pytest.raises(b200attn.B2Error):
+        b200attn.plan_num_splits(torch.tensor([1, 2], dtype=torch.int32), 7, 2)

@@ -7,3 +7,4 @@ from ._lib import B2Error, KV_BF16, KV_FP8_E4M3, LIB_PATH, load  # noqa: F401
 from .block_manager import BlockManager  # noqa: F401
 from .ops import (decode_auto_splits, decode_workspace_bytes, paged_decode,  # noqa: F401
                   plan_num_splits, reshape_and_cache)
+from .step import DecodeStep  # noqa: F401,E402

@@ -118,11 +118,16 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
     """out[b, hq] = softmax(scale * q[b, hq] . K[b, :seq_lens[b], hq // G]) . V[...]  -> bf16 [B, Hq, d].
 
     `workspace` is a uint8 device tensor of at least decode_workspace_bytes(...) bytes; one is
-    allocated per call when omitted (the engine passes a persistent one).  impl="simt" selects
+    allocated per call when omitted (the engine passes a persistent one).  `out` may be a pinned host tensor.  impl="simt" selects
     the CUDA-core A/B kernel."""
     lib = _lib.load()
+    # `out` may also be a PINNED host tensor: the kernels then store the result rows straight into host memory
+    # (unified addressing), which replaces the D2H copy of an engine step (b200attn.step.DecodeStep)
+    out_on_host = out is not None and not out.is_cuda
+    if out_on_host and not out.is_pinned():
+        raise ValueError("out must be a CUDA tensor or a pinned host tensor (b200attn has no CPU path)")
     dev = _need_cuda(q=q, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables, seq_lens=seq_lens,
-                     k_scale=k_scale, v_scale=v_scale, out=out, workspace=workspace)
+                     k_scale=k_scale, v_scale=v_scale, out=None if out_on_host else out, workspace=workspace)
     nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
     kvd = _kv_dtype_of(k_cache)
     if q.dtype != torch.bfloat16 or q.dim() != 3 or q.shape[2] != d:

@@ -7,28 +7,23 @@
 // come from reference benchmark-vllm/models.py:9,10,15.
 //
 // Design (HBM-bound gather):
-//   * Work unit = one KV block of one (sequence, kv head [, head group]) item.  The flattened unit
-//     space is cut into equal contiguous ranges, one per persistent CTA (2 CTAs per SM), so every
-//     CTA streams the same number of bytes regardless of batch size or ragged lengths ("stream-K"
-//     over the KV length).  A range is a list of segments (item, block range).
-//   * One CTA serves all G = Hq/Hkv query heads that share the kv head, so KV bytes are read once
-//     per kv head, not once per q head.
-//   * warp 4 is the producer: it walks the block table and issues one TMA tiled copy
-//     (cp.async.bulk.tensor.4d, 128-byte swizzle, L2 evict-first) per 16 x 64-element half tile
+//   * One CTA serves all G = Hq/Hkv query heads that share a kv head, so KV bytes are read once
+//     per kv head, not once per q head.  An "item" is one (sequence, kv head [, head group]).
+//   * warp 4 is the producer: it walks the block table and issues ONE TMA box per (block, head)
+//     tile and tensor (4 KiB bf16 / 2 KiB fp8, contiguous in HBM; 128-byte swizzle, L2 evict-first)
 //     into a ring of NSTAGE x 64-token stages; completion is counted in bytes on an mbarrier.
-//     The ring keeps running across segment boundaries.
 //   * warps 0-3 are consumers: each owns 16 tokens of every stage.  S^T = K.Q^T and
-//     O^T += V^T.P^T run on mma.sync m16n8k16 (tokens / head_dim on the M side, the <=8 grouped
+//     O^T += V^T.P^T run on mma.sync m16n8k16 (tokens / head_dim on the M side, the <= 8 grouped
 //     query heads on the N side, so no MMA row is wasted on padding tokens); ldmatrix(.trans)
 //     feeds the A operand straight from the swizzled stage; softmax is fp32 with warp shuffles;
-//     the P^T B-operand is produced from the S^T accumulator by movmatrix.
-//   * at a segment end the four consumers tree-merge their (m, l, O) through a small scratch
-//     area; a segment that covers its whole item writes bf16 output directly, otherwise a
-//     normalised partial + log2-sum-exp goes to one of the CTA's two workspace slots and
-//     `merge_boundary_kernel` (launched with programmatic dependent launch) combines the
-//     partials of the items that straddle a CTA boundary.
-//   * num_splits >= 1 selects the classic grid-split schedule (v1/v2 style, one CTA per
-//     (split, kv head, sequence)) built from the same producer/consumer code.
+//     the P^T B-operand is produced from the S^T accumulator by movmatrix (bf16 path: hi + lo).
+//   * schedule A (num_splits >= 1): the classic grid, one CTA per (split, item); 1 = single pass
+//     ("v1"), > 1 = split-K with an LSE merge kernel ("v2").
+//   * schedule B (num_splits = 0): persistent CTAs (2 per SM) over a fixed grid of chunks: a static
+//     contiguous share per CTA, then chunks claimed from an atomic counter so the grid drains
+//     together whatever the batch size or raggedness; partial runs are merged by
+//     merge_chunks_kernel (programmatic dependent launch).  Details above that kernel.
+//   * b2_paged_decode_plan_splits picks A(1) or B on the host from the scheduler's seq_lens.
 #include "b2_common.cuh"
 
 #include <stdlib.h>
@@ -41,7 +36,6 @@ constexpr int D = 128;        // head_dim (Llama-3 geometry)
 constexpr int NCW = 4;        // consumer warps
 constexpr int TOK = NCW * 16; // tokens per pipeline stage
 constexpr int NTHREADS = (NCW + 1) * 32;
-constexpr int MIN_TOK_PER_CTA = 128;   // persistent schedule: do not cut work finer than this
 constexpr float LOG2E = 1.4426950408889634f;
 
 // Optional per-CTA timeline (make trace -> lib/libb200attn_trace.so; scripts/trace_schedule.py reads it).
@@ -375,7 +369,12 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
     }
 
     // ------------------------------ online softmax ------------------------------
+    // bf16 carries 8 significant bits: a P rounded once to bf16 puts up to 2^-9 * |V| of error on an output built
+    // from a handful of tokens, which is outside the 2e-3 bar.  The bf16 path therefore feeds P as hi + lo
+    // (lo = bf16(P - hi)), two MMAs on the same V fragments; the f16 P of the fp8 path (11 bits) is rounded once.
+    constexpr bool PSPLIT = !FP8;
     uint32_t pb[NT][2];
+    uint32_t pl[PSPLIT ? NT : 1][2];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
         float pr[4];
@@ -403,6 +402,12 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
         const uint32_t x1 = FP8 ? pack_f16x2(pr[2], pr[3]) : b2::pack_bf16x2(pr[2], pr[3]);
         pb[nt][0] = b2::movmatrix_trans(x0);   // (tokens 2t4,2t4+1 ; head g)
         pb[nt][1] = b2::movmatrix_trans(x1);   // (tokens 8+2t4,.. ; head g)
+        if (PSPLIT) {
+            const uint32_t y0 = b2::pack_bf16x2(pr[0] - __uint_as_float(x0 << 16), pr[1] - __uint_as_float(x0 & 0xffff0000u));
+            const uint32_t y1 = b2::pack_bf16x2(pr[2] - __uint_as_float(x1 << 16), pr[3] - __uint_as_float(x1 & 0xffff0000u));
+            pl[nt][0] = b2::movmatrix_trans(y0);
+            pl[nt][1] = b2::movmatrix_trans(y1);
+        }
     }
 
     // ------------------------------ O^T += V^T . P^T -----------------------------
@@ -423,7 +428,10 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
             b2::ldmatrix_x4_trans(addr, a0, a1, a2, a3);
             a0 &= mk_lo; a1 &= mk_lo; a2 &= mk_hi; a3 &= mk_hi;
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) mma_kv<FP8>(acc.o[nt][dt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
+            for (int nt = 0; nt < NT; ++nt) {
+                mma_kv<FP8>(acc.o[nt][dt], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
+                if (PSPLIT) mma_kv<FP8>(acc.o[nt][dt], a0, a1, a2, a3, pl[nt][0], pl[nt][1]);
+            }
         }
     } else {
         // A 16-byte fp8 chunk holds 16 d values, so the b16 transpose moves (d 2g, d 2g+1) pairs: a thread
@@ -652,283 +660,7 @@ merge_splits_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ w
 }
 
 // =============================================================================================
-// schedule B (default): persistent CTAs over an equal partition of the flattened block space
-// =============================================================================================
-// Unit u of the flattened space: sequences in order, within a sequence the IPB = Hkv*HG items in order,
-// within an item its ceil(seq_len/BS) blocks in order.  CTA c of NC owns [c*U/NC, (c+1)*U/NC).
-struct Cursor {
-    int b;        // sequence
-    int j;        // item within the sequence (kvh*HG + hg)
-    int blk;      // block within the item
-};
-
-// Block-cooperative: total unit count U and, for `n_targets` unit indices given by target(U), their cursors.
-// Every thread returns the same values.  `part` is NT_+2 words of shared memory.
-template <int BS, int NT_>
-__device__ __forceinline__ uint32_t count_units(const int32_t* __restrict__ seq_lens, int B, int IPB,
-                                                uint32_t* part, uint32_t& my_local, uint32_t& my_pre, int& chunk) {
-    const int tid = threadIdx.x;
-    chunk = (B + NT_ - 1) / NT_;
-    uint32_t local = 0;
-    const int b0 = tid * chunk, b1 = min(B, b0 + chunk);
-    for (int b = b0; b < b1; ++b) local += (uint32_t)((seq_lens[b] + BS - 1) / BS) * IPB;
-    part[tid] = local;
-    __syncthreads();
-    if (tid < 32) {   // exclusive scan of NT_ partials, ceil(NT_/32) per lane
-        constexpr int PER = (NT_ + 31) / 32;
-        uint32_t v[PER], s = 0;
-#pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            const int idx = tid * PER + i;
-            v[i] = idx < NT_ ? part[idx] : 0;
-            s += v[i];
-        }
-        uint32_t incl = s;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
-            if (tid >= off) incl += t;
-        }
-        uint32_t run = incl - s;
-#pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            const int idx = tid * PER + i;
-            if (idx < NT_) part[idx] = run;
-            run += v[i];
-        }
-        if (tid == 31) part[NT_] = incl;
-    }
-    __syncthreads();
-    my_local = local;
-    my_pre = part[tid];
-    return part[NT_];
-}
-
-// The thread whose chunk contains unit u walks it and publishes the cursor through `res` (3 ints).
-template <int BS>
-__device__ __forceinline__ void locate_unit(uint32_t u, const int32_t* __restrict__ seq_lens, int B, int IPB,
-                                            uint32_t my_local, uint32_t my_pre, int chunk, int* res) {
-    if (u >= my_pre && u < my_pre + my_local) {
-        uint32_t acc = my_pre;
-        const int b0 = threadIdx.x * chunk, b1 = min(B, b0 + chunk);
-        for (int b = b0; b < b1; ++b) {
-            const uint32_t nb = (uint32_t)((seq_lens[b] + BS - 1) / BS);
-            const uint32_t span = nb * IPB;
-            if (u < acc + span) {
-                const uint32_t r = u - acc;
-                res[0] = b;
-                res[1] = (int)(r / nb);
-                res[2] = (int)(r % nb);
-                break;
-            }
-            acc += span;
-        }
-    }
-}
-
-__device__ __forceinline__ uint32_t range_begin(uint32_t c, uint32_t U, uint32_t NC) {
-    return (uint32_t)(((uint64_t)c * U) / NC);
-}
-__device__ __forceinline__ uint32_t effective_ctas(uint32_t U, uint32_t grid, int min_units) {
-    const uint32_t want = (U + min_units - 1) / min_units;
-    return want < grid ? (want ? want : 1u) : grid;
-}
-
-template <int BS, bool FP8, int NT, int NSTAGE>
-__global__ void __launch_bounds__(NTHREADS, 2)
-paged_decode_persistent_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                               const DecodeParams p) {
-    using C = Cfg<BS, FP8, NT, NSTAGE>;
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    // the unit search borrows the (not yet used) merge scratch: no static shared memory, so the
-    // dynamic region keeps its 1024-byte alignment without padding
-    uint32_t* s_part = reinterpret_cast<uint32_t*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
-    int* s_cur = reinterpret_cast<int*>(s_part + NTHREADS + 2);
-    static_assert((NTHREADS + 2 + 3) * 4 <= C::SCRATCH_BYTES, "unit search scratch");
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int c = blockIdx.x;
-    const int IPB = p.Hkv * p.HG;
-    if (tid == 0) B2_TRACE_AT(c, 0);
-    // let the boundary-merge kernel (programmatic dependent launch) get resident and run its own
-    // unit search while this grid streams; it blocks in griddepcontrol.wait until we are done
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-
-    // rows of empty sequences are defined here (no unit ever visits them)
-    for (int b = c; b < p.B; b += gridDim.x)
-        if (p.seq_lens[b] <= 0)
-            for (int i = tid; i < p.Hq * D; i += NTHREADS) p.out[b * p.out_stride + i] = __float2bfloat16(0.f);
-
-    uint32_t my_local, my_pre;
-    int chunk;
-    const uint32_t U = count_units<BS, NTHREADS>(p.seq_lens, p.B, IPB, s_part, my_local, my_pre, chunk);
-    const uint32_t NC = effective_ctas(U, gridDim.x, MIN_TOK_PER_CTA / BS);
-    if (U == 0 || (uint32_t)c >= NC) return;
-    const uint32_t u0 = range_begin(c, U, NC), u1 = range_begin(c + 1, U, NC);
-    if (u0 == u1) return;
-    locate_unit<BS>(u0, p.seq_lens, p.B, IPB, my_local, my_pre, chunk, s_cur);
-
-    const uint32_t ring = b2::smem_u32(smem_raw);
-    if (ring & 1023u) __trap();
-    const uint32_t bar_full = ring + C::RING_BYTES;
-    const uint32_t bar_empty = bar_full + NSTAGE * 8;
-    float* scratch = reinterpret_cast<float*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
-    init_pipeline(bar_full, bar_empty, NSTAGE, tid);   // also publishes s_cur
-
-    Cursor cur{s_cur[0], s_cur[1], s_cur[2]};
-    uint32_t remaining = u1 - u0;
-    uint32_t it = 0;
-    if (tid == 0) B2_TRACE_AT(c, 1);
-
-    if (warp == NCW) {
-        // ================================ producer warp =====================================
-        if (lane == 0) {
-            b2::tma_prefetch_desc(&tmK);
-            b2::tma_prefetch_desc(&tmV);
-        }
-        const uint64_t pol = b2::policy_evict_first();
-        while (remaining) {
-            const int nb = (p.seq_lens[cur.b] + BS - 1) / BS;
-            if (nb == 0) { ++cur.b; cur.j = 0; cur.blk = 0; continue; }
-            const int take = min((uint32_t)(nb - cur.blk), remaining);
-            produce_segment<C, NSTAGE>(&tmK, &tmV, p.block_tables + (int64_t)cur.b * p.max_nb + cur.blk, take,
-                                       cur.j / p.HG, ring, bar_full, bar_empty, it, lane, pol);
-            remaining -= take;
-            cur.blk += take;
-            if (cur.blk == nb) { cur.blk = 0; if (++cur.j == IPB) { cur.j = 0; ++cur.b; } }
-        }
-    } else {
-        // ================================ consumer warps ====================================
-        float sl2 = p.scale_log2, vs = 1.f;
-        if (FP8) {
-            sl2 *= *p.k_scale;
-            vs = *p.v_scale;
-        }
-        WarpAcc<NT> acc;
-        bool first = true;
-        while (remaining) {
-            const int seq_len = p.seq_lens[cur.b];
-            const int nb = (seq_len + BS - 1) / BS;
-            if (nb == 0) { ++cur.b; cur.j = 0; cur.blk = 0; continue; }
-            const int take = min((uint32_t)(nb - cur.blk), remaining);
-            const int kvh = cur.j / p.HG, hg = cur.j - kvh * p.HG;
-            const int head0 = kvh * p.G + hg * C::HEADS;
-            const int nheads = min(C::HEADS, p.G - hg * C::HEADS);
-            const int n_tok = min(seq_len, (cur.blk + take) * BS) - cur.blk * BS;
-
-            uint32_t qf[NT][8][2];
-            load_q_frags<FP8, NT>(qf, p.q + cur.b * p.q_stride + (int64_t)head0 * D, nheads, lane);
-            acc.reset();
-            consume_segment<C, FP8, NT, NSTAGE>(acc, qf, n_tok, ring, bar_full, bar_empty, it, sl2, warp, lane);
-            merge_warps<NT>(acc, scratch, C::SLOT_FLOATS, sl2, warp, lane);
-            if (warp == 0) {
-                const bool whole = cur.blk == 0 && take == nb;
-                if (whole) {
-                    write_result<FP8, NT>(acc, nheads, vs, sl2, p.out + cur.b * p.out_stride + (int64_t)head0 * D,
-                                          nullptr, nullptr, lane);
-                } else {
-                    // a partial segment is either the first or the last segment of this CTA
-                    const int64_t slot = (int64_t)c * 2 + (first ? 0 : 1);
-                    write_result<FP8, NT>(acc, nheads, vs, sl2, nullptr, p.ws_o + slot * (C::HEADS * D),
-                                          p.ws_lse + slot * C::HEADS, lane);
-                }
-            }
-            first = false;
-            remaining -= take;
-            cur.blk += take;
-            if (cur.blk == nb) { cur.blk = 0; if (++cur.j == IPB) { cur.j = 0; ++cur.b; } }
-        }
-        if (warp == 0) B2_TRACE_AT(c, 3);
-    }
-}
-
-// Items that straddle a CTA boundary: block c (one per boundary c | c+1) merges the item that crosses its
-// boundary if that item did not already cross the previous one (then an earlier block owns it).
-template <int BS, int HEADS>
-__global__ void __launch_bounds__(128)
-merge_boundary_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ ws_o,
-                      const float* __restrict__ ws_lse, const int32_t* __restrict__ seq_lens, int B, int Hkv, int G,
-                      int HG, int64_t out_stride, uint32_t grid_main) {
-    __shared__ uint32_t s_part[128 + 2];
-    __shared__ int s_cur[3];
-    const int tid = threadIdx.x;
-    const uint32_t c = blockIdx.x;
-    const int IPB = Hkv * HG;
-    uint32_t my_local, my_pre;
-    int chunk;
-    const uint32_t U = count_units<BS, 128>(seq_lens, B, IPB, s_part, my_local, my_pre, chunk);
-    const uint32_t NC = effective_ctas(U, grid_main, MIN_TOK_PER_CTA / BS);
-    if (U == 0 || c + 1 >= NC) return;
-    const uint32_t ub = range_begin(c + 1, U, NC);       // the boundary between CTA c and c+1
-    if (ub == 0 || ub >= U) return;
-    locate_unit<BS>(ub, seq_lens, B, IPB, my_local, my_pre, chunk, s_cur);
-    __syncthreads();
-    const int b = s_cur[0], j = s_cur[1], blk = s_cur[2];
-    if (blk == 0) return;                                // the boundary falls between two items
-    const int nb = (seq_lens[b] + BS - 1) / BS;
-    const uint32_t s_i = ub - blk, e_i = s_i + nb;       // the item's unit range
-    if (s_i < range_begin(c, U, NC)) return;             // it also crossed c-1 | c: block c_first owns it
-    // wait for the decode kernel's partials (programmatic dependent launch)
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    const uint32_t c_last = (uint32_t)((((uint64_t)e_i * NC) - 1) / U);
-    const int kvh = j / HG, hg = j - kvh * HG;
-    const int head0 = kvh * G + hg * HEADS;
-    const int nheads = min(HEADS, G - hg * HEADS);
-    // thread -> (head tid/16 [+8], 8 consecutive d); every load of a pass is independent, so the whole
-    // merge costs about one L2 round trip.  Partials are combined online, MAXC CTAs at a time.
-    constexpr int MAXC = 4;
-    const int dc = (tid & 15) * 8;
-    for (int h = tid >> 4; h < nheads; h += 8) {
-        float m_run = -INFINITY, den = 0.f, num[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) num[i] = 0.f;
-        for (uint32_t cb = c; cb <= c_last; cb += MAXC) {
-            float lse[MAXC];
-            float4 o0[MAXC], o1[MAXC];
-#pragma unroll
-            for (int i = 0; i < MAXC; ++i) {
-                const uint32_t cc = cb + i;
-                lse[i] = -INFINITY;
-                o0[i] = o1[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (cc <= c_last) {
-                    const int64_t slot = (int64_t)cc * 2 + (range_begin(cc, U, NC) >= s_i ? 0 : 1);
-                    lse[i] = ws_lse[slot * HEADS + h];
-                    const float4* po = reinterpret_cast<const float4*>(ws_o + (slot * HEADS + h) * D + dc);
-                    o0[i] = po[0];
-                    o1[i] = po[1];
-                }
-            }
-            float mx = m_run;
-#pragma unroll
-            for (int i = 0; i < MAXC; ++i) mx = fmaxf(mx, lse[i]);
-            if (mx == -INFINITY) continue;
-            const float a = m_run == -INFINITY ? 0.f : exp2f(m_run - mx);
-            den *= a;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) num[i] *= a;
-#pragma unroll
-            for (int i = 0; i < MAXC; ++i) {
-                const float w = lse[i] == -INFINITY ? 0.f : exp2f(lse[i] - mx);
-                den += w;
-                num[0] = fmaf(w, o0[i].x, num[0]); num[1] = fmaf(w, o0[i].y, num[1]);
-                num[2] = fmaf(w, o0[i].z, num[2]); num[3] = fmaf(w, o0[i].w, num[3]);
-                num[4] = fmaf(w, o1[i].x, num[4]); num[5] = fmaf(w, o1[i].y, num[5]);
-                num[6] = fmaf(w, o1[i].z, num[6]); num[7] = fmaf(w, o1[i].w, num[7]);
-            }
-            m_run = mx;
-        }
-        const float inv = den > 0.f ? 1.f / den : 0.f;
-        uint4 pk;
-        pk.x = b2::pack_bf16x2(num[0] * inv, num[1] * inv);
-        pk.y = b2::pack_bf16x2(num[2] * inv, num[3] * inv);
-        pk.z = b2::pack_bf16x2(num[4] * inv, num[5] * inv);
-        pk.w = b2::pack_bf16x2(num[6] * inv, num[7] * inv);
-        *reinterpret_cast<uint4*>(out + b * out_stride + (int64_t)(head0 + h) * D + dc) = pk;
-    }
-}
-
-// =============================================================================================
-// schedule C (default, num_splits = 0): persistent CTAs, a static head + dynamically claimed chunks
+// schedule B (default, num_splits = 0): persistent CTAs, a static head + dynamically claimed chunks
 // =============================================================================================
 // Work is cut on a fixed grid: item (b, j) has nck(b) = ceil(seq_len / CT) chunks of CT tokens (CT a
 // multiple of the 64-token stage).  Chunk ids are flattened sequence-major, then item, then chunk.
@@ -1411,7 +1143,6 @@ struct Plan {
     int hg;            // head groups per kv head
     int num_splits;    // 0 = persistent schedule
     int split_tokens;
-    bool dynamic;      // persistent: dynamic claims (default) or the static equal split (B2_SCHEDULE=static)
     int chunk_tokens;  // dynamic: claim granularity
     int static_pct;    // dynamic: share of the chunks dealt out statically
     int64_t slots;     // dynamic: partial slots in the workspace
@@ -1432,17 +1163,13 @@ void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_spli
     pl->hg = (G + hpc - 1) / hpc;
     pl->num_splits = 0;
     pl->split_tokens = 0;
-    pl->dynamic = false;
     pl->chunk_tokens = 0;
     pl->static_pct = 0;
     pl->slots = 0;
     pl->ipb = Hkv * pl->hg;
     const int64_t max_ctx = (int64_t)max_nb * bs;
     if (num_splits <= 0) {
-        // diagnostic overrides, read once per call (cheap): B2_SCHEDULE=static|dynamic, B2_CHUNK_TOKENS, B2_STATIC_PCT
-        const char* sch = getenv("B2_SCHEDULE");
-        pl->dynamic = !(sch && sch[0] == 's');
-        if (!pl->dynamic) return;
+        // diagnostic overrides, read per call (cheap): B2_CHUNK_TOKENS, B2_STATIC_PCT
         const int NC = persistent_grid();
         const int ipb = Hkv * pl->hg;
         const int ct_max = bs * 32 < 512 ? bs * 32 : 512;   // <= 32 blocks per chunk
@@ -1469,8 +1196,7 @@ void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_spli
 
 size_t plan_workspace(const Plan& pl, int B, int Hq) {
     if (pl.num_splits == 0) {
-        if (pl.dynamic) return ws_header_bytes(B, pl.ipb) + (size_t)pl.slots * (8 * pl.nt) * (D + 1) * sizeof(float);
-        return (size_t)persistent_grid() * 2 * (8 * pl.nt) * (D + 1) * sizeof(float);
+        return ws_header_bytes(B, pl.ipb) + (size_t)pl.slots * (8 * pl.nt) * (D + 1) * sizeof(float);
     }
     if (pl.num_splits == 1) return 0;
     return (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
@@ -1481,7 +1207,7 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
                   cudaStream_t st) {
     constexpr int NSTAGE = FP8 ? 6 : 3;
     using C = Cfg<BS, FP8, NT, NSTAGE>;
-    if (pl.num_splits == 0 && pl.dynamic) {
+    if (pl.num_splits == 0) {
         constexpr int NSTAGE_D = FP8 ? 5 : 3;   // fp8: one 16 KiB stage gives way to the per-stage q buffers
         using C = Cfg<BS, FP8, NT, NSTAGE_D>;
         auto kern = paged_decode_dynamic_kernel<BS, FP8, NT, NSTAGE_D>;
@@ -1513,31 +1239,6 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         B2_CUDA_OK(cudaLaunchKernelEx(&cfg2, merge_chunks_kernel<8 * NT>, p.out, (const float*)p.ws_o,
                                       (const float*)p.ws_lse, p.seq_lens, p.B, p.Hkv, p.G, p.HG, p.out_stride,
                                       p.chunk_tokens, p.static_pct, (uint32_t)grid));
-        return B2_OK;
-    }
-    if (pl.num_splits == 0) {
-        auto kern = paged_decode_persistent_kernel<BS, FP8, NT, NSTAGE>;
-        static bool attr_set = false;   // per instantiation; idempotent, so a race is harmless
-        if (!attr_set) {
-            B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-            attr_set = true;
-        }
-        const int grid = persistent_grid();
-        kern<<<grid, NTHREADS, C::SMEM_BYTES, st>>>(tmK, tmV, p);
-        B2_CUDA_OK(cudaGetLastError());
-        // boundary merge, launched early (PDL): its unit search overlaps the decode kernel's tail
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(grid);
-        cfg.blockDim = dim3(128);
-        cfg.stream = st;
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = at;
-        cfg.numAttrs = 1;
-        B2_CUDA_OK(cudaLaunchKernelEx(&cfg, merge_boundary_kernel<BS, 8 * NT>, p.out, (const float*)p.ws_o,
-                                      (const float*)p.ws_lse, p.seq_lens, p.B, p.Hkv, p.G, p.HG, p.out_stride,
-                                      (uint32_t)grid));
         return B2_OK;
     }
     auto kern = paged_decode_split_kernel<BS, FP8, NT, NSTAGE>;
@@ -1673,7 +1374,7 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
                    "paged_decode: workspace %zu bytes < required %zu", workspace_bytes, need);
         size_t body = need;
         char* base = static_cast<char*>(workspace);
-        if (pl.num_splits == 0 && pl.dynamic) {
+        if (pl.num_splits == 0) {
             B2_REQUIRE(pl.slots < (1LL << 27), B2_EUNSUPPORTED, "paged_decode: %lld partial slots", (long long)pl.slots);
             p.counter = reinterpret_cast<uint32_t*>(base);
             base += ws_header_bytes(B, pl.ipb);
