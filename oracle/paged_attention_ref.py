@@ -1,6 +1,6 @@
 """CPU oracle for the paged-attention decode hot path.  TEST INFRASTRUCTURE ONLY.
 
-    *** parity unpinned ***
+    *** parity: unpinned by the reference, pinned against its dependency ***
     The reference (ThakiCloud/vllm-backend-public) contains no implementation, test,
     golden vector or fixture for this path: the arithmetic lives in the third-party
     vLLM server image it launches (`vllm/vllm-openai:v0.9.1`,
@@ -12,6 +12,12 @@
     that shape it do come from the reference: `block_size` (benchmark-vllm/models.py:10),
     `max_num_seqs` / `max_model_len` (models.py:9,15), `tensor_parallel_size`
     (models.py:11), `dtype` (models.py:14).
+    What pins it: outputs of vLLM's own CUDA kernels (`reshape_and_cache`,
+    `paged_attention_v1/_v2`; the vllm 0.22.0 wheel of the image, run on a B200 by
+    tests/golden/make_vllm_crosscheck.py) committed as tests/golden/vllm_crosscheck.pt --
+    the KV write (bf16 and fp8-e4m3) is bit-identical, decode agrees within
+    4e-3 + 1e-2|ref| (vLLM rounds softmax weights to the cache dtype); see
+    tests/test_vllm_crosscheck.py.  That wheel is not the reference's pinned v0.9.1 image.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
 may import this module -- as the checker or the timed CPU baseline, never as a product

@@ -356,3 +356,33 @@ def test_decode_step_from_host_buffers(cuda, use_graph):
         ref = R.paged_decode_ref(q, kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
         assert_close(out, ref, what=f"DecodeStep graph={use_graph} step {it}")
     assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref))
+
+
+# ------------------------------------------------------------------------------------------
+# our kernels against vLLM's own kernels' outputs (committed fixture; see tests/test_vllm_crosscheck.py)
+# ------------------------------------------------------------------------------------------
+def _vllm_cases():
+    p = GOLDEN / "vllm_crosscheck.pt"
+    return torch.load(p) if p.exists() else {}
+
+
+@pytest.mark.parametrize("name", sorted(_vllm_cases()))
+def test_kernels_match_vllm_fixture(cuda, name):
+    import hashlib
+    r = _vllm_cases()[name]
+    kw, fp8 = r["make_inputs"], r["fp8"]
+    inp = R.make_inputs(**kw)
+    shape = (inp["num_blocks"], kw["Hkv"], kw["bs"], kw["d"])
+    kc = torch.zeros(shape, dtype=torch.uint8 if fp8 else torch.bfloat16, device=cuda)
+    vc = torch.zeros_like(kc)
+    ksd = vsd = None
+    if fp8:
+        ksd = torch.tensor([r["k_scale"]], dtype=torch.float32, device=cuda)
+        vsd = torch.tensor([r["v_scale"]], dtype=torch.float32, device=cuda)
+    b200attn.reshape_and_cache(inp["k"].to(cuda), inp["v"].to(cuda), kc, vc, inp["slot_mapping"].to(cuda), ksd, vsd)
+    sha = lambda t: hashlib.sha256(bits(t).numpy().tobytes()).hexdigest()  # noqa: E731
+    assert sha(kc) == r["k_cache_sha"] and sha(vc) == r["v_cache_sha"], "KV write differs from vLLM's bits"
+    for splits in (0, 1):
+        out = b200attn.paged_decode(inp["q"].to(cuda), kc, vc, inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda),
+                                    k_scale=ksd, v_scale=vsd, num_splits=splits)
+        assert_close(out, r["out_v1"].float(), atol=4e-3, rtol=1e-2, what=f"{name} vs vLLM v1 (splits {splits})")
