@@ -259,8 +259,11 @@ def run_ours(args, wl_name, wl):
     if wl["Hkv"] % tp:
         raise SystemExit(f"Hkv={wl['Hkv']} is not divisible by tp={tp}")
     # KV-head sharding, weak scaling: rank r owns kv heads [r*Hkv/tp, (r+1)*Hkv/tp) of a batch of B*tp sequences
-    B = wl["B"] * tp
-    Hq_l, Hkv_l = wl["Hq"] // tp, wl["Hkv"] // tp
+    # (--strong keeps the batch fixed instead: BASELINE configs[3], B = 256 sharded over tp = 2/4/8)
+    from b200attn import parallel
+    shard = parallel.HeadShard(tp, rank, wl["Hq"], wl["Hkv"])
+    B = wl["B"] if args.strong else wl["B"] * tp
+    Hq_l, Hkv_l = shard.Hq_local, shard.Hkv_local
     ctx, fp8 = wl["ctx"], wl["fp8"]
     kv_bytes = 1 if fp8 else 2
     prob = build_problem(dev, B, Hq_l, Hkv_l, ctx, fp8, seed=rank)
@@ -359,6 +362,23 @@ def run_ours(args, wl_name, wl):
     e2e_ms = float(t[0])
     e2e_value = bytes_rank * world / (e2e_ms * 1e-3) / 1e9
 
+    # optional consumer-side all-gather of the head-sharded output (off the attention path; reported, not in `value`)
+    allgather_us = None
+    if dist is not None:
+        for _ in range(3):
+            parallel.gather_heads(out, shard)
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        g0.record(stream)
+        for _ in range(20):
+            full = parallel.gather_heads(out, shard)
+        g1.record(stream)
+        barrier()
+        assert full.shape == (B, wl["Hq"], D)
+        tg = torch.tensor([g0.elapsed_time(g1) / 20 * 1e3], dtype=torch.float64, device=dev)
+        dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+        allgather_us = round(float(tg[0]), 2)
+
     if rank == 0:
         peak, peak_src = measured_peak()
         achieved = bytes_rank / (dec_mean_ms * 1e-3) / 1e9
@@ -371,11 +391,13 @@ def run_ours(args, wl_name, wl):
                 traffic = None
         line = {
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
-            "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "strong" if args.strong else "weak", "vs_baseline": None,
             "dtype": "bf16" if not fp8 else "fp8_e4m3 KV / bf16 q,out (fp32 accumulate)", "data": "synthetic",
             "config": {"workload": wl_name, "global_batch": B, "ctx": ctx, "Hq": wl["Hq"], "Hkv": wl["Hkv"], "d": D,
                        "block_size": BS, "kv_dtype": "fp8_e4m3" if fp8 else "bf16",
                        "parallelism": f"kv-head-shard tp{tp}" if tp > 1 else "1 GPU",
+                       "collective": "none on the attention path" + (f"; optional NCCL all-gather of out [B, Hq, d]: {allgather_us} us"
+                                                                      if allgather_us is not None else ""),
                        "per_gpu": {"B": B, "Hq": Hq_l, "Hkv": Hkv_l}, "num_splits": used_splits,
                        "schedule": schedule, "schedule_chosen_by": schedule_src,
                        "step": "reshape_and_cache(1 new token/seq) + paged_decode, one layer",
@@ -418,6 +440,7 @@ def main():
     ap.add_argument("--splits", type=int, default=-1,
                     help="num_splits for b2_paged_decode: -1 = host planner (default), 0 = dynamic persistent, 1 = single pass")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--strong", action="store_true", help="N > 1: keep the global batch fixed (strong scaling)")
     ap.add_argument("--batch", type=int, default=0, help="override the workload batch size (experiments only)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])

@@ -158,6 +158,61 @@ B2_API int     b2_bm_plan_decode(b2_block_manager* bm, const int64_t* seq_ids, i
                           int32_t* block_tables_out, int max_nb, int32_t* seq_lens_out,
                           int64_t* slot_mapping_out);
 
+/* ---------------------------------------------------------------------------------------------
+ * Continuous-batching scheduler (host only): the caller of the hot path.
+ * It owns a block manager and turns a stream of requests into per-step plans under the limits of the
+ * reference's launch contract: max_num_seqs (models.py:9), max_model_len (:15), block_size (:10), the block
+ * pool sized from gpu_memory_utilization (:8), plus a per-step token budget for chunked prefill.
+ *
+ * Policy (vLLM-style, decode first): every running sequence decodes one token per step; when the pool cannot
+ * hold the step, the most recently admitted running sequence is preempted (its blocks are freed and it goes back
+ * to the head of the waiting queue to be recomputed, prompt + tokens generated so far); then waiting requests are
+ * admitted first-come-first-served and prefilled in chunks within the remaining token budget.
+ *
+ * A request holds P prompt tokens and may generate up to max_new_tokens.  After its last prefill chunk the model
+ * samples output token #1; each decode step writes the previously sampled token into the cache (one slot),
+ * attends over seq_len tokens and samples the next one.  The request finishes by itself when it has sampled
+ * max_new_tokens or reached max_model_len; b2_sched_finish ends it earlier (EOS / abort).
+ * b2_sched_step assumes the previous plan was executed.  All plan pointers are host memory owned by the
+ * scheduler, valid until the next b2_sched_step / b2_sched_destroy.  Single-writer, like the block manager.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b2_scheduler b2_scheduler;
+
+typedef struct b2_step_plan {
+    /* decode part: one new token for each of n_decode running sequences */
+    int            n_decode;
+    int            max_nb;              /* row length of the block tables */
+    const int64_t* decode_ids;          /* [n_decode] request ids, batch row order */
+    const int32_t* block_tables;        /* [n_decode, max_nb] */
+    const int32_t* seq_lens;            /* [n_decode] tokens that attend, including the one written this step */
+    const int64_t* slot_mapping;        /* [n_decode] slot of the token written this step */
+    /* prefill part: n_prefill chunks, n_prefill_tokens tokens in total, chunk after chunk */
+    int            n_prefill;
+    int            n_prefill_tokens;
+    const int64_t* prefill_ids;         /* [n_prefill] */
+    const int32_t* prefill_start;       /* [n_prefill] position of the chunk's first token in its sequence */
+    const int32_t* prefill_len;         /* [n_prefill] tokens in the chunk */
+    const uint8_t* prefill_last;        /* [n_prefill] 1 = the prompt is complete after this chunk: sample token #1 */
+    const int64_t* prefill_slots;       /* [n_prefill_tokens] */
+    const int32_t* prefill_block_tables;/* [n_prefill, max_nb] tables covering start + len tokens */
+    /* bookkeeping the engine must mirror */
+    int            n_preempted;
+    const int64_t* preempted_ids;       /* recompute later: their KV is gone */
+    int            n_finished;
+    const int64_t* finished_ids;        /* finished by length after the PREVIOUS plan; their blocks are free again */
+} b2_step_plan;
+
+B2_API b2_scheduler* b2_sched_create(int64_t num_blocks, int bs, int max_num_seqs, int max_model_len,
+                              int max_num_batched_tokens);                         /* NULL on bad args */
+B2_API void    b2_sched_destroy(b2_scheduler* s);
+B2_API int     b2_sched_add_request(b2_scheduler* s, int64_t req_id, int prompt_len, int max_new_tokens);
+B2_API int     b2_sched_finish(b2_scheduler* s, int64_t req_id);                          /* EOS / abort */
+B2_API int     b2_sched_step(b2_scheduler* s, b2_step_plan* plan);
+B2_API int64_t b2_sched_num_waiting(const b2_scheduler* s);
+B2_API int64_t b2_sched_num_running(const b2_scheduler* s);
+B2_API int64_t b2_sched_num_free_blocks(const b2_scheduler* s);
+B2_API int64_t b2_sched_generated(const b2_scheduler* s, int64_t req_id);   /* tokens sampled so far; < 0 unknown */
+
 #ifdef __cplusplus
 }
 #endif
