@@ -8,3 +8,4 @@ from .block_manager import BlockManager  # noqa: F401
 from .ops import (decode_auto_splits, decode_workspace_bytes, paged_decode,  # noqa: F401
                   plan_num_splits, reshape_and_cache)
 from .step import DecodeStep  # noqa: F401,E402
+from .scheduler import Scheduler, StepPlan  # noqa: F401,E402

@@ -52,6 +52,15 @@ SIGNATURES = {
     "b2_bm_free_seq": (i32, [vp, i64]),
     "b2_bm_fill_tables": (i32, [vp, vp, i32, vp, i32, vp]),
     "b2_bm_plan_decode": (i32, [vp, vp, i32, vp, i32, vp, vp]),
+    "b2_sched_create": (vp, [i64, i32, i32, i32, i32]),
+    "b2_sched_destroy": (None, [vp]),
+    "b2_sched_add_request": (i32, [vp, i64, i32, i32]),
+    "b2_sched_finish": (i32, [vp, i64]),
+    "b2_sched_step": (i32, [vp, vp]),
+    "b2_sched_num_waiting": (i64, [vp]),
+    "b2_sched_num_running": (i64, [vp]),
+    "b2_sched_num_free_blocks": (i64, [vp]),
+    "b2_sched_generated": (i64, [vp, i64]),
 }
 
 _lib = None
