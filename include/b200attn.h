@@ -131,6 +131,58 @@ B2_API int b2_paged_decode_simt(void* out, const void* q,
                          void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Prompt-chunk (prefill) attention over the paged cache.  Replaces vLLM's
+ * chunked-prefill / prefix attention (flash_attn_varlen_func with a block table, `context_attention_fwd`) in the
+ * engine behind the reference's launch contract; chunk sizes follow the scheduler's token budget, table rows
+ * max_nb = ceil(max_model_len / block_size) (reference benchmark-vllm/models.py:15,10).
+ *   chunk c = token rows [cu_q[c], cu_q[c+1]) of q / out; its tokens sit at positions ctx_start[c] + i of their
+ *   sequence, whose blocks are block_tables[c][:].  The chunk's own K/V must already be in the cache
+ *   (b2_rope_and_cache / b2_reshape_and_cache run first).
+ *   out[t][hq] = softmax_{j <= ctx_start[c] + i}(scale * <q[t][hq], K[c][j][hq / G]>) . V[c][j][hq / G]
+ *   fp32 softmax / accumulation, softmax weights rounded to bf16 for the P.V product, out rounded to bf16 once.
+ * T = cu_q[n_chunks] (host knowledge: it sizes the grid).  cu_q, ctx_start, block_tables: DEVICE int32.
+ * kv_dtype: B2_KV_BF16 only (B2_EUNSUPPORTED otherwise; fp8 KV is a decode-side format here).
+ * ------------------------------------------------------------------------------------------- */
+B2_API int b2_prefill_attention(void* out, const void* q, const void* k_cache, const void* v_cache,
+                         const int32_t* block_tables, const int32_t* cu_q, const int32_t* ctx_start,
+                         int n_chunks, int T, int Hq, int Hkv, int d, int bs, int max_nb,
+                         int64_t num_blocks, int64_t q_stride, int64_t out_stride,
+                         int64_t cache_block_stride, int64_t cache_head_stride,
+                         float scale, int kv_dtype, const float* k_scale, const float* v_scale,
+                         void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Element-wise ops of one decoder layer around the attention path: what the
+ * launched engine runs between its GEMMs.  bf16 activations (VLLMConfig.dtype, reference
+ * benchmark-vllm/models.py:14), fp32 math, one rounding on the way out; strides in elements.
+ *
+ * b2_rms_norm        residual == NULL: out = bf16(w * x * rsqrt(mean(x^2) + eps))
+ *                    else: h = bf16(x + residual) is written to residual, then normalised (vLLM
+ *                    fused_add_rms_norm).  out may alias x.
+ * b2_silu_and_mul    out[t][i] = silu(gate_up[t][i]) * gate_up[t][I + i]          (vLLM silu_and_mul)
+ * b2_rope_and_cache  qkv [T, (Hq + 2 Hkv) * d] = q | k | v per token.  Neox rotary (pairs i, i + d/2) with
+ *                    cos_sin fp32 [max_pos, d] (cos[0..d/2) | sin[0..d/2) per position) applied to q and k IN
+ *                    PLACE: x1' = bf16(x1*cos - x2*sin), x2' = bf16(x2*cos + x1*sin) (products and sum each
+ *                    rounded in fp32, no fma); then k', v go to the paged cache through slot_mapping exactly as
+ *                    b2_reshape_and_cache does (slot < 0: rotated in place, not cached).
+ *                    (vLLM rotary_embedding + reshape_and_cache in one pass over qkv.)
+ * b2_sample          tokens[b] = argmax_i logits[b][i] when temperature == NULL or temperature[b] <= 0 (lowest
+ *                    index among equal maxima); else argmax_i (logits[b][i] / T_b + g_i), g_i = -log(-log(u_i)),
+ *                    u_i = (hash24(seeds[b], i) + 0.5) / 2^24 with the splitmix64 finaliser (Gumbel-max = one
+ *                    draw from softmax(logits / T)).  logits bf16 [B, V], row stride given.
+ * ------------------------------------------------------------------------------------------- */
+B2_API int b2_rms_norm(void* out, const void* x, void* residual, const void* weight, int T, int H,
+                int64_t x_stride, int64_t out_stride, int64_t res_stride, float eps, void* stream);
+B2_API int b2_silu_and_mul(void* out, const void* gate_up, int T, int I, int64_t in_stride, int64_t out_stride,
+                    void* stream);
+B2_API int b2_rope_and_cache(void* qkv, const int32_t* positions, const float* cos_sin, int max_pos,
+                      void* k_cache, void* v_cache, const int64_t* slot_mapping, int T, int Hq, int Hkv,
+                      int d, int bs, int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
+                      int kv_dtype, const float* k_scale, const float* v_scale, void* stream);
+B2_API int b2_sample(int64_t* tokens, const void* logits, int B, int V, int64_t stride, const float* temperature,
+              const int64_t* seeds, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Block manager (host only): the page allocator that produces block_tables / seq_lens /
  * slot_mapping each step.  Pool size follows VLLMConfig.gpu_memory_utilization and block_size
  * (models.py:8,10); per-sequence capacity follows max_model_len (models.py:15).

@@ -174,3 +174,144 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
         B, Hq, Hkv, d, bs, max_nb, nb, qs, os_, bstride, hstride, float(scale), kvd,
         _ptr(k_scale), _ptr(v_scale), _ptr(workspace), wbytes, num_splits, _stream(dev)))
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# prompt-chunk attention and the element-wise ops of a decoder layer
+# ------------------------------------------------------------------------------------------------
+def prefill_attention(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_tables: torch.Tensor,
+                      cu_q: torch.Tensor, ctx_start: torch.Tensor, total_tokens: Optional[int] = None,
+                      scale: Optional[float] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Causal attention of prompt chunks over the paged cache (b2_prefill_attention).
+
+    q / out: bf16 [T, Hq, d] (token stride allowed); chunk c = rows cu_q[c]:cu_q[c+1], positions
+    ctx_start[c] + i, blocks block_tables[c].  The chunk's K/V must already be in the cache.
+    `total_tokens` = cu_q[-1] as a host int (defaults to q.shape[0]; it sizes the grid without a device sync)."""
+    lib = _lib.load()
+    dev = _need_cuda(q=q, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables, cu_q=cu_q,
+                     ctx_start=ctx_start, out=out)
+    nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+    kvd = _kv_dtype_of(k_cache)
+    if q.dtype != torch.bfloat16 or q.dim() != 3 or q.shape[2] != d or q.stride(2) != 1 or q.stride(1) != d:
+        raise ValueError(f"q must be bf16 [T, Hq, {d}] with contiguous head/dim axes")
+    T, Hq, _ = q.shape
+    n_chunks = ctx_start.numel()
+    for name, t, n in (("cu_q", cu_q, n_chunks + 1), ("ctx_start", ctx_start, n_chunks)):
+        if t.dtype != torch.int32 or t.shape != (n,) or not t.is_contiguous():
+            raise ValueError(f"{name} must be a contiguous int32 [{n}]")
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != n_chunks \
+            or not block_tables.is_contiguous():
+        raise ValueError("block_tables must be a contiguous int32 [n_chunks, max_nb]")
+    if out is None:
+        out = torch.empty(T, Hq, d, dtype=torch.bfloat16, device=dev)
+    elif out.dtype != torch.bfloat16 or out.shape != (T, Hq, d) or out.stride(2) != 1 or out.stride(1) != d:
+        raise ValueError("out must be bf16 [T, Hq, d] with contiguous head/dim axes")
+    if total_tokens is None:
+        total_tokens = T
+    if not 0 <= total_tokens <= T:
+        raise ValueError(f"total_tokens={total_tokens} outside [0, {T}]")
+    if scale is None:
+        scale = 1.0 / math.sqrt(d)
+    if n_chunks == 0 or total_tokens == 0:
+        return out
+    _lib.check(lib.b2_prefill_attention(
+        _ptr(out), _ptr(q), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(cu_q), _ptr(ctx_start),
+        n_chunks, total_tokens, Hq, Hkv, d, bs, block_tables.shape[1], nb,
+        q.stride(0) if T > 1 else Hq * d, out.stride(0) if T > 1 else Hq * d, bstride, hstride,
+        float(scale), kvd, None, None, _stream(dev)))
+    return out
+
+
+def _rows(t: torch.Tensor, name: str):
+    if t.dtype != torch.bfloat16 or t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name} must be bf16 [T, H] with a contiguous last axis")
+    return t.shape[0], t.shape[1], (t.stride(0) if t.shape[0] > 1 else t.shape[1])
+
+
+def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None,
+             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out = bf16(w * h * rsqrt(mean(h^2) + eps)); with `residual`, h = bf16(x + residual) is stored back into
+    residual first (fused add).  b2_rms_norm."""
+    lib = _lib.load()
+    dev = _need_cuda(x=x, weight=weight, residual=residual, out=out)
+    T, H, xs = _rows(x, "x")
+    if weight.dtype != torch.bfloat16 or weight.shape != (H,) or not weight.is_contiguous():
+        raise ValueError(f"weight must be a contiguous bf16 [{H}]")
+    if out is None:
+        out = torch.empty(T, H, dtype=torch.bfloat16, device=dev)
+    To, Ho, os_ = _rows(out, "out")
+    if (To, Ho) != (T, H):
+        raise ValueError("out shape differs from x")
+    rs = 0
+    if residual is not None:
+        Tr, Hr, rs = _rows(residual, "residual")
+        if (Tr, Hr) != (T, H):
+            raise ValueError("residual shape differs from x")
+    _lib.check(lib.b2_rms_norm(_ptr(out), _ptr(x), _ptr(residual), _ptr(weight), T, H, xs, os_, rs, float(eps),
+                               _stream(dev)))
+    return out
+
+
+def silu_and_mul(gate_up: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[t, i] = silu(gate_up[t, i]) * gate_up[t, I + i]  (b2_silu_and_mul)."""
+    lib = _lib.load()
+    dev = _need_cuda(gate_up=gate_up, out=out)
+    T, H2, is_ = _rows(gate_up, "gate_up")
+    if H2 % 2:
+        raise ValueError("gate_up must be [T, 2*I]")
+    I = H2 // 2
+    if out is None:
+        out = torch.empty(T, I, dtype=torch.bfloat16, device=dev)
+    To, Io, os_ = _rows(out, "out")
+    if (To, Io) != (T, I):
+        raise ValueError("out must be [T, I]")
+    _lib.check(lib.b2_silu_and_mul(_ptr(out), _ptr(gate_up), T, I, is_, os_, _stream(dev)))
+    return out
+
+
+def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_sin: torch.Tensor, k_cache: torch.Tensor,
+                   v_cache: torch.Tensor, slot_mapping: torch.Tensor, Hq: int,
+                   k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None) -> None:
+    """Neox rotary on the q and k parts of qkv [T, (Hq + 2 Hkv) * d] in place, then K', V into the paged cache
+    through slot_mapping (b2_rope_and_cache).  cos_sin: fp32 [max_pos, d] = cos | sin halves per position."""
+    lib = _lib.load()
+    dev = _need_cuda(qkv=qkv, positions=positions, cos_sin=cos_sin, k_cache=k_cache, v_cache=v_cache,
+                     slot_mapping=slot_mapping, k_scale=k_scale, v_scale=v_scale)
+    nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+    kvd = _kv_dtype_of(k_cache)
+    T, W, ts = _rows(qkv, "qkv")
+    if W != (Hq + 2 * Hkv) * d:
+        raise ValueError(f"qkv rows must hold (Hq + 2 Hkv) * d = {(Hq + 2 * Hkv) * d} elements, got {W}")
+    if positions.dtype != torch.int32 or positions.shape != (T,) or not positions.is_contiguous():
+        raise ValueError("positions must be a contiguous int32 [T]")
+    if slot_mapping.dtype != torch.int64 or slot_mapping.shape != (T,) or not slot_mapping.is_contiguous():
+        raise ValueError("slot_mapping must be a contiguous int64 [T]")
+    if cos_sin.dtype != torch.float32 or cos_sin.dim() != 2 or cos_sin.shape[1] != d or not cos_sin.is_contiguous():
+        raise ValueError(f"cos_sin must be a contiguous fp32 [max_pos, {d}]")
+    if kvd == KV_FP8_E4M3:
+        for s in (k_scale, v_scale):
+            if s is None or s.dtype != torch.float32 or s.numel() != 1:
+                raise ValueError("fp8 KV cache needs 1-element fp32 device tensors k_scale / v_scale")
+    _lib.check(lib.b2_rope_and_cache(_ptr(qkv), _ptr(positions), _ptr(cos_sin), cos_sin.shape[0], _ptr(k_cache),
+                                     _ptr(v_cache), _ptr(slot_mapping), T, Hq, Hkv, d, bs, ts, bstride, hstride, kvd,
+                                     _ptr(k_scale), _ptr(v_scale), _stream(dev)))
+
+
+def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, seeds: Optional[torch.Tensor] = None,
+           out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Token per row of bf16 logits [B, V]: greedy where temperature <= 0 (or None), else one Gumbel-max draw from
+    softmax(logits / T) keyed by seeds[b] (b2_sample).  Returns int64 [B]."""
+    lib = _lib.load()
+    dev = _need_cuda(logits=logits, temperature=temperature, seeds=seeds, out=out)
+    B, V, st = _rows(logits, "logits")
+    if temperature is not None and (temperature.dtype != torch.float32 or temperature.shape != (B,)
+                                    or not temperature.is_contiguous()):
+        raise ValueError("temperature must be a contiguous fp32 [B]")
+    if seeds is not None and (seeds.dtype != torch.int64 or seeds.shape != (B,) or not seeds.is_contiguous()):
+        raise ValueError("seeds must be a contiguous int64 [B]")
+    if out is None:
+        out = torch.empty(B, dtype=torch.int64, device=dev)
+    elif out.dtype != torch.int64 or out.shape != (B,) or not out.is_contiguous():
+        raise ValueError("out must be a contiguous int64 [B]")
+    _lib.check(lib.b2_sample(_ptr(out), _ptr(logits), B, V, st, _ptr(temperature), _ptr(seeds), _stream(dev)))
+    return out

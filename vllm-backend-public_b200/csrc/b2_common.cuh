@@ -33,6 +33,10 @@ void b2_set_error(const char* fmt, ...);
         }                                                                             \
     } while (0)
 
+// TMA map over a paged KV cache: one box = one (block, kv head) tile (paged_decode.cu)
+int b2_internal_make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t num_blocks, int Hkv, int bs,
+                                 int64_t block_stride, int64_t head_stride);
+
 static inline bool b2_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 #ifdef __CUDACC__

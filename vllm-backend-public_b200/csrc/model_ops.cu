@@ -1,0 +1,372 @@
+// model_ops.cu -- the HBM-bound element-wise ops either side of the attention path in one decoder layer
+// (the random-init Llama forward that calls the hot path every step).
+//
+//   b2_rms_norm        (optional fused residual add)           vLLM: rms_norm / fused_add_rms_norm
+//   b2_rope_and_cache  neox rotary on q and k in place + KV write through slot_mapping in the same pass
+//                                                             vLLM: rotary_embedding + reshape_and_cache
+//   b2_silu_and_mul    SwiGLU gate                             vLLM: silu_and_mul
+//   b2_sample          greedy / temperature (Gumbel-max) token choice from bf16 logits
+//
+// The engine the reference launches (reference benchmark-vllm/vllm_manager.py:371-374) runs these between the
+// cuBLAS GEMMs; activation dtype is VLLMConfig.dtype (reference benchmark-vllm/models.py:14) = bf16.
+// All are byte movers: 16-byte vector loads/stores, fp32 math, one rounding to bf16 on the way out.
+#include "b2_common.cuh"
+
+namespace {
+
+__device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+
+__device__ __forceinline__ void unpack8(const int4& v, float (&f)[8]) {
+    const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        f[2 * i] = bf_lo(w[i]);
+        f[2 * i + 1] = bf_hi(w[i]);
+    }
+}
+__device__ __forceinline__ int4 pack8(const float (&f)[8]) {
+    int4 r;
+    r.x = (int)b2::pack_bf16x2(f[0], f[1]);
+    r.y = (int)b2::pack_bf16x2(f[2], f[3]);
+    r.z = (int)b2::pack_bf16x2(f[4], f[5]);
+    r.w = (int)b2::pack_bf16x2(f[6], f[7]);
+    return r;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// RMSNorm: one CTA per row.  residual != nullptr: h = bf16(x + residual) is written back to residual
+// and normalised; out = bf16(w * h * rsqrt(mean(h^2) + eps)).  VPT vectors of 8 per thread stay in registers.
+// ---------------------------------------------------------------------------------------------
+template <int VPT>
+__global__ void __launch_bounds__(256)
+rms_norm_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ x,
+                __nv_bfloat16* __restrict__ residual, const __nv_bfloat16* __restrict__ weight,
+                int H, int64_t x_stride, int64_t out_stride, int64_t res_stride, float eps) {
+    const int row = blockIdx.x;
+    const int nvec = H >> 3;
+    const __nv_bfloat16* xr = x + row * x_stride;
+    __nv_bfloat16* rr = residual ? residual + row * res_stride : nullptr;
+    float h[VPT][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = threadIdx.x + k * blockDim.x;
+        if (v < nvec) {
+            unpack8(*reinterpret_cast<const int4*>(xr + v * 8), h[k]);
+            if (rr) {
+                float r[8];
+                unpack8(*reinterpret_cast<const int4*>(rr + v * 8), r);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) h[k][i] += r[i];
+                const int4 packed = pack8(h[k]);          // the residual stream is bf16: round once, then norm
+                *reinterpret_cast<int4*>(rr + v * 8) = packed;
+                unpack8(packed, h[k]);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ss += h[k][i] * h[k][i];
+        }
+    }
+    __shared__ float red[8];
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+    const int nw = blockDim.x >> 5;
+    for (int i = 0; i < nw; ++i) tot += red[i];
+    const float inv = rsqrtf(tot / (float)H + eps);
+    __nv_bfloat16* orow = out + row * out_stride;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = threadIdx.x + k * blockDim.x;
+        if (v < nvec) {
+            float w[8], o[8];
+            unpack8(*reinterpret_cast<const int4*>(weight + v * 8), w);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = w[i] * (h[k][i] * inv);
+            *reinterpret_cast<int4*>(orow + v * 8) = pack8(o);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// SwiGLU: out[t, i] = silu(gate[t, i]) * up[t, i], gate_up = [T, 2I] (gate | up)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+silu_and_mul_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ gate_up, int I,
+                    int64_t in_stride, int64_t out_stride) {
+    const int t = blockIdx.y;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= (I >> 3)) return;
+    const __nv_bfloat16* g = gate_up + t * in_stride + v * 8;
+    float a[8], b[8], o[8];
+    unpack8(b2::ld_nc_16(g), a);
+    unpack8(b2::ld_nc_16(g + I), b);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = a[i] / (1.f + __expf(-a[i])) * b[i];
+    *reinterpret_cast<int4*>(out + t * out_stride + v * 8) = pack8(o);
+}
+
+// ---------------------------------------------------------------------------------------------
+// rotary (neox pairing i <-> i + d/2) on q and k in place, then K (rotated) and V into the paged cache.
+// One CTA per token.  Work items: (Hq + Hkv) heads x (d/16) vector pairs, then Hkv x (d/8) V vectors.
+// cos_sin: fp32 [max_pos, d] = cos[0..d/2) | sin[0..d/2) per position.
+// ---------------------------------------------------------------------------------------------
+template <bool FP8>
+__device__ __forceinline__ void store_cache8(void* cache, int64_t elem, const float (&f)[8], float scale) {
+    if (!FP8) {
+        *reinterpret_cast<int4*>(static_cast<__nv_bfloat16*>(cache) + elem) = pack8(f);
+    } else {
+        // quantise what the bf16 tensor holds: round to bf16 first (same bytes b2_reshape_and_cache would read)
+        const int4 p = pack8(f);
+        float g[8];
+        unpack8(p, g);
+        uint32_t w[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            uint32_t acc = 0;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const __nv_fp8x2_storage_t pr = __nv_cvt_float2_to_fp8x2(
+                    make_float2(__fdiv_rn(g[q * 4 + j * 2], scale), __fdiv_rn(g[q * 4 + j * 2 + 1], scale)),
+                    __NV_SATFINITE, __NV_E4M3);
+                acc |= static_cast<uint32_t>(pr) << (16 * j);
+            }
+            w[q] = acc;
+        }
+        *reinterpret_cast<uint2*>(static_cast<uint8_t*>(cache) + elem) = make_uint2(w[0], w[1]);
+    }
+}
+
+template <bool FP8>
+__global__ void __launch_bounds__(256)
+rope_and_cache_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ positions,
+                      const float* __restrict__ cos_sin, int max_pos, void* __restrict__ k_cache,
+                      void* __restrict__ v_cache, const int64_t* __restrict__ slot_mapping, int Hq, int Hkv, int d, int bs,
+                      int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
+                      const float* __restrict__ k_scale, const float* __restrict__ v_scale) {
+    const int t = blockIdx.x;
+    const int pos = min(max(positions[t], 0), max_pos - 1);   // table bound; the host validates positions
+    const int64_t slot = slot_mapping[t];
+    const int64_t blk = slot >= 0 ? slot / bs : 0;
+    const int off = slot >= 0 ? (int)(slot - blk * bs) : 0;
+    const int half = d >> 1;
+    const int pairs_per_head = half >> 3;              // vector pairs of 8 elements
+    const int n_rot = (Hq + Hkv) * pairs_per_head;
+    const int n_v = Hkv * (d >> 3);
+    __nv_bfloat16* row = qkv + t * token_stride;
+    const float* cs = cos_sin + (int64_t)pos * d;
+    float ks = 1.f, vs = 1.f;
+    if (FP8) { ks = *k_scale; vs = *v_scale; }
+    for (int i = threadIdx.x; i < n_rot + n_v; i += blockDim.x) {
+        if (i < n_rot) {
+            const int h = i / pairs_per_head;
+            const int c = i - h * pairs_per_head;
+            __nv_bfloat16* p = row + h * d + c * 8;
+            float x1[8], x2[8], co[8], si[8], o1[8], o2[8];
+            unpack8(*reinterpret_cast<const int4*>(p), x1);
+            unpack8(*reinterpret_cast<const int4*>(p + half), x2);
+            *reinterpret_cast<float4*>(co) = *reinterpret_cast<const float4*>(cs + c * 8);
+            *reinterpret_cast<float4*>(co + 4) = *reinterpret_cast<const float4*>(cs + c * 8 + 4);
+            *reinterpret_cast<float4*>(si) = *reinterpret_cast<const float4*>(cs + half + c * 8);
+            *reinterpret_cast<float4*>(si + 4) = *reinterpret_cast<const float4*>(cs + half + c * 8 + 4);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                o1[j] = __fsub_rn(__fmul_rn(x1[j], co[j]), __fmul_rn(x2[j], si[j]));
+                o2[j] = __fadd_rn(__fmul_rn(x2[j], co[j]), __fmul_rn(x1[j], si[j]));
+            }
+            *reinterpret_cast<int4*>(p) = pack8(o1);
+            *reinterpret_cast<int4*>(p + half) = pack8(o2);
+            if (h >= Hq && slot >= 0) {
+                const int64_t e = blk * cache_block_stride + (int64_t)(h - Hq) * cache_head_stride + (int64_t)off * d + c * 8;
+                store_cache8<FP8>(k_cache, e, o1, ks);
+                store_cache8<FP8>(k_cache, e + half, o2, ks);
+            }
+        } else if (slot >= 0) {
+            const int j = i - n_rot;
+            const int h = j / (d >> 3);
+            const int c = j - h * (d >> 3);
+            float f[8];
+            unpack8(*reinterpret_cast<const int4*>(row + (Hq + Hkv + h) * d + c * 8), f);
+            const int64_t e = blk * cache_block_stride + (int64_t)h * cache_head_stride + (int64_t)off * d + c * 8;
+            store_cache8<FP8>(v_cache, e, f, vs);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// token choice: one CTA per row of bf16 logits [B, V].
+//   temperature[b] <= 0: argmax (lowest index among equal maxima)
+//   else: argmax of logit / T + g, g = -log(-log(u)), u from a counter hash of (seed[b], index)   (Gumbel-max)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t hash_u32(uint64_t seed, uint32_t idx) {
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (uint64_t)(idx + 1);    // splitmix64 finaliser
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (uint32_t)(z >> 40);                                          // 24 bits
+}
+
+__global__ void __launch_bounds__(1024)
+sample_kernel(int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ logits, int V, int64_t stride,
+              const float* __restrict__ temperature, const int64_t* __restrict__ seeds) {
+    const int b = blockIdx.x;
+    const float T = temperature ? temperature[b] : 0.f;
+    const uint64_t seed = seeds ? (uint64_t)seeds[b] : 0ull;
+    const __nv_bfloat16* row = logits + b * stride;
+    float best = -INFINITY;
+    int best_i = 0x7fffffff;
+    const float invT = T > 0.f ? 1.f / T : 1.f;
+    for (int v = threadIdx.x; v < (V >> 3); v += blockDim.x) {
+        float f[8];
+        unpack8(b2::ld_nc_16(row + v * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int idx = v * 8 + j;
+            float s = f[j];
+            if (T > 0.f) {
+                const float u = ((float)hash_u32(seed, (uint32_t)idx) + 0.5f) * (1.f / 16777216.f);
+                s = s * invT - __logf(-__logf(u));
+            }
+            if (s > best || (s == best && idx < best_i)) { best = s; best_i = idx; }
+        }
+    }
+    for (int idx = (V & ~7) + threadIdx.x; idx < V; idx += blockDim.x) {     // tail (V not a multiple of 8)
+        float s = __bfloat162float(row[idx]);
+        if (T > 0.f) {
+            const float u = ((float)hash_u32(seed, (uint32_t)idx) + 0.5f) * (1.f / 16777216.f);
+            s = s * invT - __logf(-__logf(u));
+        }
+        if (s > best || (s == best && idx < best_i)) { best = s; best_i = idx; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+        if (ob > best || (ob == best && oi < best_i)) { best = ob; best_i = oi; }
+    }
+    __shared__ float sb[32];
+    __shared__ int si[32];
+    if ((threadIdx.x & 31) == 0) { sb[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = best_i; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int nw = blockDim.x >> 5;
+        best = threadIdx.x < nw ? sb[threadIdx.x] : -INFINITY;
+        best_i = threadIdx.x < nw ? si[threadIdx.x] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+            if (ob > best || (ob == best && oi < best_i)) { best = ob; best_i = oi; }
+        }
+        if (threadIdx.x == 0) tokens[b] = best_i == 0x7fffffff ? 0 : best_i;
+    }
+}
+
+}  // namespace
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" int b2_rms_norm(void* out, const void* x, void* residual, const void* weight, int T, int H,
+                           int64_t x_stride, int64_t out_stride, int64_t res_stride, float eps, void* stream) {
+    B2_REQUIRE(T >= 0 && H > 0, B2_EINVAL, "rms_norm: bad sizes T=%d H=%d", T, H);
+    if (T == 0) return B2_OK;
+    B2_REQUIRE(out && x && weight, B2_EINVAL, "rms_norm: null pointer");
+    B2_REQUIRE(H % 8 == 0 && H <= 16384, B2_EUNSUPPORTED, "rms_norm: H=%d must be a multiple of 8 and <= 16384", H);
+    B2_REQUIRE(b2_aligned16(out) && b2_aligned16(x) && b2_aligned16(weight) && b2_aligned16(residual), B2_EINVAL,
+               "rms_norm: pointers must be 16-byte aligned");
+    B2_REQUIRE(x_stride % 8 == 0 && out_stride % 8 == 0 && res_stride % 8 == 0, B2_EINVAL,
+               "rms_norm: row strides must keep 16-byte alignment");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nvec = H / 8;
+    auto* o = static_cast<__nv_bfloat16*>(out);
+    auto* xi = static_cast<const __nv_bfloat16*>(x);
+    auto* r = static_cast<__nv_bfloat16*>(residual);
+    auto* w = static_cast<const __nv_bfloat16*>(weight);
+    if (nvec <= 256) {
+        const int threads = ((nvec + 31) / 32) * 32;
+        rms_norm_kernel<1><<<T, threads, 0, st>>>(o, xi, r, w, H, x_stride, out_stride, res_stride, eps);
+    } else if (nvec <= 512) {
+        rms_norm_kernel<2><<<T, 256, 0, st>>>(o, xi, r, w, H, x_stride, out_stride, res_stride, eps);
+    } else if (nvec <= 1024) {
+        rms_norm_kernel<4><<<T, 256, 0, st>>>(o, xi, r, w, H, x_stride, out_stride, res_stride, eps);
+    } else {
+        rms_norm_kernel<8><<<T, 256, 0, st>>>(o, xi, r, w, H, x_stride, out_stride, res_stride, eps);
+    }
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}
+
+extern "C" int b2_silu_and_mul(void* out, const void* gate_up, int T, int I, int64_t in_stride, int64_t out_stride,
+                               void* stream) {
+    B2_REQUIRE(T >= 0 && I > 0, B2_EINVAL, "silu_and_mul: bad sizes T=%d I=%d", T, I);
+    if (T == 0) return B2_OK;
+    B2_REQUIRE(out && gate_up, B2_EINVAL, "silu_and_mul: null pointer");
+    B2_REQUIRE(I % 8 == 0, B2_EUNSUPPORTED, "silu_and_mul: I=%d must be a multiple of 8", I);
+    B2_REQUIRE(b2_aligned16(out) && b2_aligned16(gate_up) && in_stride % 8 == 0 && out_stride % 8 == 0, B2_EINVAL,
+               "silu_and_mul: pointers / strides must keep 16-byte alignment");
+    B2_REQUIRE(T <= 65535 * 64, B2_EUNSUPPORTED, "silu_and_mul: T=%d too large", T);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nvec = I / 8;
+    auto* o = static_cast<__nv_bfloat16*>(out);
+    auto* g = static_cast<const __nv_bfloat16*>(gate_up);
+    for (int t0 = 0; t0 < T; t0 += 65535) {       // grid.y limit
+        const int n = T - t0 < 65535 ? T - t0 : 65535;
+        silu_and_mul_kernel<<<dim3((nvec + 255) / 256, n), 256, 0, st>>>(o + t0 * out_stride, g + t0 * in_stride, I,
+                                                                        in_stride, out_stride);
+    }
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}
+
+extern "C" int b2_rope_and_cache(void* qkv, const int32_t* positions, const float* cos_sin, int max_pos,
+                                 void* k_cache, void* v_cache, const int64_t* slot_mapping, int T, int Hq, int Hkv,
+                                 int d, int bs, int64_t token_stride, int64_t cache_block_stride,
+                                 int64_t cache_head_stride, int kv_dtype, const float* k_scale, const float* v_scale,
+                                 void* stream) {
+    B2_REQUIRE(T >= 0 && Hq > 0 && Hkv > 0 && d > 0 && bs > 0 && max_pos > 0, B2_EINVAL,
+               "rope_and_cache: bad sizes T=%d Hq=%d Hkv=%d d=%d bs=%d", T, Hq, Hkv, d, bs);
+    if (T == 0) return B2_OK;
+    B2_REQUIRE(qkv && positions && cos_sin && k_cache && v_cache && slot_mapping, B2_EINVAL,
+               "rope_and_cache: null pointer");
+    B2_REQUIRE(kv_dtype == B2_KV_BF16 || kv_dtype == B2_KV_FP8_E4M3, B2_EUNSUPPORTED, "rope_and_cache: kv_dtype %d",
+               kv_dtype);
+    B2_REQUIRE(d % 16 == 0, B2_EUNSUPPORTED, "rope_and_cache: d=%d must be a multiple of 16", d);
+    B2_REQUIRE(b2_aligned16(qkv) && b2_aligned16(cos_sin) && b2_aligned16(k_cache) && b2_aligned16(v_cache), B2_EINVAL,
+               "rope_and_cache: pointers must be 16-byte aligned");
+    B2_REQUIRE(token_stride % 8 == 0 && token_stride >= (int64_t)(Hq + 2 * Hkv) * d && cache_block_stride % 16 == 0 &&
+                   cache_head_stride % 16 == 0 && cache_head_stride >= (int64_t)bs * d,
+               B2_EINVAL, "rope_and_cache: bad strides");
+    if (kv_dtype == B2_KV_FP8_E4M3) B2_REQUIRE(k_scale && v_scale, B2_EINVAL, "rope_and_cache: fp8 needs scales");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    auto* p = static_cast<__nv_bfloat16*>(qkv);
+    if (kv_dtype == B2_KV_BF16)
+        rope_and_cache_kernel<false><<<T, 256, 0, st>>>(p, positions, cos_sin, max_pos, k_cache, v_cache, slot_mapping, Hq, Hkv, d,
+                                                        bs, token_stride, cache_block_stride, cache_head_stride,
+                                                        nullptr, nullptr);
+    else
+        rope_and_cache_kernel<true><<<T, 256, 0, st>>>(p, positions, cos_sin, max_pos, k_cache, v_cache, slot_mapping, Hq, Hkv, d,
+                                                       bs, token_stride, cache_block_stride, cache_head_stride, k_scale,
+                                                       v_scale);
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}
+
+extern "C" int b2_sample(int64_t* tokens, const void* logits, int B, int V, int64_t stride, const float* temperature,
+                         const int64_t* seeds, void* stream) {
+    B2_REQUIRE(B >= 0 && V > 0, B2_EINVAL, "sample: bad sizes B=%d V=%d", B, V);
+    if (B == 0) return B2_OK;
+    B2_REQUIRE(tokens && logits, B2_EINVAL, "sample: null pointer");
+    B2_REQUIRE(b2_aligned16(logits) && stride % 8 == 0, B2_EINVAL, "sample: logits rows must be 16-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    sample_kernel<<<B, 1024, 0, st>>>(tokens, static_cast<const __nv_bfloat16*>(logits), V, stride, temperature, seeds);
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}

@@ -1271,6 +1271,12 @@ bool shape_ok(int B, int Hq, int Hkv, int d, int bs, int max_nb) {
 
 }  // namespace
 
+// shared with prefill_attention.cu (internal to the library's objects, not exported)
+int b2_internal_make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t num_blocks, int Hkv, int bs,
+                                 int64_t block_stride, int64_t head_stride) {
+    return make_cache_tmap(tm, cache, kv_dtype, num_blocks, Hkv, bs, block_stride, head_stride);
+}
+
 extern "C" int b2_paged_decode_auto_splits(int B, int Hq, int Hkv, int d, int bs, int max_nb, int kv_dtype) {
     (void)kv_dtype;
     if (!shape_ok(B, Hq, Hkv, d, bs, max_nb)) return B2_EINVAL;
