@@ -165,3 +165,47 @@ def sample_ref(logits, temperature=None, seeds=None) -> torch.Tensor:
     mx = s.max(dim=-1, keepdim=True).values
     first = torch.where(s == mx, torch.arange(s.shape[1]).expand_as(s), torch.full_like(s, s.shape[1], dtype=torch.long))
     return first.min(dim=-1).values
+
+
+# --------------------------------------------------------------------------------------
+# whole-model restatement: a Llama decoder over ONE sequence, dense causal attention (no paging), fp32 math with the
+# activations rounded to bf16 where the engine's tensors are bf16.  HF LlamaForCausalLM semantics
+# (transformers/models/llama/modeling_llama.py); checked against that class in tests/test_layer_oracle.py.
+# weights: the engine's dict (embed, l{i}.ln1/wqkv[/bqkv]/wo/ln2/wgu/wdown, norm, lm_head) as CPU tensors.
+# --------------------------------------------------------------------------------------
+def llama_forward_ref(w: dict, token_ids, *, layers: int, Hq: int, Hkv: int, d: int, eps: float,
+                      cos_sin: torch.Tensor) -> torch.Tensor:
+    """Returns fp32 logits [T, vocab] for positions 0..T-1 of one sequence."""
+    f32 = lambda t: t.to(torch.float32)                              # noqa: E731
+    ids = torch.as_tensor(token_ids, dtype=torch.long)
+    T = ids.numel()
+    half = d // 2
+    G = Hq // Hkv
+    resid = w["embed"][ids].to(torch.bfloat16)
+    cos = cos_sin[:T, :half].unsqueeze(1)
+    sin = cos_sin[:T, half:].unsqueeze(1)
+    causal = torch.arange(T).unsqueeze(0) > torch.arange(T).unsqueeze(1)
+    x, _ = rms_norm_ref(resid, w["l0.ln1"], eps)
+    for l in range(layers):
+        if l > 0:
+            x, resid = rms_norm_ref(x, w[f"l{l}.ln1"], eps, resid)
+        qkv = f32(x) @ f32(w[f"l{l}.wqkv"]).T
+        if f"l{l}.bqkv" in w:
+            qkv = qkv + f32(w[f"l{l}.bqkv"])
+        qkv = f32(_bf16_round(qkv)).view(T, Hq + 2 * Hkv, d)
+        rot = qkv[:, : Hq + Hkv]
+        x1, x2 = rot[..., :half], rot[..., half:]
+        rot = f32(_bf16_round(torch.cat([x1 * cos - x2 * sin, x2 * cos + x1 * sin], dim=-1)))
+        q = rot[:, :Hq].permute(1, 0, 2)
+        k = rot[:, Hq:].permute(1, 0, 2).repeat_interleave(G, 0)
+        v = qkv[:, Hq + Hkv:].permute(1, 0, 2).repeat_interleave(G, 0)
+        s = (q @ k.transpose(1, 2)) / math.sqrt(d)
+        s = s.masked_fill(causal.unsqueeze(0), float("-inf"))
+        attn = _bf16_round((torch.softmax(s, -1) @ v).permute(1, 0, 2).reshape(T, Hq * d))
+        o = _bf16_round(f32(attn) @ f32(w[f"l{l}.wo"]).T)
+        x, resid = rms_norm_ref(o, w[f"l{l}.ln2"], eps, resid)
+        gu = _bf16_round(f32(x) @ f32(w[f"l{l}.wgu"]).T)
+        act = silu_and_mul_ref(gu)
+        x = _bf16_round(f32(act) @ f32(w[f"l{l}.wdown"]).T)
+    x, _ = rms_norm_ref(x, w["norm"], eps, resid)
+    return f32(x) @ f32(w["lm_head"]).T

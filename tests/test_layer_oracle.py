@@ -130,3 +130,33 @@ def test_sample_oracle():
     got = L.sample_ref(rows, torch.ones(N), torch.arange(N, dtype=torch.int64) * 977 + 5)
     freq = torch.bincount(got, minlength=4).float() / N
     assert (freq - torch.softmax(rows[0].float(), 0)).abs().max() < 0.03
+
+
+def test_llama_forward_oracle_matches_transformers():
+    """The whole-model oracle against transformers' LlamaForCausalLM (fp32 weights = the bf16 values)."""
+    from transformers import LlamaConfig, LlamaForCausalLM
+    hidden, layers, Hq, Hkv, d, inter, vocab = 256, 2, 2, 1, 128, 512, 300
+    cfg = LlamaConfig(hidden_size=hidden, num_hidden_layers=layers, num_attention_heads=Hq, num_key_value_heads=Hkv,
+                      head_dim=d, intermediate_size=inter, vocab_size=vocab, rms_norm_eps=1e-5, rope_theta=500000.0,
+                      max_position_embeddings=512, tie_word_embeddings=False, attention_bias=False)
+    torch.manual_seed(0)
+    m = LlamaForCausalLM(cfg).eval()
+    sd = {k: v.to(torch.bfloat16) for k, v in m.state_dict().items()}
+    m.load_state_dict({k: v.float() for k, v in sd.items()})
+    w = {"embed": sd["model.embed_tokens.weight"], "norm": sd["model.norm.weight"], "lm_head": sd["lm_head.weight"]}
+    for l in range(layers):
+        p = f"model.layers.{l}."
+        w[f"l{l}.ln1"] = sd[p + "input_layernorm.weight"]
+        w[f"l{l}.ln2"] = sd[p + "post_attention_layernorm.weight"]
+        w[f"l{l}.wqkv"] = torch.cat([sd[p + f"self_attn.{x}_proj.weight"] for x in "qkv"])
+        w[f"l{l}.wo"] = sd[p + "self_attn.o_proj.weight"]
+        w[f"l{l}.wgu"] = torch.cat([sd[p + "mlp.gate_proj.weight"], sd[p + "mlp.up_proj.weight"]])
+        w[f"l{l}.wdown"] = sd[p + "mlp.down_proj.weight"]
+    ids = torch.randint(0, vocab, (40,))
+    with torch.no_grad():
+        hf = m(ids.unsqueeze(0)).logits[0]
+    ours = L.llama_forward_ref(w, ids, layers=layers, Hq=Hq, Hkv=Hkv, d=d, eps=1e-5,
+                               cos_sin=L.rope_table(512, d, 500000.0))
+    # ours rounds activations to bf16 between ops (as the engine does); HF here runs pure fp32
+    assert (ours - hf).abs().max() < 3e-2 * hf.abs().max()
+    assert (ours.argmax(-1) == hf.argmax(-1)).float().mean() > 0.9

@@ -1,0 +1,258 @@
+"""Llama-family decoder on the b200attn ops: the caller of the hot path.
+
+What the engine launched by the reference (reference benchmark-vllm/vllm_manager.py:371-374, flags from
+benchmark-vllm/vllm_templates.py:50-87) computes for every scheduled token.  The projections are plain library
+GEMMs (torch.matmul -> cuBLAS); everything between them is this repo's sm_100a kernels behind the C ABI:
+b2_rms_norm (fused residual add), b2_rope_and_cache (rotary + KV write in one pass over the fused QKV rows),
+b2_paged_decode / b2_prefill_attention, b2_silu_and_mul, b2_sample.  There is no CPU path.
+
+Weights: random-init from a seed (BASELINE.json configs[4] is random-init; the box has no network), or a local
+HF directory (config.json + *.safetensors) when `model` is a path.  Geometry comes from the registry below or
+from that config.json.  head_dim must be 128 (what the attention kernels are built for).
+"""
+from __future__ import annotations
+
+import json
+import math
+from dataclasses import dataclass, field
+from pathlib import Path
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+
+
+@dataclass
+class ModelConfig:
+    name: str
+    hidden: int
+    layers: int
+    Hq: int
+    Hkv: int
+    inter: int
+    vocab: int
+    d: int = 128
+    rope_theta: float = 500000.0
+    rope_scaling: Optional[dict] = None
+    eps: float = 1e-5
+    qkv_bias: bool = False
+    tie_embeddings: bool = False
+    max_position: int = 131072
+
+    @property
+    def params(self) -> int:
+        per_layer = self.hidden * (self.Hq + 2 * self.Hkv) * self.d + self.Hq * self.d * self.hidden \
+            + 3 * self.hidden * self.inter + 2 * self.hidden
+        emb = self.vocab * self.hidden * (1 if self.tie_embeddings else 2)
+        return self.layers * per_layer + emb + self.hidden
+
+    def kv_bytes_per_token(self, kv_elem_bytes: int = 2, tp: int = 1) -> int:
+        return 2 * self.layers * (self.Hkv // tp) * self.d * kv_elem_bytes
+
+
+_LLAMA3_SCALING = dict(factor=8.0, low_freq_factor=1.0, high_freq_factor=4.0, original_max_position_embeddings=8192)
+
+REGISTRY: Dict[str, ModelConfig] = {
+    "llama-3-8b": ModelConfig("llama-3-8b", 4096, 32, 32, 8, 14336, 128256, max_position=8192),
+    "llama-3.1-8b": ModelConfig("llama-3.1-8b", 4096, 32, 32, 8, 14336, 128256, rope_scaling=_LLAMA3_SCALING),
+    "llama-3-70b": ModelConfig("llama-3-70b", 8192, 80, 64, 8, 28672, 128256, max_position=8192),
+    "qwen2-1.5b": ModelConfig("qwen2-1.5b", 1536, 28, 12, 2, 8960, 151936, rope_theta=1e6, eps=1e-6,
+                              qkv_bias=True, tie_embeddings=True, max_position=32768),
+    "qwen2-7b": ModelConfig("qwen2-7b", 3584, 28, 28, 4, 18944, 152064, rope_theta=1e6, eps=1e-6, qkv_bias=True,
+                            max_position=32768),
+    # test-sized geometries (same head_dim, same op sequence)
+    "tiny": ModelConfig("tiny", 512, 2, 4, 2, 1024, 1024, max_position=8192),
+    "small": ModelConfig("small", 1024, 4, 8, 2, 2816, 32000, max_position=32768),
+}
+
+_ALIASES = {
+    "meta-llama/meta-llama-3-8b": "llama-3-8b", "meta-llama/meta-llama-3-8b-instruct": "llama-3-8b",
+    "meta-llama/llama-3.1-8b": "llama-3.1-8b", "meta-llama/llama-3.1-8b-instruct": "llama-3.1-8b",
+    "meta-llama/meta-llama-3-70b": "llama-3-70b", "meta-llama/meta-llama-3-70b-instruct": "llama-3-70b",
+    "qwen/qwen2-1.5b-instruct": "qwen2-1.5b", "qwen/qwen2-1.5b": "qwen2-1.5b",
+    "qwen/qwen2-7b-instruct": "qwen2-7b", "qwen/qwen2-7b": "qwen2-7b",
+}
+
+
+def config_from_hf_dir(path: Path) -> ModelConfig:
+    c = json.loads((path / "config.json").read_text())
+    Hq = c["num_attention_heads"]
+    d = c.get("head_dim") or c["hidden_size"] // Hq
+    scaling = c.get("rope_scaling")
+    if scaling and scaling.get("rope_type", scaling.get("type")) != "llama3":
+        scaling = None
+    return ModelConfig(
+        name=path.name, hidden=c["hidden_size"], layers=c["num_hidden_layers"], Hq=Hq,
+        Hkv=c.get("num_key_value_heads", Hq), inter=c["intermediate_size"], vocab=c["vocab_size"], d=d,
+        rope_theta=float(c.get("rope_theta", 10000.0)), rope_scaling=scaling, eps=float(c.get("rms_norm_eps", 1e-5)),
+        qkv_bias=bool(c.get("attention_bias", False)) or "qwen2" in c.get("model_type", ""),
+        tie_embeddings=bool(c.get("tie_word_embeddings", False)),
+        max_position=int(c.get("max_position_embeddings", 8192)))
+
+
+def resolve_config(model: str) -> ModelConfig:
+    """`--model` of the launch contract -> geometry.  A local HF directory wins; else the registry (by short name or
+    by the hub id the reference's configs use); unknown names fail loudly (nothing can be downloaded here)."""
+    p = Path(model)
+    if p.is_dir() and (p / "config.json").exists():
+        return config_from_hf_dir(p)
+    key = model.lower()
+    key = _ALIASES.get(key, key)
+    if key in REGISTRY:
+        return REGISTRY[key]
+    raise ValueError(f"unknown model {model!r}: not a local HF directory and not one of {sorted(REGISTRY)} "
+                     f"(or hub ids {sorted(_ALIASES)})")
+
+
+def rope_table(max_pos: int, d: int, theta: float, scaling: Optional[dict], device) -> torch.Tensor:
+    """fp32 [max_pos, d] = cos | sin halves per position (fp64 angles), Llama-3.1 frequency scaling when given.
+    Same construction as the oracle's table (oracle/layer_ref.py::rope_table); transformers' llama3 init agrees."""
+    inv = 1.0 / (theta ** (torch.arange(0, d, 2, dtype=torch.float64) / d))
+    if scaling:
+        f, lo, hi = scaling["factor"], scaling["low_freq_factor"], scaling["high_freq_factor"]
+        old = scaling["original_max_position_embeddings"]
+        wavelen = 2 * math.pi / inv
+        smooth = ((old / wavelen) - lo) / (hi - lo)
+        scaled = torch.where(wavelen > old / lo, inv / f, inv)
+        mid = (wavelen <= old / lo) & (wavelen >= old / hi)
+        inv = torch.where(mid, (1 - smooth) * inv / f + smooth * inv, scaled)
+    ang = torch.arange(max_pos, dtype=torch.float64).unsqueeze(1) * inv.unsqueeze(0)
+    return torch.cat([torch.cos(ang), torch.sin(ang)], dim=1).to(torch.float32).contiguous().to(device)
+
+
+@dataclass
+class PrefillBatch:
+    """Device-side description of the prompt chunks of one step (rows n_decode.. of the token batch)."""
+    cu_q: torch.Tensor            # int32 [n + 1], relative to the first prefill row
+    ctx_start: torch.Tensor       # int32 [n]
+    block_tables: torch.Tensor    # int32 [n, max_nb]
+    total_tokens: int
+
+
+class LlamaModel:
+    """Weights + KV cache + forward over one scheduled token batch.  One instance per GPU."""
+
+    def __init__(self, cfg: ModelConfig, device: torch.device, num_blocks: int, block_size: int = 16,
+                 seed: int = 0, weights_dir: Optional[Path] = None, max_position: Optional[int] = None,
+                 kv_dtype: torch.dtype = torch.bfloat16):
+        if cfg.d != 128:
+            raise ValueError(f"head_dim {cfg.d}: the attention kernels are built for 128")
+        if device.type != "cuda":
+            raise ValueError("LlamaModel needs a CUDA device (b200attn has no CPU path)")
+        self.cfg, self.dev, self.bs, self.num_blocks = cfg, device, block_size, num_blocks
+        self.max_position = max_position or cfg.max_position
+        self.qkv_width = (cfg.Hq + 2 * cfg.Hkv) * cfg.d
+        self.w: Dict[str, torch.Tensor] = {}
+        if weights_dir is not None and any(weights_dir.glob("*.safetensors")):
+            self._load_hf(weights_dir)
+        else:
+            self._random_init(seed)
+        self.cos_sin = rope_table(self.max_position, cfg.d, cfg.rope_theta, cfg.rope_scaling, device)
+        # KV pool: [layers, 2, num_blocks, Hkv, bs, d]; one (block, head) tile = bs x d contiguous ("HND")
+        self.kv = torch.zeros(cfg.layers, 2, num_blocks, cfg.Hkv, block_size, cfg.d, dtype=kv_dtype, device=device)
+        self.k_scale = self.v_scale = None
+        if kv_dtype != torch.bfloat16:
+            self.k_scale = torch.ones(1, dtype=torch.float32, device=device)
+            self.v_scale = torch.ones(1, dtype=torch.float32, device=device)
+        self._ws: Optional[torch.Tensor] = None
+
+    # ------------------------------------------------------------------ weights
+    def _random_init(self, seed: int) -> None:
+        c, dev = self.cfg, self.dev
+        g = torch.Generator(device=dev).manual_seed(seed)
+
+        def rnd(*shape, std=0.02):
+            return (torch.randn(*shape, generator=g, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
+
+        w = self.w
+        w["embed"] = rnd(c.vocab, c.hidden)
+        for l in range(c.layers):
+            w[f"l{l}.ln1"] = torch.ones(c.hidden, dtype=torch.bfloat16, device=dev)
+            w[f"l{l}.wqkv"] = rnd(self.qkv_width, c.hidden)
+            if c.qkv_bias:
+                w[f"l{l}.bqkv"] = rnd(self.qkv_width)
+            w[f"l{l}.wo"] = rnd(c.hidden, c.Hq * c.d)
+            w[f"l{l}.ln2"] = torch.ones(c.hidden, dtype=torch.bfloat16, device=dev)
+            w[f"l{l}.wgu"] = rnd(2 * c.inter, c.hidden)
+            w[f"l{l}.wdown"] = rnd(c.hidden, c.inter)
+        w["norm"] = torch.ones(c.hidden, dtype=torch.bfloat16, device=dev)
+        w["lm_head"] = w["embed"] if c.tie_embeddings else rnd(c.vocab, c.hidden)
+
+    def _load_hf(self, path: Path) -> None:
+        from safetensors import safe_open
+        c, dev = self.cfg, self.dev
+        raw: Dict[str, torch.Tensor] = {}
+        for f in sorted(path.glob("*.safetensors")):
+            with safe_open(str(f), framework="pt", device="cpu") as sf:
+                for k in sf.keys():
+                    raw[k] = sf.get_tensor(k)
+
+        def get(name):
+            return raw[name].to(torch.bfloat16).to(dev)
+
+        w = self.w
+        w["embed"] = get("model.embed_tokens.weight")
+        for l in range(c.layers):
+            p = f"model.layers.{l}."
+            w[f"l{l}.ln1"] = get(p + "input_layernorm.weight")
+            w[f"l{l}.wqkv"] = torch.cat([get(p + f"self_attn.{x}_proj.weight") for x in "qkv"]).contiguous()
+            if c.qkv_bias:
+                w[f"l{l}.bqkv"] = torch.cat([get(p + f"self_attn.{x}_proj.bias") for x in "qkv"]).contiguous()
+            w[f"l{l}.wo"] = get(p + "self_attn.o_proj.weight")
+            w[f"l{l}.ln2"] = get(p + "post_attention_layernorm.weight")
+            w[f"l{l}.wgu"] = torch.cat([get(p + "mlp.gate_proj.weight"), get(p + "mlp.up_proj.weight")]).contiguous()
+            w[f"l{l}.wdown"] = get(p + "mlp.down_proj.weight")
+        w["norm"] = get("model.norm.weight")
+        w["lm_head"] = w["embed"] if c.tie_embeddings or "lm_head.weight" not in raw else get("lm_head.weight")
+
+    def weight_bytes(self) -> int:
+        seen, n = set(), 0
+        for t in self.w.values():
+            if t.data_ptr() not in seen:
+                seen.add(t.data_ptr())
+                n += t.numel() * t.element_size()
+        return n
+
+    # ------------------------------------------------------------------ forward
+    def decode_workspace(self, max_batch: int, max_nb: int) -> torch.Tensor:
+        need = max(ops.decode_workspace_bytes(max_batch, self.cfg.Hq, self.cfg.Hkv, self.cfg.d, self.bs, max_nb, 0), 16)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.zeros(need, dtype=torch.uint8, device=self.dev)
+        return self._ws
+
+    def forward(self, tokens: torch.Tensor, positions: torch.Tensor, slots: torch.Tensor, n_decode: int,
+                dec_block_tables: Optional[torch.Tensor], dec_seq_lens: Optional[torch.Tensor],
+                prefill: Optional[PrefillBatch], sample_rows: Optional[torch.Tensor], num_splits: int = 0) -> torch.Tensor:
+        """tokens int64 [T] (rows [0, n_decode) = one new token per running sequence, the rest = prompt chunks),
+        positions int32 [T], slots int64 [T].  Returns bf16 logits [len(sample_rows) or T, vocab]."""
+        c, w = self.cfg, self.w
+        T = tokens.shape[0]
+        resid = w["embed"].index_select(0, tokens)                       # [T, hidden]  (residual stream, bf16)
+        x = ops.rms_norm(resid, w["l0.ln1"], c.eps)
+        attn = torch.empty(T, c.Hq, c.d, dtype=torch.bfloat16, device=self.dev)
+        for l in range(c.layers):
+            if l > 0:
+                x = ops.rms_norm(x, w[f"l{l}.ln1"], c.eps, residual=resid, out=x)
+            qkv = torch.nn.functional.linear(x, w[f"l{l}.wqkv"], w.get(f"l{l}.bqkv"))
+            kc, vc = self.kv[l, 0], self.kv[l, 1]
+            ops.rope_and_cache(qkv, positions, self.cos_sin, kc, vc, slots, c.Hq, self.k_scale, self.v_scale)
+            q = qkv.view(T, c.Hq + 2 * c.Hkv, c.d)[:, : c.Hq]
+            if n_decode:
+                ops.paged_decode(q[:n_decode], kc, vc, dec_block_tables, dec_seq_lens, k_scale=self.k_scale,
+                                 v_scale=self.v_scale, out=attn[:n_decode],
+                                 workspace=self.decode_workspace(n_decode, dec_block_tables.shape[1]),
+                                 num_splits=num_splits)
+            if prefill is not None and prefill.total_tokens:
+                ops.prefill_attention(q[n_decode:], kc, vc, prefill.block_tables, prefill.cu_q, prefill.ctx_start,
+                                      total_tokens=prefill.total_tokens, out=attn[n_decode:])
+            o = torch.nn.functional.linear(attn.view(T, c.Hq * c.d), w[f"l{l}.wo"])
+            x = ops.rms_norm(o, w[f"l{l}.ln2"], c.eps, residual=resid, out=o)
+            gu = torch.nn.functional.linear(x, w[f"l{l}.wgu"])
+            act = ops.silu_and_mul(gu)
+            x = torch.nn.functional.linear(act, w[f"l{l}.wdown"])
+        if sample_rows is not None:
+            x = x.index_select(0, sample_rows)
+            resid = resid.index_select(0, sample_rows)
+        x = ops.rms_norm(x, w["norm"], c.eps, residual=resid, out=x)
+        return torch.nn.functional.linear(x, w["lm_head"])
