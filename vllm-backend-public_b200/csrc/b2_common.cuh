@@ -37,6 +37,15 @@ void b2_set_error(const char* fmt, ...);
 int b2_internal_make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t num_blocks, int Hkv, int bs,
                                  int64_t block_stride, int64_t head_stride);
 
+int b2_internal_encode_bf16_sw128(CUtensorMap* tm, const void* ptr, int rank, const uint64_t* dims,
+                                  const uint64_t* strides_bytes, const uint32_t* box);
+// tcgen05 prompt-chunk attention (prefill_tc5.cu); same arguments as b2_prefill_attention after validation
+int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const void* v_cache,
+                            const int32_t* block_tables, const int32_t* cu_q, const int32_t* ctx_start, int n_chunks,
+                            int T, int Hq, int Hkv, int bs, int max_nb, int64_t num_blocks, int64_t q_stride,
+                            int64_t out_stride, int64_t cache_block_stride, int64_t cache_head_stride, float scale,
+                            void* stream);
+
 static inline bool b2_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 #ifdef __CUDACC__

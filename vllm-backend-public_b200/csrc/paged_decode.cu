@@ -1271,6 +1271,22 @@ bool shape_ok(int B, int Hq, int Hkv, int d, int bs, int max_nb) {
 
 }  // namespace
 
+// generic bf16 tiled map with 128-byte swizzle (prefill_tc5.cu builds its Q and half-tile cache maps with it)
+int b2_internal_encode_bf16_sw128(CUtensorMap* tm, const void* ptr, int rank, const uint64_t* dims,
+                                  const uint64_t* strides_bytes, const uint32_t* box) {
+    EncodeTiledFn enc = get_encode_tiled();
+    B2_REQUIRE(enc != nullptr, B2_ECUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t d[5], st[4];
+    cuuint32_t b[5], es[5];
+    for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; es[i] = 1; }
+    for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), d, st, b, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B2_REQUIRE(r == CUDA_SUCCESS, B2_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return B2_OK;
+}
+
 // shared with prefill_attention.cu (internal to the library's objects, not exported)
 int b2_internal_make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t num_blocks, int Hkv, int bs,
                                  int64_t block_stride, int64_t head_stride) {

@@ -23,6 +23,8 @@
 // Tensor-bound (4*d flop per (q, kv) pair against 2*d*2 B of KV per kv token per 128 queries).
 #include "b2_common.cuh"
 
+#include <stdlib.h>
+
 namespace {
 
 constexpr int D = 128;
@@ -309,6 +311,13 @@ extern "C" int b2_prefill_attention(void* out, const void* q, const void* k_cach
                B2_EINVAL, "prefill_attention: bad cache strides");
     const int64_t n_qtiles = (int64_t)T / BM + n_chunks;       // upper bound of sum ceil(len_c / BM)
     B2_REQUIRE(n_qtiles <= 65535, B2_EUNSUPPORTED, "prefill_attention: %lld q tiles exceed the grid", (long long)n_qtiles);
+
+    // default: the tcgen05 kernel (prefill_tc5.cu); B2_PREFILL_IMPL=mma keeps this file's mma.sync kernel as the A/B
+    static const bool use_mma = []() { const char* e = getenv("B2_PREFILL_IMPL"); return e && e[0] == 'm'; }();
+    if (!use_mma)
+        return b2_internal_prefill_tc5(out, q, k_cache, v_cache, block_tables, cu_q, ctx_start, n_chunks, T, Hq, Hkv, bs,
+                                       max_nb, num_blocks, q_stride, out_stride, cache_block_stride, cache_head_stride,
+                                       scale, stream);
 
     CUtensorMap tmK, tmV;
     int rc = b2_internal_make_cache_tmap(&tmK, k_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride);

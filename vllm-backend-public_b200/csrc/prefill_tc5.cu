@@ -1,0 +1,434 @@
+// prefill_tc5.cu -- prompt-chunk attention over the paged KV cache on the 5th-gen tensor cores (sm_100a):
+// tcgen05.mma with TMEM accumulators, TMA-staged paged K/V, warp-specialised (FlashAttention-4 style dataflow).
+// Same contract as prefill_attention.cu (include/b200attn.h `b2_prefill_attention`); this is the default kernel,
+// the mma.sync one is kept as the A/B (B2_PREFILL_IMPL=mma).
+//
+// One CTA = 256 query tokens of one q head = two 128-row tiles A and B, 10 warps:
+//   warps 0-3  softmax of tile A   (one thread = one query row = one TMEM lane)
+//   warps 4-7  softmax of tile B
+//   warp  8    TMA producer: Q (two 128x128 tiles) once, then the chunk's block table -> K|V stages of 128 tokens
+//   warp  9    MMA issuer (one lane): S = Q.K^T and O += P.V as tcgen05.mma 128x128x16, bf16 -> fp32 in TMEM
+// TMEM (512 columns x 128 lanes): S_A [0,128) S_B [128,256) O_A [256,384) O_B [384,512); P (bf16 pairs) overwrites the
+// first 64 columns of its S tile and is fed back as the A operand straight from TMEM, so P never touches shared memory.
+// Issue order  QK_A(0) QK_B(0) | PV_A(j) QK_A(j+1) PV_B(j) QK_B(j+1) ...  lets the softmax of one tile run under the
+// MMAs of the other.  Rescaling of O is lazy: a row keeps its stale maximum until the true one exceeds it by 2^8.
+//
+// Shared memory (1024-byte aligned, 128-byte swizzle, the canonical UMMA layouts):
+//   Q_A, Q_B     2 x [2 halves][128 rows][64 el]           K-major operand A           64 KiB
+//   stage s      K: [2 halves][128 tok][64 el]  K-major operand B (QK^T)
+//                V: [2 halves][128 tok][64 el]  MN-major operand B (P.V)               2 x 64 KiB
+// One TMA box = one 64-element half of one (block, kv head) tile: bs rows x 128 B, contiguous in HBM.
+#include "b2_common.cuh"
+
+namespace {
+
+constexpr int D = 128;
+constexpr int BM = 128;             // rows per q tile
+constexpr int BN = 128;             // kv tokens per stage
+constexpr int NSTAGE = 2;
+constexpr int NTHREADS = 320;
+constexpr int SUB_BYTES = 128 * 128;               // one [128 rows][64 el] sub-tile
+constexpr int TILE_BYTES = 2 * SUB_BYTES;          // 32 KiB: a 128 x 128 bf16 tile
+constexpr int Q_BYTES = 2 * TILE_BYTES;
+constexpr int STAGE_BYTES = 2 * TILE_BYTES;        // K | V
+constexpr int SMEM_BYTES = Q_BYTES + NSTAGE * STAGE_BYTES + 256;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float RESCALE_THRESHOLD = 8.f;           // log2 units
+
+// barrier slots (8 bytes each) after the tiles
+enum { BAR_Q = 0, BAR_K = 1, BAR_V = BAR_K + NSTAGE, BAR_KE = BAR_V + NSTAGE, BAR_VE = BAR_KE + NSTAGE,
+       BAR_S = BAR_VE + NSTAGE, BAR_P = BAR_S + 2, BAR_PV = BAR_P + 2, BAR_COUNT = BAR_PV + 2 };
+static_assert(BAR_COUNT * 8 + 16 <= 256, "barrier area");
+
+struct Tc5Params {
+    __nv_bfloat16* out;
+    const int32_t* block_tables;
+    const int32_t* cu_q;
+    const int32_t* ctx_start;
+    int n_chunks, Hq, G, bs, max_nb;
+    int64_t out_stride;
+    float scale_log2;
+};
+
+// ---- tcgen05 wrappers --------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+           (1ull << 46) | (2ull << 61);             // version 1 (Blackwell), SWIZZLE_128B
+}
+__host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, int b_mn_major) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);              // D f32, A bf16, B bf16, A K-major
+}
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, bool acc) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"((uint32_t)acc) : "memory");
+}
+__device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, bool acc) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"((uint32_t)acc) : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint32_t bar) {       // arrives on `bar` when all MMAs issued so far are done
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// 32 lanes x 32 columns of 32 bits: thread i of the warp gets lane (base + i), 32 consecutive columns
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%32], "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31};"
+        ::"r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+          "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+          "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+          "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]),
+          "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+
+// =============================================================================================
+// the kernel
+// =============================================================================================
+__global__ void __launch_bounds__(NTHREADS, 1)
+prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                   const __grid_constant__ CUtensorMap tmV, const Tc5Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ int s_tile[4];
+    __shared__ uint32_t s_tmem;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int hq = blockIdx.x, kvh = hq / p.G;
+    const uint32_t sbase = b2::smem_u32(smem_raw);
+    const uint32_t q_smem = sbase;
+    const uint32_t ring = sbase + Q_BYTES;
+    const uint32_t bars = ring + NSTAGE * STAGE_BYTES;
+    auto bar = [&](int i) { return bars + 8u * i; };
+
+    if (tid == 0) {
+        if (sbase & 1023u) __trap();
+        int want = (int)(gridDim.y - 1 - blockIdx.y), found = -1, q0 = 0;
+        for (int c = 0; c < p.n_chunks; ++c) {
+            const int len = p.cu_q[c + 1] - p.cu_q[c];
+            const int nt = (len + 2 * BM - 1) / (2 * BM);
+            if (want < nt) { found = c; q0 = want * 2 * BM; break; }
+            want -= nt;
+        }
+        s_tile[0] = found;
+        s_tile[1] = q0;
+        s_tile[2] = found >= 0 ? p.cu_q[found + 1] - p.cu_q[found] : 0;
+        s_tile[3] = found >= 0 ? p.ctx_start[found] : 0;
+        b2::mbar_init(bar(BAR_Q), 1);
+        for (int s = 0; s < NSTAGE; ++s) {
+            b2::mbar_init(bar(BAR_K + s), 1);
+            b2::mbar_init(bar(BAR_V + s), 1);
+            b2::mbar_init(bar(BAR_KE + s), 1);
+            b2::mbar_init(bar(BAR_VE + s), 1);
+        }
+        for (int x = 0; x < 2; ++x) {
+            b2::mbar_init(bar(BAR_S + x), 1);
+            b2::mbar_init(bar(BAR_P + x), 4);      // one arrive per softmax warp of the tile
+            b2::mbar_init(bar(BAR_PV + x), 1);
+        }
+        b2::fence_mbar_init();
+    }
+    if (warp == 9) {                               // TMEM: all 512 columns (one CTA per SM)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(b2::smem_u32(&s_tmem)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+    const int chunk = s_tile[0];
+    const int q0 = s_tile[1], len = s_tile[2], start = s_tile[3];
+
+    if (chunk >= 0) {
+        const int rows = min(2 * BM, len - q0);                 // valid query rows of the CTA
+        const int rowsX[2] = {min(BM, rows), max(0, rows - BM)};
+        // keys [0, hiX) are visible to the last row of tile X; tiles of 128 keys
+        const int hiX[2] = {start + q0 + rowsX[0], rowsX[1] ? start + q0 + BM + rowsX[1] : 0};
+        const int nX[2] = {(hiX[0] + BN - 1) / BN, (hiX[1] + BN - 1) / BN};
+        const int n_tiles = max(nX[0], nX[1]);
+        const int kv_hi = max(hiX[0], hiX[1]);
+        const int row0 = p.cu_q[chunk] + q0;                    // first token row in q / out
+
+        if (warp == 8) {
+            // ------------------------------------------ TMA producer ------------------------------------------
+            if (lane == 0) {
+                b2::tma_prefetch_desc(&tmQ);
+                b2::tma_prefetch_desc(&tmK);
+                b2::tma_prefetch_desc(&tmV);
+            }
+            uint64_t pol_keep, pol_once;
+            asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+            asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_once));
+            if (lane == 0) {
+                b2::mbar_arrive_expect_tx(bar(BAR_Q), Q_BYTES);
+                for (int x = 0; x < 2; ++x)
+                    for (int h = 0; h < 2; ++h)                 // rows past T are zero-filled by the TMA unit
+                        b2::tma_load_4d(q_smem + x * TILE_BYTES + h * SUB_BYTES, &tmQ, bar(BAR_Q), 0, h, hq,
+                                        row0 + x * BM, pol_once);
+            }
+            const int32_t* bt = p.block_tables + (int64_t)chunk * p.max_nb;
+            const int bps = BN / p.bs;
+            const uint32_t box = p.bs * 128;                    // bytes of one half-tile box
+            const int n_blk = (kv_hi + p.bs - 1) / p.bs;
+            // one 128-token K (kv = 0) or V (kv = 1) tile: two half-tile boxes per block
+            auto load_tile = [&](int it, int kv, int win) {
+                const uint32_t s = it % NSTAGE, ph = (it / NSTAGE) & 1;
+                b2::mbar_wait(bar((kv ? BAR_VE : BAR_KE) + s), ph ^ 1);
+                const int nb = min(bps, n_blk - it * bps);
+                const uint32_t dst0 = ring + s * STAGE_BYTES + kv * TILE_BYTES;
+                const uint32_t fb = bar((kv ? BAR_V : BAR_K) + s);
+                const CUtensorMap* tm = kv ? &tmV : &tmK;
+                if (lane == 0) b2::mbar_arrive_expect_tx(fb, nb * 2 * box);
+                for (int j = 0; j < bps; ++j) {         // bps divides 32: a tile never straddles a 32-entry window
+                    const int blk = __shfl_sync(0xffffffffu, win, (it * bps + j) & 31);
+                    if (j < nb && lane == 0) {
+                        b2::tma_load_5d(dst0 + j * box, tm, fb, 0, 0, 0, kvh, blk, pol_keep);
+                        b2::tma_load_5d(dst0 + SUB_BYTES + j * box, tm, fb, 0, 1, 0, kvh, blk, pol_keep);
+                    }
+                }
+            };
+            auto window = [&](int it) {                 // the 32 table entries that hold tile `it`
+                const int first = (it * bps) & ~31;
+                return first + lane < n_blk ? bt[first + lane] : 0;
+            };
+            // order of need: K(0) | K(1) V(0) | K(2) V(1) | ...
+            int wk = window(0), wv = wk;
+            load_tile(0, 0, wk);
+            for (int it = 0; it < n_tiles; ++it) {
+                if (it + 1 < n_tiles) {
+                    if ((((it + 1) * bps) & 31) == 0) wk = window(it + 1);
+                    load_tile(it + 1, 0, wk);
+                }
+                if (it > 0 && ((it * bps) & 31) == 0) wv = window(it);
+                load_tile(it, 1, wv);
+            }
+        }
+        else if (warp == 9) {
+            // ------------------------------------------ MMA issuer (one lane) ------------------------------------------
+            if (lane == 0) {
+                constexpr uint32_t ID_QK = idesc_bf16(128, 128, 0), ID_PV = idesc_bf16(128, 128, 1);
+                auto issue_qk = [&](int x, int j) {        // S_x = Q_x . K(j)^T : 8 k-steps of 16 over d
+                    const uint32_t kb = ring + (j % NSTAGE) * STAGE_BYTES, qb = q_smem + x * TILE_BYTES;
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {
+                        const uint32_t off = (kk >> 2) * SUB_BYTES + (kk & 3) * 32;
+                        mma_ss(tmem + x * 128, smem_desc(qb + off, 16, 1024), smem_desc(kb + off, 16, 1024), ID_QK, kk > 0);
+                    }
+                    mma_commit(bar(BAR_S + x));
+                };
+                b2::mbar_wait(bar(BAR_Q), 0);
+                b2::mbar_wait(bar(BAR_K + 0), 0);
+                tc_fence_after();
+                for (int x = 0; x < 2; ++x)
+                    if (nX[x] > 0) issue_qk(x, 0);
+                mma_commit(bar(BAR_KE + 0));                                   // K(0) consumed
+                for (int j = 0; j < n_tiles; ++j) {
+                    const uint32_t s = j % NSTAGE;
+                    const uint32_t vb = ring + s * STAGE_BYTES + TILE_BYTES;
+                    b2::mbar_wait(bar(BAR_V + s), (j / NSTAGE) & 1);
+                    if (j == n_tiles - 1) {
+                        // rows of the last stage past the sequence hold whatever the cache (or an older stage) held:
+                        // zero the ones the last 16-token k-step still reads, so 0 * NaN cannot reach an accumulator
+                        const int valid = kv_hi - j * BN;
+                        const int upto = min(BN, (valid + 15) & ~15);
+                        for (int r = valid; r < upto; ++r)
+                            for (int h = 0; h < 2; ++h)
+                                for (int c = 0; c < 8; ++c)
+                                    asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(vb + h * SUB_BYTES + r * 128 + c * 16), "r"(0) : "memory");
+                        b2::fence_proxy_async();
+                    }
+                    const bool more = j + 1 < n_tiles;
+                    if (more) b2::mbar_wait(bar(BAR_K + (j + 1) % NSTAGE), ((j + 1) / NSTAGE) & 1);
+                    for (int x = 0; x < 2; ++x) {
+                        if (j < nX[x]) {
+                            b2::mbar_wait(bar(BAR_P + x), j & 1);          // P_x(j) is in TMEM, O_x rescaled if needed
+                            tc_fence_after();
+                            const int ksteps = min(8, (hiX[x] - j * BN + 15) >> 4);
+                            for (int t = 0; t < ksteps; ++t)               // O_x += P_x . V(j) : k-steps of 16 tokens
+                                mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, smem_desc(vb + t * 2048, SUB_BYTES, 1024),
+                                       ID_PV, j > 0 || t > 0);
+                            mma_commit(bar(BAR_PV + x));
+                        }
+                        if (j + 1 < nX[x]) issue_qk(x, j + 1);
+                    }
+                    mma_commit(bar(BAR_VE + s));                            // V(j) consumed
+                    if (more) mma_commit(bar(BAR_KE + (j + 1) % NSTAGE));  // K(j+1) consumed (both tiles issued above)
+                }
+            }
+        }
+        else {
+            // ------------------------------------------ softmax warps: tile x = warp / 4 ------------------------------------------
+            const int x = warp >> 2, wq = warp & 3;
+            const int row = wq * 32 + lane;                       // query row in the tile = TMEM lane
+            const uint32_t lane_off = (uint32_t)(wq * 32) << 16;
+            const uint32_t s_addr = tmem + lane_off + x * 128, o_addr = tmem + lane_off + 256 + x * 128;
+            const int n = nX[x];
+            const float sl2 = p.scale_log2;
+            const int lim = start + q0 + x * BM + min(row, max(rowsX[x] - 1, 0));   // last key this row may see
+            const int lim_min = start + q0 + x * BM;                                 // ... of the tile's first row
+            float m = -INFINITY, l = 0.f;
+            for (int j = 0; j < n; ++j) {
+                b2::mbar_wait(bar(BAR_S + x), j & 1);
+                tc_fence_after();
+                uint32_t sr[4][32];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) tmem_ld32(s_addr + c * 32, sr[c]);
+                tmem_wait_ld();
+                const int j0 = j * BN;
+                if (j0 + BN - 1 > lim_min) {                      // tile touches the diagonal (or the end of the sequence)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (j0 + c * 32 + i > lim) sr[c][i] = 0xff800000u;   // -inf
+                }
+                float mx = -INFINITY;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(sr[c][i]));
+                const float m_new = fmaxf(m, mx);                 // finite: key 0 is visible to every row, tiles in order
+                if (j == 0) {
+                    m = m_new;
+                } else {
+                    const bool need = (m_new - m) * sl2 > RESCALE_THRESHOLD;
+                    if (__any_sync(0xffffffffu, need)) {          // rare after the first tiles: bring O_x to the new maximum
+                        b2::mbar_wait(bar(BAR_PV + x), (j - 1) & 1);
+                        tc_fence_after();
+                        const float alpha = need ? b2::fast_exp2((m - m_new) * sl2) : 1.f;
+                        if (need) { m = m_new; l *= alpha; }
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            uint32_t orr[32];
+                            tmem_ld32(o_addr + c * 32, orr);
+                            tmem_wait_ld();
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) orr[i] = __float_as_uint(__uint_as_float(orr[i]) * alpha);
+                            tmem_st32(o_addr + c * 32, orr);
+                        }
+                    }
+                }
+                const float ms = m * sl2;
+                float sum = 0.f;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {                     // 64 keys -> 32 packed bf16 pairs per store
+                    uint32_t pk[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int cc = 2 * c + (i >> 4), ii = (2 * i) & 31;
+                        const float p0 = b2::fast_exp2(fmaf(__uint_as_float(sr[cc][ii]), sl2, -ms));
+                        const float p1 = b2::fast_exp2(fmaf(__uint_as_float(sr[cc][ii + 1]), sl2, -ms));
+                        pk[i] = b2::pack_bf16x2(p0, p1);
+                        sum += __uint_as_float(pk[i] << 16) + __uint_as_float(pk[i] & 0xffff0000u);   // the rounded weights
+                    }
+                    tmem_st32(s_addr + c * 32, pk);               // P overwrites the first 64 columns of S_x
+                }
+                l += sum;
+                tmem_wait_st();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) b2::mbar_arrive(bar(BAR_P + x));
+            }
+            if (n > 0) {
+                b2::mbar_wait(bar(BAR_PV + x), (n - 1) & 1);
+                tc_fence_after();
+                const float inv = 1.f / l;
+                const bool valid = row < rowsX[x];
+                __nv_bfloat16* orow = p.out + (int64_t)(row0 + x * BM + row) * p.out_stride + (int64_t)hq * D;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t orr[32];
+                    tmem_ld32(o_addr + c * 32, orr);
+                    tmem_wait_ld();
+                    if (valid) {
+#pragma unroll
+                        for (int i = 0; i < 32; i += 8) {
+                            int4 v;
+                            v.x = (int)b2::pack_bf16x2(__uint_as_float(orr[i]) * inv, __uint_as_float(orr[i + 1]) * inv);
+                            v.y = (int)b2::pack_bf16x2(__uint_as_float(orr[i + 2]) * inv, __uint_as_float(orr[i + 3]) * inv);
+                            v.z = (int)b2::pack_bf16x2(__uint_as_float(orr[i + 4]) * inv, __uint_as_float(orr[i + 5]) * inv);
+                            v.w = (int)b2::pack_bf16x2(__uint_as_float(orr[i + 6]) * inv, __uint_as_float(orr[i + 7]) * inv);
+                            *reinterpret_cast<int4*>(orow + c * 32 + i) = v;
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    // ------------------------------------------ teardown ------------------------------------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
+}  // namespace
+
+int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const void* v_cache,
+                            const int32_t* block_tables, const int32_t* cu_q, const int32_t* ctx_start, int n_chunks,
+                            int T, int Hq, int Hkv, int bs, int max_nb, int64_t num_blocks, int64_t q_stride,
+                            int64_t out_stride, int64_t cache_block_stride, int64_t cache_head_stride, float scale,
+                            void* stream) {
+    const int64_t n_qtiles = (int64_t)T / (2 * BM) + n_chunks;          // upper bound of sum ceil(len_c / 256)
+    B2_REQUIRE(n_qtiles <= 65535, B2_EUNSUPPORTED, "prefill_attention: %lld q tiles exceed the grid", (long long)n_qtiles);
+    B2_REQUIRE(bs <= 64 && BN % bs == 0, B2_EUNSUPPORTED, "prefill_attention: block_size %d", bs);
+
+    CUtensorMap tmQ, tmK, tmV;
+    {   // q viewed as [T][Hq][2 halves][64]: one box = 128 rows x one 64-element half of one head
+        const uint64_t dims[4] = {64, 2, (uint64_t)Hq, (uint64_t)T};
+        const uint64_t strides[3] = {128, 256, (uint64_t)q_stride * 2};
+        const uint32_t box[4] = {64, 1, 1, (uint32_t)BM};
+        int rc = b2_internal_encode_bf16_sw128(&tmQ, q, 4, dims, strides, box);
+        if (rc != B2_OK) return rc;
+    }
+    for (int kv = 0; kv < 2; ++kv) {   // cache viewed as [num_blocks][Hkv][bs][2 halves][64]: one box = bs rows x one half
+        const uint64_t dims[5] = {64, 2, (uint64_t)bs, (uint64_t)Hkv, (uint64_t)num_blocks};
+        const uint64_t strides[4] = {128, 256, (uint64_t)cache_head_stride * 2, (uint64_t)cache_block_stride * 2};
+        const uint32_t box[5] = {64, 1, (uint32_t)bs, 1, 1};
+        int rc = b2_internal_encode_bf16_sw128(kv ? &tmV : &tmK, kv ? v_cache : k_cache, 5, dims, strides, box);
+        if (rc != B2_OK) return rc;
+    }
+    Tc5Params p;
+    p.out = static_cast<__nv_bfloat16*>(out);
+    p.block_tables = block_tables;
+    p.cu_q = cu_q;
+    p.ctx_start = ctx_start;
+    p.n_chunks = n_chunks;
+    p.Hq = Hq;
+    p.G = Hq / Hkv;
+    p.bs = bs;
+    p.max_nb = max_nb;
+    p.out_stride = out_stride;
+    p.scale_log2 = scale * LOG2E;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B2_CUDA_OK(cudaFuncSetAttribute(prefill_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        attr_set = true;
+    }
+    prefill_tc5_kernel<<<dim3(Hq, (unsigned)n_qtiles), NTHREADS, SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(tmQ, tmK, tmV, p);
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}
