@@ -46,6 +46,7 @@ struct Tc5Params {
     const int32_t* cu_q;
     const int32_t* ctx_start;
     int n_chunks, Hq, G, bs, max_nb;
+    int rows_per_cta;      // 256 (tiles A and B) or 128 (tile A only: small batches fill the 148 SMs better)
     int64_t out_stride;
     float scale_log2;
 };
@@ -126,8 +127,8 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         int want = (int)(gridDim.y - 1 - blockIdx.y), found = -1, q0 = 0;
         for (int c = 0; c < p.n_chunks; ++c) {
             const int len = p.cu_q[c + 1] - p.cu_q[c];
-            const int nt = (len + 2 * BM - 1) / (2 * BM);
-            if (want < nt) { found = c; q0 = want * 2 * BM; break; }
+            const int nt = (len + p.rows_per_cta - 1) / p.rows_per_cta;
+            if (want < nt) { found = c; q0 = want * p.rows_per_cta; break; }
             want -= nt;
         }
         s_tile[0] = found;
@@ -160,7 +161,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int q0 = s_tile[1], len = s_tile[2], start = s_tile[3];
 
     if (chunk >= 0) {
-        const int rows = min(2 * BM, len - q0);                 // valid query rows of the CTA
+        const int rows = min(p.rows_per_cta, len - q0);         // valid query rows of the CTA
         const int rowsX[2] = {min(BM, rows), max(0, rows - BM)};
         // keys [0, hiX) are visible to the last row of tile X; tiles of 128 keys
         const int hiX[2] = {start + q0 + rowsX[0], rowsX[1] ? start + q0 + BM + rowsX[1] : 0};
@@ -392,7 +393,10 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
                             int T, int Hq, int Hkv, int bs, int max_nb, int64_t num_blocks, int64_t q_stride,
                             int64_t out_stride, int64_t cache_block_stride, int64_t cache_head_stride, float scale,
                             void* stream) {
-    const int64_t n_qtiles = (int64_t)T / (2 * BM) + n_chunks;          // upper bound of sum ceil(len_c / 256)
+    // 256 query rows per CTA share each K/V stage between two tiles; when that leaves SMs idle, 128 rows per CTA
+    static const int n_sm = []() { int dev = 0, n = 148; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); return n; }();
+    const int rows_per_cta = ((int64_t)T / (2 * BM) + n_chunks) * Hq < n_sm ? BM : 2 * BM;      // less than one wave
+    const int64_t n_qtiles = (int64_t)T / rows_per_cta + n_chunks;        // upper bound of sum ceil(len_c / rows_per_cta)
     B2_REQUIRE(n_qtiles <= 65535, B2_EUNSUPPORTED, "prefill_attention: %lld q tiles exceed the grid", (long long)n_qtiles);
     B2_REQUIRE(bs <= 64 && BN % bs == 0, B2_EUNSUPPORTED, "prefill_attention: block_size %d", bs);
 
@@ -421,6 +425,7 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
     p.G = Hq / Hkv;
     p.bs = bs;
     p.max_nb = max_nb;
+    p.rows_per_cta = rows_per_cta;
     p.out_stride = out_stride;
     p.scale_log2 = scale * LOG2E;
     static bool attr_set = false;
