@@ -45,7 +45,8 @@ WORKLOADS = {
     "llama3-70b_b256_ctx8k_bf16kv": dict(B=256, Hq=64, Hkv=8, ctx=8192, fp8=False),  # BASELINE configs[3]
     "oracle_b4_ctx512": dict(B=4, Hq=8, Hkv=2, ctx=512, fp8=False),                 # BASELINE configs[0]
 }
-D, BS = 128, 16
+D = 128
+BS = int(os.environ.get("B2_BENCH_BLOCK_SIZE", "16"))   # BASELINE fixes 16; other sizes are experiments only
 
 
 def algorithmic_bytes(B, Hq, Hkv, ctx, kv_bytes):

@@ -41,11 +41,12 @@ def build_caches(inp, dev, fp8=False, poison=False):
     if fp8:
         ks = float(inp["k"].float().abs().max()) / 448.0
         vs = float(inp["v"].float().abs().max()) / 448.0
-        kc_ref = torch.zeros(shape, dtype=torch.uint8)
-        vc_ref = torch.zeros(shape, dtype=torch.uint8)
+        fill8 = 0x7F if poison else 0     # 0x7f is the e4m3 NaN
+        kc_ref = torch.full(shape, fill8, dtype=torch.uint8)
+        vc_ref = torch.full(shape, fill8, dtype=torch.uint8)
         R.reshape_and_cache_ref(inp["k"], inp["v"], kc_ref, vc_ref, inp["slot_mapping"], R.KV_FP8_E4M3, ks, vs)
-        kc = torch.zeros(shape, dtype=torch.uint8, device=dev)
-        vc = torch.zeros(shape, dtype=torch.uint8, device=dev)
+        kc = torch.full(shape, fill8, dtype=torch.uint8, device=dev)
+        vc = torch.full(shape, fill8, dtype=torch.uint8, device=dev)
         ksd = torch.tensor([ks], dtype=torch.float32, device=dev)
         vsd = torch.tensor([vs], dtype=torch.float32, device=dev)
         b200attn.reshape_and_cache(inp["k"].to(dev), inp["v"].to(dev), kc, vc, inp["slot_mapping"].to(dev), ksd, vsd)
@@ -236,6 +237,47 @@ def test_decode_fp8(cuda, Hq, Hkv, splits):
     ref = R.paged_decode_ref(inp["q"], kb, vb, inp["block_tables"], inp["seq_lens"], return_f32=True)
     out = run_decode(inp, kc, vc, cuda, k_scale=ksd, v_scale=vsd)
     assert_close(out, ref, atol=5e-2, rtol=1e-1, what="fp8 vs unquantised oracle")
+
+
+@pytest.mark.parametrize("bs", [8, 16, 32])
+@pytest.mark.parametrize("splits", [0, 1, 3])
+def test_decode_fp8_block_sizes_and_edge_lengths(cuda, bs, splits):
+    """fp8 cache: seq_len 0, 1, around block, warp-slab (32-token) and stage (128-token) boundaries; untouched
+    cache bytes are the e4m3 NaN (0x7f), so a read past seq_len that reaches an MMA gives a non-finite row."""
+    lens = [0, 1, bs - 1, bs, bs + 1, 31, 32, 33, 63, 64, 65, 127, 128, 129, 255, 257, 300]
+    B = len(lens)
+    inp = R.make_inputs(B, 8, 2, 128, bs, 320, seed=40 + bs + splits)
+    sl = torch.tensor(lens, dtype=torch.int32)
+    keep = torch.cat([torch.arange(320 * b, 320 * b + lens[b]) for b in range(B)])
+    inp["k"], inp["v"], inp["slot_mapping"] = inp["k"][keep], inp["v"][keep], inp["slot_mapping"][keep]
+    inp["seq_lens"] = sl
+    kc, vc, kc_ref, vc_ref, (ks, vs, ksd, vsd) = build_caches(inp, cuda, fp8=True, poison=True)
+    assert torch.equal(kc.cpu(), kc_ref) and torch.equal(vc.cpu(), vc_ref)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], sl,
+                             kv_dtype=R.KV_FP8_E4M3, k_scale=ks, v_scale=vs, return_f32=True)
+    out = run_decode(inp, kc, vc, cuda, k_scale=ksd, v_scale=vsd, num_splits=splits)
+    assert torch.all(out[0] == 0), "seq_len 0 must give a zero row"
+    assert_close(out, ref, what=f"fp8 bs={bs} splits={splits}")
+
+
+@pytest.mark.parametrize("qmul", [2.0 ** -12, 1.0, 37.0, 2.0 ** 9])
+def test_decode_fp8_q_range(cuda, qmul):
+    """The fp8 path feeds q to the e4m3 MMA as two terms after a per-head power-of-two scaling: q rows of very
+    different magnitude (and one all-zero head) must come out as with exact bf16 q.  The softmax scale is
+    divided by the same factor so that the scores stay O(1)."""
+    inp = R.make_inputs(3, 16, 2, 128, 16, 500, seed=77, ragged=True)
+    qf = inp["q"].float() * qmul
+    qf[:, 3] *= 1e-3           # heads of one group with unlike ranges
+    qf[:, 5] = 0.0
+    qf[:, 9] *= 50.0
+    inp["q"] = qf.to(torch.bfloat16)
+    scale = 128 ** -0.5 / qmul
+    kc, vc, kc_ref, vc_ref, (ks, vs, ksd, vsd) = build_caches(inp, cuda, fp8=True)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], scale=scale,
+                             kv_dtype=R.KV_FP8_E4M3, k_scale=ks, v_scale=vs, return_f32=True)
+    for splits in (0, 1, 2):
+        out = run_decode(inp, kc, vc, cuda, k_scale=ksd, v_scale=vsd, num_splits=splits, scale=scale)
+        assert_close(out, ref, atol=4e-3, rtol=2e-2, what=f"fp8 q x{qmul} splits={splits}")
 
 
 # ------------------------------------------------------------------------------------------

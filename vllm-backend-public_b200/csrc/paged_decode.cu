@@ -93,6 +93,10 @@ struct Cfg {
     static constexpr int QROW_BYTES = D * 2;
     static constexpr int QBUF_BYTES = QSMEM ? HEADS * QROW_BYTES : 0;
     static constexpr int DYN_SMEM_BYTES = SMEM_BYTES + META_BYTES + PRE_BYTES + NSTAGE * QBUF_BYTES;
+    // fp8 does twice the tokens (MMA + softmax + e4m3->f16 conversion) per byte: its consumers, not HBM, set the pace
+    // with 8 consumer warps per SM, so the shallow-ring variants run three CTAs per SM (12 consumer warps).
+    static constexpr int CTAS_SPLIT = (FP8 && 3 * (SMEM_BYTES + 1024) <= 233472) ? 3 : 2;
+    static constexpr int CTAS_DYN = (FP8 && 3 * (DYN_SMEM_BYTES + 1024) <= 233472) ? 3 : 2;
     static_assert(TOK % BS == 0 && BS % 8 == 0, "block size must divide the stage and keep the swizzle phase");
     static_assert(RING_BYTES % 1024 == 0, "stages must stay 1024-byte aligned");
     static_assert(2 * (SMEM_BYTES + 1024) <= 233472, "two CTAs per SM must fit");
@@ -102,6 +106,12 @@ struct Cfg {
 __device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t v) {
     uint32_t r;
     asm("{\n\t.reg .b16 lo;\n\tcvt.u16.u32 lo, %1;\n\tcvt.rn.f16x2.e4m3x2 %0, lo;\n\t}" : "=r"(r) : "r"(v));
+    return r;
+}
+// same for the high 16 bits of `v` (SASS: F2FP...UNPACK_B Rx.H1 -- no shift instruction)
+__device__ __forceinline__ uint32_t e4m3x2_hi_to_f16x2(uint32_t v) {
+    uint32_t r;
+    asm("{\n\t.reg .b16 lo, hi;\n\tmov.b32 {lo, hi}, %1;\n\tcvt.rn.f16x2.e4m3x2 %0, hi;\n\t}" : "=r"(r) : "r"(v));
     return r;
 }
 __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
@@ -254,70 +264,67 @@ struct WarpAcc {
     }
 };
 
-// Q^T as the B operand of S^T = K.Q^T: b0 = Q[head g][k-pair], b1 = the +8 pair.
+// Q^T as the B operand of S^T = K.Q^T: r[nt][kc] = {Q[head g][k-pair], the +8 pair}.
 // bf16: logical k == physical d.  fp8: ldmatrix hands each thread 4 consecutive fp8 of a 16-element
 // chunk, so logical k = 2*t4+{0,1} <-> d = 16kc + 4*t4 + {0,1} and the +8 pair <-> d = 16kc + 4*t4 + {2,3};
 // the contraction is permutation invariant.
-template <bool FP8, int NT>
-__device__ __forceinline__ void load_q_frags(uint32_t (&qf)[NT][8][2], const __nv_bfloat16* __restrict__ qbase,
-                                             int nheads, int lane) {
-    const int g = lane >> 2, t4 = lane & 3;
-#pragma unroll
-    for (int nt = 0; nt < NT; ++nt) {
-        const int hl = nt * 8 + g;
-        const bool valid = hl < nheads;
-        const uint32_t* qrow = reinterpret_cast<const uint32_t*>(qbase + (int64_t)(valid ? hl : 0) * D);
-#pragma unroll
-        for (int kc = 0; kc < 8; ++kc) {
-            uint32_t w0, w1;
-            if (!FP8) {
-                w0 = qrow[kc * 8 + t4];
-                w1 = qrow[kc * 8 + 4 + t4];
-            } else {
-                w0 = qrow[kc * 8 + 2 * t4];
-                w1 = qrow[kc * 8 + 2 * t4 + 1];
-                // bf16x2 -> f16x2 (the fp8 path runs the f16 MMA; see DESIGN.md on range)
-                w0 = pack_f16x2(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u));
-                w1 = pack_f16x2(__uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
-            }
-            qf[nt][kc][0] = valid ? w0 : 0u;
-            qf[nt][kc][1] = valid ? w1 : 0u;
-        }
-    }
-}
+// The fp8 path runs the f16 MMA (K and V convert exactly), so q becomes f16: each q row is first scaled by a power
+// of two that puts its largest |element| into [128, 256) -- exact for bf16 values down to 2^-21 of the row maximum,
+// whatever the magnitude of q.  hs[nt][j] = the inverse factor of head 2t4 + j, applied to this thread's score columns.
+template <int NT>
+struct QFrags {
+    uint32_t r[NT][8][2];
+    float hs[NT][2];
+};
 
-// same fragments, read from the q rows staged in shared memory ([head][D] bf16, heads >= nheads are garbage)
+// qbase: [head][D/2] words in global or shared memory; rows >= nheads are never read.
 template <bool FP8, int NT>
-__device__ __forceinline__ void load_q_frags_smem(uint32_t (&qf)[NT][8][2], const uint32_t* qsm, int nheads, int lane) {
+__device__ __forceinline__ void load_q_frags(QFrags<NT>& qf, const uint32_t* qbase, int nheads, int lane) {
     const int g = lane >> 2, t4 = lane & 3;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
         const int hl = nt * 8 + g;
         const bool valid = hl < nheads;
-        const uint32_t* qrow = qsm + hl * (D / 2);
+        const uint32_t* qrow = qbase + (valid ? hl : 0) * (D / 2);
+        if (!FP8) {
 #pragma unroll
-        for (int kc = 0; kc < 8; ++kc) {
-            uint32_t w0 = 0u, w1 = 0u;
-            if (valid) {
-                if (!FP8) {
-                    w0 = qrow[kc * 8 + t4];
-                    w1 = qrow[kc * 8 + 4 + t4];
-                } else {
-                    w0 = qrow[kc * 8 + 2 * t4];
-                    w1 = qrow[kc * 8 + 2 * t4 + 1];
-                    w0 = pack_f16x2(__uint_as_float(w0 << 16), __uint_as_float(w0 & 0xffff0000u));
-                    w1 = pack_f16x2(__uint_as_float(w1 << 16), __uint_as_float(w1 & 0xffff0000u));
-                }
+            for (int kc = 0; kc < 8; ++kc) {
+                const uint32_t w0 = qrow[kc * 8 + t4], w1 = qrow[kc * 8 + 4 + t4];
+                qf.r[nt][kc][0] = valid ? w0 : 0u;
+                qf.r[nt][kc][1] = valid ? w1 : 0u;
             }
-            qf[nt][kc][0] = w0;
-            qf[nt][kc][1] = w1;
+            qf.hs[nt][0] = qf.hs[nt][1] = 1.f;
+        } else {
+            uint2 w[8];
+            float amax = 0.f;
+#pragma unroll
+            for (int kc = 0; kc < 8; ++kc) {
+                w[kc] = *reinterpret_cast<const uint2*>(qrow + kc * 8 + 2 * t4);
+                if (!valid) w[kc] = make_uint2(0u, 0u);
+                amax = fmaxf(amax, fmaxf(fabsf(__uint_as_float(w[kc].x << 16)), fabsf(__uint_as_float(w[kc].x & 0xffff0000u))));
+                amax = fmaxf(amax, fmaxf(fabsf(__uint_as_float(w[kc].y << 16)), fabsf(__uint_as_float(w[kc].y & 0xffff0000u))));
+            }
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));   // the four lanes of one g hold one head
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            // exponent field clamped so that both factors are normal floats
+            uint32_t ef = (__float_as_uint(amax) >> 23) & 0xffu;
+            ef = ef < 16u ? 16u : (ef > 240u ? 240u : ef);
+            const float up = __uint_as_float((261u - ef) << 23);     // 2^(7 - (ef - 127))
+            const float down = __uint_as_float((ef - 7u) << 23);     // 2^((ef - 127) - 7)
+#pragma unroll
+            for (int kc = 0; kc < 8; ++kc) {
+                qf.r[nt][kc][0] = pack_f16x2(__uint_as_float(w[kc].x << 16) * up, __uint_as_float(w[kc].x & 0xffff0000u) * up);
+                qf.r[nt][kc][1] = pack_f16x2(__uint_as_float(w[kc].y << 16) * up, __uint_as_float(w[kc].y & 0xffff0000u) * up);
+            }
+            qf.hs[nt][0] = __shfl_sync(0xffffffffu, down, 8 * t4);       // lane 4 * (2t4)     holds head 2t4
+            qf.hs[nt][1] = __shfl_sync(0xffffffffu, down, 8 * t4 + 4);   // lane 4 * (2t4 + 1) holds head 2t4 + 1
         }
     }
 }
 
 // One warp, one stage: 16 token rows [row_base, row_base+16) of which the first `nvalid` are real.
 template <class C, bool FP8, int NT>
-__device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&qf)[NT][8][2], uint32_t kbase,
+__device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const QFrags<NT>& qf, uint32_t kbase,
                                              uint32_t vbase, int row_base, int nvalid, float sl2, int lane) {
     const int g = lane >> 2, t4 = lane & 3;
     const int mi = lane >> 3, ri = lane & 7;   // ldmatrix: lane -> (matrix, row)
@@ -336,7 +343,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
             uint32_t a0, a1, a2, a3;
             b2::ldmatrix_x4(addr, a0, a1, a2, a3);
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) mma_kv<FP8>(sacc[nt], a0, a1, a2, a3, qf[nt][kc][0], qf[nt][kc][1]);
+            for (int nt = 0; nt < NT; ++nt) mma_kv<FP8>(sacc[nt], a0, a1, a2, a3, qf.r[nt][kc][0], qf.r[nt][kc][1]);
         }
     } else {
         // fp8 rows are 128 bytes = 8 chunks of 16 elements; one ldmatrix.x4 covers two k-chunks:
@@ -349,14 +356,19 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
             uint32_t r0, r1, r2, r3;
             b2::ldmatrix_x4(addr, r0, r1, r2, r3);
             const uint32_t a0 = e4m3x2_to_f16x2(r0), a1 = e4m3x2_to_f16x2(r1);
-            const uint32_t a2 = e4m3x2_to_f16x2(r0 >> 16), a3 = e4m3x2_to_f16x2(r1 >> 16);
+            const uint32_t a2 = e4m3x2_hi_to_f16x2(r0), a3 = e4m3x2_hi_to_f16x2(r1);
             const uint32_t c0 = e4m3x2_to_f16x2(r2), c1 = e4m3x2_to_f16x2(r3);
-            const uint32_t c2 = e4m3x2_to_f16x2(r2 >> 16), c3 = e4m3x2_to_f16x2(r3 >> 16);
+            const uint32_t c2 = e4m3x2_hi_to_f16x2(r2), c3 = e4m3x2_hi_to_f16x2(r3);
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
-                mma_kv<FP8>(sacc[nt], a0, a1, a2, a3, qf[nt][2 * kc2][0], qf[nt][2 * kc2][1]);
-                mma_kv<FP8>(sacc[nt], c0, c1, c2, c3, qf[nt][2 * kc2 + 1][0], qf[nt][2 * kc2 + 1][1]);
+                mma_kv<FP8>(sacc[nt], a0, a1, a2, a3, qf.r[nt][2 * kc2][0], qf.r[nt][2 * kc2][1]);
+                mma_kv<FP8>(sacc[nt], c0, c1, c2, c3, qf.r[nt][2 * kc2 + 1][0], qf.r[nt][2 * kc2 + 1][1]);
             }
+        }
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {   // back to raw score units (q rows were scaled per head)
+            sacc[nt][0] *= qf.hs[nt][0]; sacc[nt][1] *= qf.hs[nt][1];
+            sacc[nt][2] *= qf.hs[nt][0]; sacc[nt][3] *= qf.hs[nt][1];
         }
     }
     // sacc[nt] = {S[tok g][head 2t4], S[tok g][2t4+1], S[tok g+8][2t4], S[tok g+8][2t4+1]}
@@ -447,10 +459,14 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
             b2::ldmatrix_x4_trans(addr, r0, r1, r2, r3);
             r0 = __byte_perm(r0, 0, 0x3120); r1 = __byte_perm(r1, 0, 0x3120);
             r2 = __byte_perm(r2, 0, 0x3120); r3 = __byte_perm(r3, 0, 0x3120);
-            const uint32_t a0 = e4m3x2_to_f16x2(r0) & mk_lo, a1 = e4m3x2_to_f16x2(r0 >> 16) & mk_lo;
-            const uint32_t a2 = e4m3x2_to_f16x2(r1) & mk_hi, a3 = e4m3x2_to_f16x2(r1 >> 16) & mk_hi;
-            const uint32_t c0 = e4m3x2_to_f16x2(r2) & mk_lo, c1 = e4m3x2_to_f16x2(r2 >> 16) & mk_lo;
-            const uint32_t c2 = e4m3x2_to_f16x2(r3) & mk_hi, c3 = e4m3x2_to_f16x2(r3 >> 16) & mk_hi;
+            uint32_t a0 = e4m3x2_to_f16x2(r0), a1 = e4m3x2_hi_to_f16x2(r0);
+            uint32_t a2 = e4m3x2_to_f16x2(r1), a3 = e4m3x2_hi_to_f16x2(r1);
+            uint32_t c0 = e4m3x2_to_f16x2(r2), c1 = e4m3x2_hi_to_f16x2(r2);
+            uint32_t c2 = e4m3x2_to_f16x2(r3), c3 = e4m3x2_hi_to_f16x2(r3);
+            if (nvalid < 16) {   // warp-uniform; full slabs (all but a sequence's last) skip the eight ANDs
+                a0 &= mk_lo; a1 &= mk_lo; a2 &= mk_hi; a3 &= mk_hi;
+                c0 &= mk_lo; c1 &= mk_lo; c2 &= mk_hi; c3 &= mk_hi;
+            }
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
                 mma_kv<FP8>(acc.o[nt][2 * dt2], a0, a1, a2, a3, pb[nt][0], pb[nt][1]);
@@ -462,7 +478,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const uint32_t (&
 
 // Consume the stages of one segment (n_tok tokens starting at a block boundary).
 template <class C, bool FP8, int NT, int NSTAGE>
-__device__ __forceinline__ void consume_segment(WarpAcc<NT>& acc, const uint32_t (&qf)[NT][8][2], int n_tok,
+__device__ __forceinline__ void consume_segment(WarpAcc<NT>& acc, const QFrags<NT>& qf, int n_tok,
                                                 uint32_t ring, uint32_t bar_full, uint32_t bar_empty,
                                                 uint32_t& it, float sl2, int warp, int lane) {
     const int n_stage = (n_tok + TOK - 1) / TOK;
@@ -544,7 +560,7 @@ __device__ __forceinline__ void init_pipeline(uint32_t bar_full, uint32_t bar_em
 // schedule A: classic grid split, one CTA per (split, kv head x head group, sequence)
 // =============================================================================================
 template <int BS, bool FP8, int NT, int NSTAGE>
-__global__ void __launch_bounds__(NTHREADS, 2)
+__global__ void __launch_bounds__(NTHREADS, (Cfg<BS, FP8, NT, NSTAGE>::CTAS_SPLIT))
 paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                           const DecodeParams p) {
     using C = Cfg<BS, FP8, NT, NSTAGE>;
@@ -596,8 +612,8 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
             sl2 *= *p.k_scale;   // K dequant scale folds into the softmax scale
             vs = *p.v_scale;     // V dequant scale folds into the epilogue
         }
-        uint32_t qf[NT][8][2];
-        load_q_frags<FP8, NT>(qf, p.q + b * p.q_stride + (int64_t)head0 * D, nheads, lane);
+        QFrags<NT> qf;
+        load_q_frags<FP8, NT>(qf, reinterpret_cast<const uint32_t*>(p.q + b * p.q_stride + (int64_t)head0 * D), nheads, lane);
         WarpAcc<NT> acc;
         acc.reset();
         consume_segment<C, FP8, NT, NSTAGE>(acc, qf, n_tok, ring, bar_full, bar_empty, it, sl2, warp, lane);
@@ -821,11 +837,11 @@ __device__ __forceinline__ void merge_item(__nv_bfloat16* __restrict__ out_rows,
 }
 
 template <int BS, bool FP8, int NT, int NSTAGE>
-__global__ void __launch_bounds__(NTHREADS, 2)
+__global__ void __launch_bounds__(NTHREADS, (Cfg<BS, FP8, NT, NSTAGE>::CTAS_DYN))
 paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                             const DecodeParams p) {
     using C = Cfg<BS, FP8, NT, NSTAGE>;
-    static_assert(2 * (C::DYN_SMEM_BYTES + 1024) <= 233472, "two CTAs per SM must fit (dynamic schedule)");
+    static_assert(C::CTAS_DYN * (C::DYN_SMEM_BYTES + 1024) <= 233472, "the CTAs of one SM must fit (dynamic schedule)");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     int4* s_meta = reinterpret_cast<int4*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
     float* scratch = reinterpret_cast<float*>(smem_raw + C::RING_BYTES + C::BAR_BYTES + C::META_BYTES);
@@ -979,11 +995,13 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
         }
         WarpAcc<NT> acc;
         acc.reset();
-        uint32_t qf[NT][8][2];
+        QFrags<NT> qf;
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
+        for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
-            for (int kc = 0; kc < 8; ++kc) qf[nt][kc][0] = qf[nt][kc][1] = 0u;
+            for (int kc = 0; kc < 8; ++kc) qf.r[nt][kc][0] = qf.r[nt][kc][1] = 0u;
+            qf.hs[nt][0] = qf.hs[nt][1] = 1.f;
+        }
         int cb = 0, head0 = 0, nheads = 0;
         const int row_base = warp * 16;
         for (;; ++it) {
@@ -1003,9 +1021,10 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
                 head0 = kvh * p.G + hg * C::HEADS;
                 nheads = min(C::HEADS, p.G - hg * C::HEADS);
                 if (C::QSMEM)
-                    load_q_frags_smem<FP8, NT>(qf, reinterpret_cast<const uint32_t*>(s_q + s * C::QBUF_BYTES), nheads, lane);
+                    load_q_frags<FP8, NT>(qf, reinterpret_cast<const uint32_t*>(s_q + s * C::QBUF_BYTES), nheads, lane);
                 else
-                    load_q_frags<FP8, NT>(qf, p.q + cb * p.q_stride + (int64_t)head0 * D, nheads, lane);
+                    load_q_frags<FP8, NT>(qf, reinterpret_cast<const uint32_t*>(p.q + cb * p.q_stride + (int64_t)head0 * D),
+                                          nheads, lane);
                 acc.reset();
             }
             const int nvalid = m.z - row_base;
@@ -1129,13 +1148,22 @@ int make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t nu
     return B2_OK;
 }
 
-int persistent_grid() {
-    static int n = []() {
-        int dev = 0, sms = 148;
-        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        return 2 * sms;   // two resident CTAs per SM (shared-memory bound)
+int env_int(const char* name, int dflt) {
+    const char* s = getenv(name);
+    return (s && *s) ? atoi(s) : dflt;
+}
+
+// resident CTAs per SM (shared-memory bound): 2, or 3 for the shallow-ring fp8 variants (B2_FP8_CTAS=2 for A/B runs)
+// (G > 8 serves 16 q heads per CTA: its accumulators do not fit the 128-register budget of three CTAs)
+int ctas_per_sm(bool fp8, int G) { return fp8 && G <= 8 && env_int("B2_FP8_CTAS", 3) == 3 ? 3 : 2; }
+
+int persistent_grid(int per_sm) {
+    static int sms = []() {
+        int dev = 0, n = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        return n;
     }();
-    return n;
+    return per_sm * sms;
 }
 
 struct Plan {
@@ -1147,17 +1175,14 @@ struct Plan {
     int static_pct;    // dynamic: share of the chunks dealt out statically
     int64_t slots;     // dynamic: partial slots in the workspace
     int ipb;           // items per sequence = Hkv * hg
+    int nc;            // dynamic: CTAs of the persistent grid the plan was made for
 };
 
 // dynamic schedule: workspace header (claim counter)
 size_t ws_header_bytes(int, int) { return 256; }
 
-int env_int(const char* name, int dflt) {
-    const char* s = getenv(name);
-    return (s && *s) ? atoi(s) : dflt;
-}
-
-void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_splits) {
+// per_sm: CTAs per SM of the kernel that will run (3 also bounds the workspace of every variant from above)
+void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_splits, int per_sm) {
     pl->nt = G <= 8 ? 1 : 2;
     const int hpc = 8 * pl->nt;
     pl->hg = (G + hpc - 1) / hpc;
@@ -1167,10 +1192,11 @@ void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_spli
     pl->static_pct = 0;
     pl->slots = 0;
     pl->ipb = Hkv * pl->hg;
+    pl->nc = 0;
     const int64_t max_ctx = (int64_t)max_nb * bs;
     if (num_splits <= 0) {
         // diagnostic overrides, read per call (cheap): B2_CHUNK_TOKENS, B2_STATIC_PCT
-        const int NC = persistent_grid();
+        const int NC = persistent_grid(per_sm);
         const int ipb = Hkv * pl->hg;
         const int ct_max = bs * 32 < 512 ? bs * 32 : 512;   // <= 32 blocks per chunk
         // aim for >= 8 chunks per CTA (run boundaries cost more than a slightly longer tail), within [64, ct_max] tokens
@@ -1182,6 +1208,7 @@ void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_spli
         int pct = env_int("B2_STATIC_PCT", 85);
         pct = pct < 0 ? 0 : (pct > 100 ? 100 : pct);
         pl->chunk_tokens = ct;
+        pl->nc = NC;
         pl->static_pct = pct;
         const int64_t ctot_max = (int64_t)B * ipb * ((max_ctx + ct - 1) / ct);
         pl->slots = 2 * (int64_t)NC + ctot_max * (100 - pct) / 100 + NC + 2;
@@ -1202,13 +1229,13 @@ size_t plan_workspace(const Plan& pl, int B, int Hq) {
     return (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
 }
 
-template <int BS, bool FP8, int NT>
+// NSTAGE / NSTAGE_D: ring depth of the grid-split / dynamic kernel.  bf16: 3 x 32 KiB, two CTAs per SM.
+// fp8 (16 KiB stages): 4 / 3 stages with three CTAs per SM (default), or 6 / 5 with two.
+template <int BS, bool FP8, int NT, int NSTAGE, int NSTAGE_D>
 int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, const Plan& pl,
                   cudaStream_t st) {
-    constexpr int NSTAGE = FP8 ? 6 : 3;
     using C = Cfg<BS, FP8, NT, NSTAGE>;
     if (pl.num_splits == 0) {
-        constexpr int NSTAGE_D = FP8 ? 5 : 3;   // fp8: one 16 KiB stage gives way to the per-stage q buffers
         using C = Cfg<BS, FP8, NT, NSTAGE_D>;
         auto kern = paged_decode_dynamic_kernel<BS, FP8, NT, NSTAGE_D>;
         static bool attr_set3 = false;   // per instantiation; idempotent, so a race is harmless
@@ -1216,7 +1243,8 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
             B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::DYN_SMEM_BYTES));
             attr_set3 = true;
         }
-        const int grid = persistent_grid();
+        const int grid = persistent_grid(C::CTAS_DYN);
+        B2_REQUIRE(grid == pl.nc, B2_EINVAL, "paged_decode: plan made for %d CTAs, kernel runs %d", pl.nc, grid);
         zero_counter_kernel<<<1, 32, 0, st>>>(p.counter);
         B2_CUDA_OK(cudaGetLastError());
         cudaLaunchAttribute at[1];
@@ -1261,8 +1289,12 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
 template <int BS>
 int dispatch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, const Plan& pl, bool fp8,
                     cudaStream_t st) {
-    if (!fp8) return pl.nt == 1 ? launch_decode<BS, false, 1>(tmK, tmV, p, pl, st) : launch_decode<BS, false, 2>(tmK, tmV, p, pl, st);
-    return pl.nt == 1 ? launch_decode<BS, true, 1>(tmK, tmV, p, pl, st) : launch_decode<BS, true, 2>(tmK, tmV, p, pl, st);
+    if (!fp8)
+        return pl.nt == 1 ? launch_decode<BS, false, 1, 3, 3>(tmK, tmV, p, pl, st)
+                          : launch_decode<BS, false, 2, 3, 3>(tmK, tmV, p, pl, st);
+    if (ctas_per_sm(true, p.G) == 3) return launch_decode<BS, true, 1, 4, 3>(tmK, tmV, p, pl, st);
+    return pl.nt == 1 ? launch_decode<BS, true, 1, 6, 5>(tmK, tmV, p, pl, st)
+                      : launch_decode<BS, true, 2, 6, 5>(tmK, tmV, p, pl, st);
 }
 
 bool shape_ok(int B, int Hq, int Hkv, int d, int bs, int max_nb) {
@@ -1306,12 +1338,11 @@ extern "C" int b2_paged_decode_auto_splits(int B, int Hq, int Hkv, int d, int bs
 // single-pass grid wins (no workspace, no merge, no schedule prologue); otherwise the dynamic schedule does.
 extern "C" int b2_paged_decode_plan_splits(const int32_t* seq_lens_host, int B, int Hq, int Hkv, int d, int bs,
                                            int kv_dtype) {
-    (void)kv_dtype;
     if (!seq_lens_host || !shape_ok(B, Hq, Hkv, d, bs, 1)) return B2_EINVAL;
     const int G = Hq / Hkv;
     const int hpc = G <= 8 ? 8 : 16;
     const int ipb = Hkv * ((G + hpc - 1) / hpc);
-    const int NC = persistent_grid();
+    const int NC = persistent_grid(ctas_per_sm(kv_dtype == B2_KV_FP8_E4M3, G));
     const int64_t items = (int64_t)B * ipb;
     if (items < NC) return 0;
     constexpr int64_t OVERHEAD_TOK = 128;   // CTA launch + pipeline fill, in streamed-token equivalents
@@ -1338,7 +1369,7 @@ extern "C" size_t b2_paged_decode_workspace_bytes(int B, int Hq, int Hkv, int d,
                                                   int num_splits) {
     if (!shape_ok(B, Hq, Hkv, d, bs, max_nb)) return 0;
     Plan pl;
-    make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits);
+    make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits, 3);   // no kv_dtype here: the bound for every variant
     return plan_workspace(pl, B, Hq);
 }
 
@@ -1373,7 +1404,7 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
 
     const int G = Hq / Hkv;
     Plan pl;
-    make_plan(&pl, B, Hkv, G, bs, max_nb, num_splits);
+    make_plan(&pl, B, Hkv, G, bs, max_nb, num_splits, ctas_per_sm(kv_dtype == B2_KV_FP8_E4M3, G));
 
     DecodeParams p;
     p.out = static_cast<__nv_bfloat16*>(out);
