@@ -18,6 +18,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--skip-model", action="store_true")
 ap.add_argument("--model", default="llama-3-8b")
 ap.add_argument("--steps", type=int, default=100)
+ap.add_argument("--only", choices=["all", "prefill", "ops", "decode"], default="all")
 a = ap.parse_args()
 dev = torch.device("cuda:0")
 peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
@@ -51,7 +52,7 @@ def emit(**kw):
 # ---------------------------------------------------------------- prefill attention
 Hq, Hkv, d, bs = 32, 8, 128, 16
 g = torch.Generator(device=dev).manual_seed(0)
-for chunk, start in ((8192, 0), (8192, 8192), (8192, 24576), (2048, 0), (512, 3584)):
+for chunk, start in ((8192, 0), (8192, 8192), (8192, 24576), (2048, 0), (512, 3584)) if a.only in ("all", "prefill") else ():
     total = start + chunk
     nb = (total + bs - 1) // bs
     num_blocks = nb + 8
@@ -70,7 +71,7 @@ for chunk, start in ((8192, 0), (8192, 8192), (8192, 24576), (2048, 0), (512, 35
          note="causal flops only (4*d per visible (q,k) pair)")
 
 # ---------------------------------------------------------------- element-wise ops
-for T in (64, 8192):
+for T in (64, 8192) if a.only in ("all", "ops") else ():
     H, I = 4096, 14336
     x = torch.randn(T, H, device=dev).to(torch.bfloat16)
     r = torch.randn(T, H, device=dev).to(torch.bfloat16)
@@ -104,7 +105,9 @@ emit(op="sample(greedy)", B=64, V=128256, us=med * 1e3, GBps=64 * 128256 * 2 / m
 if a.skip_model:
     sys.exit(0)
 # ---------------------------------------------------------------- whole-model decode tok/s, b64 ctx4k
-del kc, vc, q, out, gu, oo, logits
+if a.only not in ("all", "decode"):
+    sys.exit(0)
+kc = vc = q = out = gu = oo = logits = None
 torch.cuda.empty_cache()
 from b200attn.engine import LLMEngine, SamplingParams  # noqa: E402
 from b200attn.model import resolve_config  # noqa: E402

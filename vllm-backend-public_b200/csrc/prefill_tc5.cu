@@ -303,11 +303,16 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         for (int i = 0; i < 32; ++i)
                             if (j0 + c * 32 + i > lim) sr[c][i] = 0xff800000u;   // -inf
                 }
-                float mx = -INFINITY;
+                // one warp per tile and scheduler: nothing hides a 128-long dependent chain, so reduce in 8 short ones
+                float mxp[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) mxp[k] = -INFINITY;
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(sr[c][i]));
+                    for (int i = 0; i < 32; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], __uint_as_float(sr[c][i]));
+                const float mx = fmaxf(fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3])),
+                                       fmaxf(fmaxf(mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7])));
                 const float m_new = fmaxf(m, mx);                 // finite: key 0 is visible to every row, tiles in order
                 if (j == 0) {
                     m = m_new;
@@ -330,7 +335,8 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     }
                 }
                 const float ms = m * sl2;
-                float sum = 0.f;
+                // l sums the fp32 weights (the bf16 rounding of P is zero-mean; FlashAttention convention), 4 chains
+                float sum[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {                     // 64 keys -> 32 packed bf16 pairs per store
                     uint32_t pk[32];
@@ -340,11 +346,11 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         const float p0 = b2::fast_exp2(fmaf(__uint_as_float(sr[cc][ii]), sl2, -ms));
                         const float p1 = b2::fast_exp2(fmaf(__uint_as_float(sr[cc][ii + 1]), sl2, -ms));
                         pk[i] = b2::pack_bf16x2(p0, p1);
-                        sum += __uint_as_float(pk[i] << 16) + __uint_as_float(pk[i] & 0xffff0000u);   // the rounded weights
+                        sum[i & 3] += p0 + p1;
                     }
                     tmem_st32(s_addr + c * 32, pk);               // P overwrites the first 64 columns of S_x
                 }
-                l += sum;
+                l += (sum[0] + sum[1]) + (sum[2] + sum[3]);
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
