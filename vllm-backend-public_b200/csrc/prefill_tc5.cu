@@ -26,7 +26,7 @@ constexpr int D = 128;
 constexpr int BM = 128;             // rows per q tile
 constexpr int BN = 128;             // kv tokens per stage
 constexpr int NSTAGE = 2;
-constexpr int NTHREADS = 320;
+constexpr int NTHREADS = 384;       // 3 warpgroups: softmax A, softmax B, {TMA producer, MMA issuer, 2 idle warps}
 constexpr int SUB_BYTES = 128 * 128;               // one [128 rows][64 el] sub-tile
 constexpr int TILE_BYTES = 2 * SUB_BYTES;          // 32 KiB: a 128 x 128 bf16 tile
 constexpr int Q_BYTES = 2 * TILE_BYTES;
@@ -104,9 +104,38 @@ __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 
+// 2^x for x <= 0 on the FMA/ALU pipes (the MUFU unit does 16 ex2 per clock and SM: with every weight on it the two
+// tiles' softmax needs as many cycles as their MMAs, profiles/r1_ncu_prefill_tc5.md).  Round x to the nearest integer
+// n with the 1.5 * 2^23 trick, 2^f on [-0.5, 0.5] by a cubic (relative error 7.5e-5, far below the bf16 rounding of
+// P), n added to the exponent field.
+__device__ __forceinline__ float poly_exp2(float x) {
+    x = fmaxf(x, -126.f);
+    const float t = x + 12582912.f;
+    const float f = x - (t - 12582912.f);
+    float p = fmaf(f, 0.05517157f, 0.24261111f);
+    p = fmaf(p, f, 0.69326103f);
+    p = fmaf(p, f, 0.99992806f);
+    return __uint_as_float(__float_as_uint(p) + (__float_as_uint(t) << 23));
+}
+
+// Blackwell's packed fp32 pipe: two FMAs / adds per instruction (the softmax warps are issue- and latency-bound).
+__device__ __forceinline__ void fma_x2(float& d0, float& d1, float a0, float a1, float b, float c) {
+    asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+        "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %4};\n\tmov.b64 rc, {%5, %5};\n\t"
+        "fma.rn.f32x2 rd, ra, rb, rc;\n\tmov.b64 {%0, %1}, rd;\n\t}"
+        : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b), "f"(c));
+}
+__device__ __forceinline__ void add_x2(float& d0, float& d1, float a0, float a1) {   // (d0, d1) += (a0, a1)
+    asm("{\n\t.reg .b64 ra, rd;\n\t"
+        "mov.b64 ra, {%2, %3};\n\tmov.b64 rd, {%0, %1};\n\t"
+        "add.rn.f32x2 rd, rd, ra;\n\tmov.b64 {%0, %1}, rd;\n\t}"
+        : "+f"(d0), "+f"(d1) : "f"(a0), "f"(a1));
+}
+
 // =============================================================================================
-// the kernel
+// the kernel.  POLY of every 4 consecutive softmax weights take poly_exp2, the rest MUFU.EX2.
 // =============================================================================================
+template <int POLY>
 __global__ void __launch_bounds__(NTHREADS, 1)
 prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const Tc5Params p) {
@@ -157,10 +186,14 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    // register file: 384 threads start with 168 each (where the 128 live S values of a row + packed P spill); the
+    // third warpgroup keeps 64, the two softmax warpgroups take 216
+    // (setmaxnreg opens each role's branch below)
     const int chunk = s_tile[0];
     const int q0 = s_tile[1], len = s_tile[2], start = s_tile[3];
 
-    if (chunk >= 0) {
+    const bool active = chunk >= 0;               // CTA-uniform
+    {
         const int rows = min(p.rows_per_cta, len - q0);         // valid query rows of the CTA
         const int rowsX[2] = {min(BM, rows), max(0, rows - BM)};
         // keys [0, hiX) are visible to the last row of tile X; tiles of 128 keys
@@ -168,9 +201,11 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const int nX[2] = {(hiX[0] + BN - 1) / BN, (hiX[1] + BN - 1) / BN};
         const int n_tiles = max(nX[0], nX[1]);
         const int kv_hi = max(hiX[0], hiX[1]);
-        const int row0 = p.cu_q[chunk] + q0;                    // first token row in q / out
+        const int row0 = active ? p.cu_q[chunk] + q0 : 0;       // first token row in q / out
 
-        if (warp == 8) {
+        if (warp >= 8) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        if (active && warp == 8) {
             // ------------------------------------------ TMA producer ------------------------------------------
             if (lane == 0) {
                 b2::tma_prefetch_desc(&tmQ);
@@ -224,7 +259,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 load_tile(it, 1, wv);
             }
         }
-        else if (warp == 9) {
+        else if (active && warp == 9) {
             // ------------------------------------------ MMA issuer (one lane) ------------------------------------------
             if (lane == 0) {
                 constexpr uint32_t ID_QK = idesc_bf16(128, 128, 0), ID_PV = idesc_bf16(128, 128, 1);
@@ -277,7 +312,10 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 }
             }
         }
+        }
         else {
+            asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+            if (active) {
             // ------------------------------------------ softmax warps: tile x = warp / 4 ------------------------------------------
             const int x = warp >> 2, wq = warp & 3;
             const int row = wq * 32 + lane;                       // query row in the tile = TMEM lane
@@ -343,10 +381,13 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
                         const int cc = 2 * c + (i >> 4), ii = (2 * i) & 31;
-                        const float p0 = b2::fast_exp2(fmaf(__uint_as_float(sr[cc][ii]), sl2, -ms));
-                        const float p1 = b2::fast_exp2(fmaf(__uint_as_float(sr[cc][ii + 1]), sl2, -ms));
+                        float x0, x1;
+                        fma_x2(x0, x1, __uint_as_float(sr[cc][ii]), __uint_as_float(sr[cc][ii + 1]), sl2, -ms);
+                        // (i & 1, element) -> slot 0..3 of the group of four; slots < POLY go to the polynomial
+                        const float p0 = (POLY >= 2 && (i & 1)) || POLY >= 3 ? poly_exp2(x0) : b2::fast_exp2(x0);
+                        const float p1 = (POLY >= 1 && (i & 1)) || POLY >= 4 ? poly_exp2(x1) : b2::fast_exp2(x1);
                         pk[i] = b2::pack_bf16x2(p0, p1);
-                        sum[i & 3] += p0 + p1;
+                        add_x2(sum[2 * (i & 1)], sum[2 * (i & 1) + 1], p0, p1);
                     }
                     tmem_st32(s_addr + c * 32, pk);               // P overwrites the first 64 columns of S_x
                 }
@@ -379,6 +420,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         }
                     }
                 }
+            }
             }
         }
     }
@@ -434,12 +476,12 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
     p.rows_per_cta = rows_per_cta;
     p.out_stride = out_stride;
     p.scale_log2 = scale * LOG2E;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B2_CUDA_OK(cudaFuncSetAttribute(prefill_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        attr_set = true;
-    }
-    prefill_tc5_kernel<<<dim3(Hq, (unsigned)n_qtiles), NTHREADS, SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(tmQ, tmK, tmV, p);
+    // share of the softmax weights computed by polynomial (B2_PREFILL_POLY = 0..3 of every 4; A/B knob)
+    static const int poly = []() { const char* e = getenv("B2_PREFILL_POLY"); return e && *e ? atoi(e) : 0; }();
+    auto kern = poly <= 0 ? prefill_tc5_kernel<0> : poly == 1 ? prefill_tc5_kernel<1> : poly == 2 ? prefill_tc5_kernel<2>
+                                                                                     : prefill_tc5_kernel<3>;
+    B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    kern<<<dim3(Hq, (unsigned)n_qtiles), NTHREADS, SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(tmQ, tmK, tmV, p);
     B2_CUDA_OK(cudaGetLastError());
     return B2_OK;
 }
