@@ -55,14 +55,26 @@ rms_norm_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict
     __nv_bfloat16* rr = residual ? residual + row * res_stride : nullptr;
     float h[VPT][8];
     float ss = 0.f;
+    // every load of the row (x, residual, weight) is issued before the first use: one DRAM round trip per CTA
+    int4 xv[VPT], rv[VPT], wv[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = threadIdx.x + k * blockDim.x;
+        xv[k] = rv[k] = wv[k] = make_int4(0, 0, 0, 0);
+        if (v < nvec) {
+            xv[k] = *reinterpret_cast<const int4*>(xr + v * 8);
+            if (rr) rv[k] = *reinterpret_cast<const int4*>(rr + v * 8);
+            wv[k] = *reinterpret_cast<const int4*>(weight + v * 8);
+        }
+    }
 #pragma unroll
     for (int k = 0; k < VPT; ++k) {
         const int v = threadIdx.x + k * blockDim.x;
         if (v < nvec) {
-            unpack8(*reinterpret_cast<const int4*>(xr + v * 8), h[k]);
+            unpack8(xv[k], h[k]);
             if (rr) {
                 float r[8];
-                unpack8(*reinterpret_cast<const int4*>(rr + v * 8), r);
+                unpack8(rv[k], r);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) h[k][i] += r[i];
                 const int4 packed = pack8(h[k]);          // the residual stream is bf16: round once, then norm
@@ -87,7 +99,7 @@ rms_norm_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict
         const int v = threadIdx.x + k * blockDim.x;
         if (v < nvec) {
             float w[8], o[8];
-            unpack8(*reinterpret_cast<const int4*>(weight + v * 8), w);
+            unpack8(wv[k], w);
 #pragma unroll
             for (int i = 0; i < 8; ++i) o[i] = w[i] * (h[k][i] * inv);
             *reinterpret_cast<int4*>(orow + v * 8) = pack8(o);
@@ -152,50 +164,99 @@ rope_and_cache_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict
                       int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
                       const float* __restrict__ k_scale, const float* __restrict__ v_scale) {
     const int t = blockIdx.x;
-    const int pos = min(max(positions[t], 0), max_pos - 1);   // table bound; the host validates positions
-    const int64_t slot = slot_mapping[t];
-    const int64_t blk = slot >= 0 ? slot / bs : 0;
-    const int off = slot >= 0 ? (int)(slot - blk * bs) : 0;
     const int half = d >> 1;
     const int pairs_per_head = half >> 3;              // vector pairs of 8 elements
+    const int vec_per_head = d >> 3;
     const int n_rot = (Hq + Hkv) * pairs_per_head;
-    const int n_v = Hkv * (d >> 3);
+    const int n_v = Hkv * vec_per_head;
     __nv_bfloat16* row = qkv + t * token_stride;
+
+    // A thread owns up to ITEMS work items (i = tid + k * blockDim): a rotation pair (two 16-byte vectors of one head)
+    // or one 16-byte vector of V.  All of a thread's q/k/v loads are issued before anything depends on them; the
+    // position / slot / cos-sin chain runs underneath.  (One item per loop trip left a CTA with one DRAM round trip
+    // in flight per thread: 3.4 TB/s at 8k tokens.)
+    constexpr int ITEMS = 2;
+    int4 xa[ITEMS], xb[ITEMS];
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+        const int i = threadIdx.x + k * blockDim.x;
+        xa[k] = xb[k] = make_int4(0, 0, 0, 0);
+        if (i < n_rot) {
+            const int h = i / pairs_per_head, c = i - h * pairs_per_head;
+            xa[k] = *reinterpret_cast<const int4*>(row + h * d + c * 8);
+            xb[k] = *reinterpret_cast<const int4*>(row + h * d + c * 8 + half);
+        } else if (i < n_rot + n_v) {
+            const int j = i - n_rot;
+            xa[k] = *reinterpret_cast<const int4*>(row + (int64_t)(Hq + Hkv) * d + j * 8);
+        }
+    }
+    const int pos = min(max(positions[t], 0), max_pos - 1);   // table bound; the host validates positions
+    const int64_t slot = slot_mapping[t];
+    int64_t blk = 0;
+    int off = 0;
+    if (slot >= 0) {
+        if (slot < (int64_t)0x7fffffff) {                     // 32-bit divide (the 64-bit one is a subroutine call)
+            const uint32_t s32 = (uint32_t)slot;
+            blk = s32 / (uint32_t)bs;
+            off = (int)(s32 - (uint32_t)blk * (uint32_t)bs);
+        } else {
+            blk = slot / bs;
+            off = (int)(slot - blk * bs);
+        }
+    }
     const float* cs = cos_sin + (int64_t)pos * d;
     float ks = 1.f, vs = 1.f;
     if (FP8) { ks = *k_scale; vs = *v_scale; }
-    for (int i = threadIdx.x; i < n_rot + n_v; i += blockDim.x) {
-        if (i < n_rot) {
-            const int h = i / pairs_per_head;
-            const int c = i - h * pairs_per_head;
-            __nv_bfloat16* p = row + h * d + c * 8;
-            float x1[8], x2[8], co[8], si[8], o1[8], o2[8];
-            unpack8(*reinterpret_cast<const int4*>(p), x1);
-            unpack8(*reinterpret_cast<const int4*>(p + half), x2);
-            *reinterpret_cast<float4*>(co) = *reinterpret_cast<const float4*>(cs + c * 8);
-            *reinterpret_cast<float4*>(co + 4) = *reinterpret_cast<const float4*>(cs + c * 8 + 4);
-            *reinterpret_cast<float4*>(si) = *reinterpret_cast<const float4*>(cs + half + c * 8);
-            *reinterpret_cast<float4*>(si + 4) = *reinterpret_cast<const float4*>(cs + half + c * 8 + 4);
+
+    for (int base = 0; base < n_rot + n_v; base += ITEMS * blockDim.x) {
+        if (base > 0) {                                       // more than ITEMS items per thread (wide models)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                o1[j] = __fsub_rn(__fmul_rn(x1[j], co[j]), __fmul_rn(x2[j], si[j]));
-                o2[j] = __fadd_rn(__fmul_rn(x2[j], co[j]), __fmul_rn(x1[j], si[j]));
+            for (int k = 0; k < ITEMS; ++k) {
+                const int i = base + threadIdx.x + k * blockDim.x;
+                if (i < n_rot) {
+                    const int h = i / pairs_per_head, c = i - h * pairs_per_head;
+                    xa[k] = *reinterpret_cast<const int4*>(row + h * d + c * 8);
+                    xb[k] = *reinterpret_cast<const int4*>(row + h * d + c * 8 + half);
+                } else if (i < n_rot + n_v) {
+                    xa[k] = *reinterpret_cast<const int4*>(row + (int64_t)(Hq + Hkv) * d + (i - n_rot) * 8);
+                }
             }
-            *reinterpret_cast<int4*>(p) = pack8(o1);
-            *reinterpret_cast<int4*>(p + half) = pack8(o2);
-            if (h >= Hq && slot >= 0) {
-                const int64_t e = blk * cache_block_stride + (int64_t)(h - Hq) * cache_head_stride + (int64_t)off * d + c * 8;
-                store_cache8<FP8>(k_cache, e, o1, ks);
-                store_cache8<FP8>(k_cache, e + half, o2, ks);
+        }
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) {
+            const int i = base + threadIdx.x + k * blockDim.x;
+            if (i < n_rot) {
+                const int h = i / pairs_per_head;
+                const int c = i - h * pairs_per_head;
+                __nv_bfloat16* p = row + h * d + c * 8;
+                float x1[8], x2[8], co[8], si[8], o1[8], o2[8];
+                unpack8(xa[k], x1);
+                unpack8(xb[k], x2);
+                *reinterpret_cast<float4*>(co) = *reinterpret_cast<const float4*>(cs + c * 8);
+                *reinterpret_cast<float4*>(co + 4) = *reinterpret_cast<const float4*>(cs + c * 8 + 4);
+                *reinterpret_cast<float4*>(si) = *reinterpret_cast<const float4*>(cs + half + c * 8);
+                *reinterpret_cast<float4*>(si + 4) = *reinterpret_cast<const float4*>(cs + half + c * 8 + 4);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    o1[j] = __fsub_rn(__fmul_rn(x1[j], co[j]), __fmul_rn(x2[j], si[j]));
+                    o2[j] = __fadd_rn(__fmul_rn(x2[j], co[j]), __fmul_rn(x1[j], si[j]));
+                }
+                *reinterpret_cast<int4*>(p) = pack8(o1);
+                *reinterpret_cast<int4*>(p + half) = pack8(o2);
+                if (h >= Hq && slot >= 0) {
+                    const int64_t e = blk * cache_block_stride + (int64_t)(h - Hq) * cache_head_stride + (int64_t)off * d + c * 8;
+                    store_cache8<FP8>(k_cache, e, o1, ks);
+                    store_cache8<FP8>(k_cache, e + half, o2, ks);
+                }
+            } else if (i < n_rot + n_v && slot >= 0) {
+                const int j = i - n_rot;
+                const int h = j / vec_per_head;
+                const int c = j - h * vec_per_head;
+                float f[8];
+                unpack8(xa[k], f);
+                const int64_t e = blk * cache_block_stride + (int64_t)h * cache_head_stride + (int64_t)off * d + c * 8;
+                store_cache8<FP8>(v_cache, e, f, vs);
             }
-        } else if (slot >= 0) {
-            const int j = i - n_rot;
-            const int h = j / (d >> 3);
-            const int c = j - h * (d >> 3);
-            float f[8];
-            unpack8(*reinterpret_cast<const int4*>(row + (Hq + Hkv + h) * d + c * 8), f);
-            const int64_t e = blk * cache_block_stride + (int64_t)h * cache_head_stride + (int64_t)off * d + c * 8;
-            store_cache8<FP8>(v_cache, e, f, vs);
         }
     }
 }
