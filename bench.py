@@ -276,7 +276,8 @@ def run_ours(args, wl_name, wl):
     ks, vs = prob["scales"] or (None, None)
     # schedule: the engine's scheduler holds seq_lens on the host and picks the schedule from them (--splits -1)
     if args.splits < 0:
-        num_splits = b200attn.plan_num_splits(prob["seq_lens"], Hq_l, Hkv_l, D, BS)
+        num_splits = b200attn.plan_num_splits(prob["seq_lens"], Hq_l, Hkv_l, D, BS,
+                                              b200attn.KV_FP8_E4M3 if fp8 else b200attn.KV_BF16)
         schedule_src = "host planner (b2_paged_decode_plan_splits on host seq_lens)"
     else:
         num_splits = args.splits
@@ -336,7 +337,8 @@ def run_ours(args, wl_name, wl):
     # b200attn.DecodeStep: pinned q|k|v and block_tables|seq_lens|slots -> 2 H2D copies, both kernels, result rows
     # stored by the kernels straight into pinned host memory, stream sync; replayed as one CUDA graph per step.
     step = b200attn.DecodeStep(prob["k_cache"], prob["v_cache"], max_batch=B, Hq=Hq_l, max_nb=prob["max_nb"],
-                               k_scale=ks, v_scale=vs)
+                               k_scale=ks, v_scale=vs,
+                               zero_copy_inputs=os.environ.get("B2_E2E_ZERO_COPY", "1") == "1")
     step.h_qkv[:, :Hq_l].copy_(prob["q"].cpu())
     step.h_qkv[:, Hq_l:Hq_l + Hkv_l].copy_(prob["k_new"].cpu())
     step.h_qkv[:, Hq_l + Hkv_l:].copy_(prob["v_new"].cpu())
@@ -412,9 +414,12 @@ def run_ours(args, wl_name, wl):
                          "frac_of_8TBps": round(achieved / NOMINAL_HBM_GBS, 4)},
             "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(e2e_ms, 5),
-                    "path": "b200attn.DecodeStep: 2 H2D copies from pinned memory, reshape_and_cache + paged_decode, "
-                            "result rows stored by the kernels into pinned host memory (the D2H leg), stream sync; "
-                            "one CUDA-graph replay per step, schedule planned on the host per step"},
+                    "path": ("b200attn.DecodeStep: H2D copy of block_tables|seq_lens|slots from pinned memory, "
+                             + ("q|k|v rows read by the kernels straight from pinned host memory (the H2D leg, no "
+                                "staging copy), " if step.zero_copy_inputs and num_splits != 0 else "H2D copy of the q|k|v rows, ")
+                             + "reshape_and_cache + paged_decode, result rows stored by the kernels into pinned host "
+                               "memory (the D2H leg), stream sync; one CUDA-graph replay per step, schedule planned "
+                               "on the host per step")},
             "gpu_launches": launches_per_step * K,
             "clocks": clk.summary(),
         }

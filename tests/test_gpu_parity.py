@@ -374,12 +374,13 @@ def test_decode_many_sequences_grouped_prefix(cuda):
 # ------------------------------------------------------------------------------------------
 # the engine-facing step: host buffers in, host rows out (CUDA graph, output stored to pinned memory)
 # ------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("use_graph", [False, True])
-def test_decode_step_from_host_buffers(cuda, use_graph):
+@pytest.mark.parametrize("use_graph,zero_copy", [(False, False), (True, False), (False, True), (True, True)])
+def test_decode_step_from_host_buffers(cuda, use_graph, zero_copy):
     B, Hq, Hkv, ctx = 6, 8, 2, 300
     inp = R.make_inputs(B, Hq, Hkv, 128, 16, ctx, seed=21, ragged=True)
     kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
-    step = b200attn.DecodeStep(kc, vc, max_batch=8, Hq=Hq, max_nb=inp["max_nb"], use_graph=use_graph)
+    step = b200attn.DecodeStep(kc, vc, max_batch=8, Hq=Hq, max_nb=inp["max_nb"], use_graph=use_graph,
+                               zero_copy_inputs=zero_copy)
     g = torch.Generator().manual_seed(5)
     for it in range(3):    # three decode steps: each rewrites the last token of every sequence, then attends
         k_new = torch.randn(B, Hkv, 128, generator=g).to(torch.bfloat16)

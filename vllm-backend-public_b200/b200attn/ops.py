@@ -20,10 +20,17 @@ def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
+# step inputs that may also live in PINNED host memory: the kernels then read them over PCIe (unified addressing),
+# which replaces the H2D copy of an engine step (b200attn.step.DecodeStep(zero_copy_inputs=True))
+_PINNED_OK = ("q", "k_new", "v_new")
+
+
 def _need_cuda(**tensors) -> torch.device:
     dev = None
     for name, t in tensors.items():
         if t is None:
+            continue
+        if not t.is_cuda and name in _PINNED_OK and t.is_pinned():
             continue
         if not t.is_cuda:
             raise ValueError(f"{name} must be a CUDA tensor (b200attn has no CPU path)")

@@ -28,7 +28,7 @@ from . import ops
 class DecodeStep:
     def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, max_batch: int, Hq: int, max_nb: int,
                  k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None,
-                 use_graph: bool = True):
+                 use_graph: bool = True, zero_copy_inputs: bool = False):
         if not k_cache.is_cuda:
             raise ValueError("DecodeStep needs CUDA caches (b200attn has no CPU path)")
         self.dev = k_cache.device
@@ -36,6 +36,8 @@ class DecodeStep:
         _, self.Hkv, self.bs, self.d = k_cache.shape
         self.Hq, self.max_nb, self.max_batch = Hq, max_nb, max_batch
         self.use_graph = use_graph
+        # True: no H2D copy of the q|k|v rows; reshape_and_cache and paged_decode read them from the pinned buffer
+        self.zero_copy_inputs = zero_copy_inputs
         B, H = max_batch, Hq + 2 * self.Hkv
         self.h_qkv = torch.zeros(B, H, self.d, dtype=torch.bfloat16).pin_memory()
         self.d_qkv = torch.zeros(B, H, self.d, dtype=torch.bfloat16, device=self.dev)
@@ -57,32 +59,38 @@ class DecodeStep:
     # ------------------------------------------------------------------------------------------
     @property
     def h2d_bytes(self) -> int:
-        return self.h_qkv.numel() * 2 + self.h_meta.numel() * 4
+        return self.h_qkv.numel() * 2 + self.h_meta.numel() * 4   # zero-copy moves the same bytes, inside the kernels
 
     @property
     def d2h_bytes(self) -> int:
         return self.h_out.numel() * 2
 
-    def _views(self, B: int):
+    def _views(self, B: int, zero_copy: bool):
         Hq, Hkv = self.Hq, self.Hkv
-        q = self.d_qkv[:B, :Hq]
-        k = self.d_qkv[:B, Hq:Hq + Hkv]
-        v = self.d_qkv[:B, Hq + Hkv:]
+        src = self.h_qkv if zero_copy else self.d_qkv
+        q = src[:B, :Hq]
+        k = src[:B, Hq:Hq + Hkv]
+        v = src[:B, Hq + Hkv:]
         bt = self.d_meta[: self._off_sl].view(self.max_batch, self.max_nb)[:B]
         sl = self.d_meta[self._off_sl: self._off_sl + B]
         slots = self.d_meta[self._off_slot: self._off_slot + 2 * self.max_batch].view(torch.int64)[:B]
         return q, k, v, bt, sl, slots
 
     def _enqueue(self, B: int, num_splits: int) -> None:
-        self.d_qkv.copy_(self.h_qkv, non_blocking=True)
+        # the dynamic schedule fetches a run's q rows with every run it starts: a PCIe round trip each would sit on
+        # the pipeline's critical path, so zero-copy inputs are for the single-pass / grid-split schedules only
+        zero_copy = self.zero_copy_inputs and num_splits != 0
+        if not zero_copy:
+            self.d_qkv.copy_(self.h_qkv, non_blocking=True)
         self.d_meta.copy_(self.h_meta, non_blocking=True)
-        q, k, v, bt, sl, slots = self._views(B)
+        q, k, v, bt, sl, slots = self._views(B, zero_copy)
         ops.reshape_and_cache(k, v, self.k_cache, self.v_cache, slots, self.k_scale, self.v_scale)
         ops.paged_decode(q, self.k_cache, self.v_cache, bt, sl, k_scale=self.k_scale, v_scale=self.v_scale,
                          out=self.h_out[:B], workspace=self.workspace, num_splits=num_splits)
 
     def plan(self, B: int) -> int:
-        return ops.plan_num_splits(self.h_seq_lens[:B], self.Hq, self.Hkv, self.d, self.bs)
+        return ops.plan_num_splits(self.h_seq_lens[:B], self.Hq, self.Hkv, self.d, self.bs,
+                                   ops.KV_FP8_E4M3 if self.k_cache.dtype == torch.uint8 else ops.KV_BF16)
 
     def run(self, B: Optional[int] = None, num_splits: Optional[int] = None) -> torch.Tensor:
         """Run the step for the first B rows of the host buffers; returns the pinned output rows (valid on return)."""
@@ -91,18 +99,22 @@ class DecodeStep:
             raise ValueError(f"B={B} outside (0, {self.max_batch}]")
         if num_splits is None:
             num_splits = self.plan(B)
-        with torch.cuda.stream(self._stream):
-            if not self.use_graph:
-                self._enqueue(B, num_splits)
-            else:
-                g = self._graphs.get((B, num_splits))
-                if g is None:
+        # everything runs on the caller's current stream (a stream context per step costs ~7 us of host time);
+        # only the one-time capture uses the private stream
+        cur = torch.cuda.current_stream(self.dev)
+        if not self.use_graph:
+            self._enqueue(B, num_splits)
+        else:
+            g = self._graphs.get((B, num_splits))
+            if g is None:
+                cur.synchronize()
+                with torch.cuda.stream(self._stream):
                     self._enqueue(B, num_splits)          # warm-up outside capture (function attributes, lazy init)
                     self._stream.synchronize()
                     g = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g, stream=self._stream):
                         self._enqueue(B, num_splits)
-                    self._graphs[(B, num_splits)] = g
-                g.replay()
-        self._stream.synchronize()
+                self._graphs[(B, num_splits)] = g
+            g.replay()
+        cur.synchronize()
         return self.h_out[:B]
