@@ -44,6 +44,7 @@ WORKLOADS = {
     "llama3-8b_b128_ctx8k_fp8kv": dict(B=128, Hq=32, Hkv=8, ctx=8192, fp8=True),     # BASELINE configs[2]
     "llama3-70b_b256_ctx8k_bf16kv": dict(B=256, Hq=64, Hkv=8, ctx=8192, fp8=False),  # BASELINE configs[3]
     "oracle_b4_ctx512": dict(B=4, Hq=8, Hkv=2, ctx=512, fp8=False),                 # BASELINE configs[0]
+    "llama3-70b_tp8_shard": dict(B=256, Hq=8, Hkv=1, ctx=8192, fp8=False),           # one rank's share of configs[3] at tp = 8
 }
 D = 128
 BS = int(os.environ.get("B2_BENCH_BLOCK_SIZE", "16"))   # BASELINE fixes 16; other sizes are experiments only

@@ -141,7 +141,12 @@ B2_API int b2_paged_decode_simt(void* out, const void* q,
  *   out[t][hq] = softmax_{j <= ctx_start[c] + i}(scale * <q[t][hq], K[c][j][hq / G]>) . V[c][j][hq / G]
  *   fp32 softmax / accumulation, softmax weights rounded to bf16 for the P.V product, out rounded to bf16 once.
  * T = cu_q[n_chunks] (host knowledge: it sizes the grid).  cu_q, ctx_start, block_tables: DEVICE int32.
- * kv_dtype: B2_KV_BF16 only (B2_EUNSUPPORTED otherwise; fp8 KV is a decode-side format here).
+ * kv_dtype: B2_KV_BF16 only (B2_EUNSUPPORTED otherwise).  Over an fp8-e4m3 cache the caller first gathers the
+ * blocks the chunks can see into a bf16 scratch cache with b2_dequant_kv_blocks (below) and passes that scratch
+ * with its own block table and the cache's scales: the conversion moves 3 bytes per cache element once, the
+ * attention then re-reads bf16.
+ * k_scale / v_scale: optional DEVICE fp32 scalars (NULL = 1): the cache holds K / k_scale and V / v_scale;
+ * k_scale multiplies the softmax scale, v_scale the output -- exactly the fp8 dequantisation of b2_paged_decode.
  * ------------------------------------------------------------------------------------------- */
 B2_API int b2_prefill_attention(void* out, const void* q, const void* k_cache, const void* v_cache,
                          const int32_t* block_tables, const int32_t* cu_q, const int32_t* ctx_start,
@@ -150,6 +155,14 @@ B2_API int b2_prefill_attention(void* out, const void* q, const void* k_cache, c
                          int64_t cache_block_stride, int64_t cache_head_stride,
                          float scale, int kv_dtype, const float* k_scale, const float* v_scale,
                          void* stream);
+
+/* fp8-e4m3 -> bf16 gather of whole cache blocks (the prefill side of VLLMConfig additional_args `kv-cache-dtype`,
+ * reference benchmark-vllm/models.py:23-28): out block i = float(e4m3 block src_blocks[i]) for i < n, which is
+ * exact in bf16; the per-tensor scales are applied by b2_prefill_attention (k_scale / v_scale arguments).
+ * k_out / v_out: bf16 [n][Hkv][bs][d], contiguous, caller-owned.  src_blocks: DEVICE int32 [n]. */
+B2_API int b2_dequant_kv_blocks(void* k_out, void* v_out, const void* k_cache, const void* v_cache,
+                         const int32_t* src_blocks, int64_t n, int Hkv, int d, int bs,
+                         int64_t cache_block_stride, int64_t cache_head_stride, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Element-wise ops of one decoder layer around the attention path: what the

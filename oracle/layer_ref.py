@@ -25,7 +25,8 @@ from typing import List, Optional
 import numpy as np
 import torch
 
-from paged_attention_ref import KV_BF16, KV_FP8_E4M3, reshape_and_cache_ref, _load_cache_f32  # noqa: F401
+from paged_attention_ref import (KV_BF16, KV_FP8_E4M3, reshape_and_cache_ref, _load_cache_f32,  # noqa: F401
+                                 e4m3_decode, e4m3_encode)
 
 
 def _bf16_round(x: torch.Tensor) -> torch.Tensor:
@@ -37,17 +38,19 @@ def _bf16_round(x: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------------------
 def prefill_attention_ref(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_tables: torch.Tensor,
                           cu_q: torch.Tensor, ctx_start: torch.Tensor, scale: Optional[float] = None,
-                          return_f32: bool = False) -> torch.Tensor:
+                          return_f32: bool = False, kv_dtype: int = KV_BF16, k_scale: float = 1.0,
+                          v_scale: float = 1.0) -> torch.Tensor:
     """q [T, Hq, d] bf16; chunk c = rows cu_q[c]:cu_q[c+1] at positions ctx_start[c] + i; token i attends cache
-    positions j <= ctx_start[c] + i of block_tables[c].  fp32 softmax and contractions, one rounding to bf16."""
+    positions j <= ctx_start[c] + i of block_tables[c].  fp32 softmax and contractions, one rounding to bf16.
+    fp8-e4m3 caches (uint8) are read as float(e4m3) * scale, exactly (paged_attention_ref._load_cache_f32)."""
     T, Hq, d = q.shape
     nb, Hkv, bs, _ = k_cache.shape
     G = Hq // Hkv
     if scale is None:
         scale = 1.0 / math.sqrt(d)
     out = torch.zeros(T, Hq, d, dtype=torch.float32)
-    kc = k_cache.to(torch.float32)
-    vc = v_cache.to(torch.float32)
+    kc = _load_cache_f32(k_cache, kv_dtype, k_scale)
+    vc = _load_cache_f32(v_cache, kv_dtype, v_scale)
     for c in range(ctx_start.numel()):
         r0, r1 = int(cu_q[c]), int(cu_q[c + 1])
         n = r1 - r0
@@ -174,8 +177,10 @@ def sample_ref(logits, temperature=None, seeds=None) -> torch.Tensor:
 # weights: the engine's dict (embed, l{i}.ln1/wqkv[/bqkv]/wo/ln2/wgu/wdown, norm, lm_head) as CPU tensors.
 # --------------------------------------------------------------------------------------
 def llama_forward_ref(w: dict, token_ids, *, layers: int, Hq: int, Hkv: int, d: int, eps: float,
-                      cos_sin: torch.Tensor) -> torch.Tensor:
-    """Returns fp32 logits [T, vocab] for positions 0..T-1 of one sequence."""
+                      cos_sin: torch.Tensor, kv_fp8_scales=None) -> torch.Tensor:
+    """Returns fp32 logits [T, vocab] for positions 0..T-1 of one sequence.
+    kv_fp8_scales = (k_scale, v_scale): K (after rotary) and V pass through the e4m3 cache encoding
+    (sat_rne(x / scale), read back as float(e4m3) * scale), as an engine with an fp8 KV cache stores them."""
     f32 = lambda t: t.to(torch.float32)                              # noqa: E731
     ids = torch.as_tensor(token_ids, dtype=torch.long)
     T = ids.numel()
@@ -197,8 +202,13 @@ def llama_forward_ref(w: dict, token_ids, *, layers: int, Hq: int, Hkv: int, d: 
         x1, x2 = rot[..., :half], rot[..., half:]
         rot = f32(_bf16_round(torch.cat([x1 * cos - x2 * sin, x2 * cos + x1 * sin], dim=-1)))
         q = rot[:, :Hq].permute(1, 0, 2)
-        k = rot[:, Hq:].permute(1, 0, 2).repeat_interleave(G, 0)
-        v = qkv[:, Hq + Hkv:].permute(1, 0, 2).repeat_interleave(G, 0)
+        k_tok, v_tok = rot[:, Hq:], qkv[:, Hq + Hkv:]
+        if kv_fp8_scales is not None:
+            ks, vs = kv_fp8_scales
+            k_tok = e4m3_decode(e4m3_encode(k_tok / ks)) * ks
+            v_tok = e4m3_decode(e4m3_encode(v_tok / vs)) * vs
+        k = k_tok.permute(1, 0, 2).repeat_interleave(G, 0)
+        v = v_tok.permute(1, 0, 2).repeat_interleave(G, 0)
         s = (q @ k.transpose(1, 2)) / math.sqrt(d)
         s = s.masked_fill(causal.unsqueeze(0), float("-inf"))
         attn = _bf16_round((torch.softmax(s, -1) @ v).permute(1, 0, 2).reshape(T, Hq * d))

@@ -1,8 +1,13 @@
 // Instruction-rate probe for the fp8 decode design choice:
-//   (a) mma.sync m16n8k16 f16      (what the fp8 path used: K/V converted e4m3 -> f16 in registers)
+//   (a) mma.sync m16n8k16 f16      (what the fp8 path uses: K/V converted e4m3 -> f16 in registers)
 //   (b) mma.sync m16n8k32 e4m3     (K/V fed to the MMA as stored, q and P split into e4m3 terms)
 //   (c) cvt.rn.f16x2.e4m3x2        (the conversion (a) needs: one per two cache elements)
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o mma_rate scripts/mma_rate.cu ; run on the GPU box.
+// Finding (B200, CUDA 12.9): sm_100a has no native legacy fp8 MMA.  `cuobjdump -sass` of this file shows (b) lowered
+// to F2FP.F16.E4M3.UNPACK_B + two HMMA.16816.F32 per instruction; in this loop the operands are loop-invariant, so
+// ptxas hoists the conversions and (b) *looks* 1.9x faster per instruction than (a) -- in a real kernel the
+// conversion is paid per element either way.  (c) confirms F2FP runs on the half-rate ALU pipe (~3.9 G warp
+// instructions/s/SM with its companions).  Native fp8 on Blackwell = tcgen05.mma.kind::f8f6f4.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o scripts/bin/mma_rate scripts/mma_rate.cu ; run on the GPU box.
 #include <cstdio>
 #include <cstdint>
 #include <cuda_runtime.h>

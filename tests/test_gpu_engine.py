@@ -19,14 +19,15 @@ pytestmark = pytest.mark.gpu
 GAP = 0.06          # logits of the tiny model have std ~0.35; bf16 GEMM noise is ~1e-2
 
 
-def oracle_check(eng, reqs, gap=GAP):
+def oracle_check(eng, reqs, gap=GAP, kv_fp8_scales=None):
     c = eng.cfg
     w = {k: v.cpu() for k, v in eng.model.w.items()}
     table = eng.model.cos_sin.cpu()
     worst = 0.0
     for r in reqs:
         ids = r.prompt_ids + r.output_ids
-        logits = L.llama_forward_ref(w, ids[:-1], layers=c.layers, Hq=c.Hq, Hkv=c.Hkv, d=c.d, eps=c.eps, cos_sin=table)
+        logits = L.llama_forward_ref(w, ids[:-1], layers=c.layers, Hq=c.Hq, Hkv=c.Hkv, d=c.d, eps=c.eps, cos_sin=table,
+                                     kv_fp8_scales=kv_fp8_scales)
         P = len(r.prompt_ids)
         rows = logits[P - 1:]                                  # row P-1 predicts output token 0
         picked = rows.gather(1, torch.tensor(r.output_ids).unsqueeze(1)).squeeze(1)
@@ -52,6 +53,20 @@ def test_engine_greedy_matches_oracle(cuda):
     assert eng.stats.mixed_steps > 0 and eng.stats.decode_steps > 0
     assert eng.sched.num_free_blocks == eng.num_blocks
     oracle_check(eng, reqs)
+
+
+def test_engine_fp8_kv_cache_matches_quantising_oracle(cuda):
+    """--kv-cache-dtype fp8: rotary + e4m3 cache write, fp8 decode, prompt chunks through the dequantised scratch
+    cache -- against the dense oracle whose K / V pass through the same e4m3 encoding (per-tensor scale 1)."""
+    eng = make_engine(num_blocks=600, kv_cache_dtype="fp8")
+    assert eng.model.kv.dtype == torch.uint8
+    rng = random.Random(3)
+    prompts = [[rng.randrange(1024) for _ in range(n)] for n in (1, 17, 100, 300, 520, 64, 257, 129)]
+    reqs = [eng.add_request(p, SamplingParams(max_tokens=20, temperature=0.0)) for p in prompts]
+    eng.run_until_idle()
+    assert all(r.finished and len(r.output_ids) == 20 for r in reqs)
+    assert eng.stats.mixed_steps > 0 and eng.stats.decode_steps > 0
+    oracle_check(eng, reqs, gap=0.08, kv_fp8_scales=(1.0, 1.0))
 
 
 def test_engine_eager_equals_graph(cuda):

@@ -12,11 +12,16 @@ def test_uniform_large_batches_take_the_single_pass_grid():
     assert plan([4096] * 64) == 1                 # BASELINE configs[1]: 512 items on 296 CTA slots
     assert plan([8192] * 128) == 1                # configs[2]
     assert plan([8192] * 256, 64, 8) == 1         # configs[3], tp = 1
+    assert plan([8192] * 256, 8, 1) == 1          # configs[3] at tp = 8: 256 equal items fill 86 % of one wave (measured
+                                                  # 6.7 TB/s single pass vs 6.1 dynamic)
+    KV_FP8 = b200attn.KV_FP8_E4M3
+    lens = torch.tensor([8192] * 128, dtype=torch.int32)
+    assert b200attn.plan_num_splits(lens, 32, 8, 128, 16, KV_FP8) == 0   # fp8 (3 CTAs per SM): 2.3 waves lose to dynamic
 
 
 def test_small_or_skewed_batches_take_the_dynamic_schedule():
     assert plan([512] * 4, 8, 2) == 0             # configs[0]: 8 items
-    assert plan([8192] * 256, 8, 1) == 0          # configs[3] at tp = 8: 256 items < 296 slots
+    assert plan([8192] * 100, 8, 1) == 0          # 100 items on 296 slots: a third of the SMs would idle
     assert plan([32768] + [200] * 63) == 0        # one long prompt among short ones
     assert plan(list(range(100, 6500, 100))) == 0
 

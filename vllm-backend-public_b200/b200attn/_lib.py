@@ -43,6 +43,7 @@ SIGNATURES = {
                                    f32, i32, vp, vp, vp]),
     "b2_prefill_attention": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64,
                                    i64, i64, f32, i32, vp, vp, vp]),
+    "b2_dequant_kv_blocks": (i32, [vp, vp, vp, vp, vp, i64, i32, i32, i32, i64, i64, vp]),
     "b2_rms_norm": (i32, [vp, vp, vp, vp, i32, i32, i64, i64, i64, f32, vp]),
     "b2_silu_and_mul": (i32, [vp, vp, i32, i32, i64, i64, vp]),
     "b2_rope_and_cache": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, vp, vp, vp]),

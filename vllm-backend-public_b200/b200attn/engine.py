@@ -80,9 +80,9 @@ class LLMEngine:
                  kv_cache_dtype: str = "auto"):
         if not torch.cuda.is_available():
             raise RuntimeError("b200attn engine needs a CUDA device: there is no CPU path")
-        if kv_cache_dtype not in ("auto", "bfloat16", "bf16"):
-            raise ValueError(f"kv-cache-dtype {kv_cache_dtype!r}: the serving engine keeps a bf16 KV cache "
-                             "(the fp8-e4m3 cache is available to b2_paged_decode / b2_reshape_and_cache callers)")
+        if kv_cache_dtype not in ("auto", "bfloat16", "bf16", "fp8", "fp8_e4m3"):
+            raise ValueError(f"kv-cache-dtype {kv_cache_dtype!r}: supported are auto / bfloat16 / fp8 (= fp8_e4m3)")
+        self.kv_dtype = torch.uint8 if kv_cache_dtype.startswith("fp8") else torch.bfloat16
         self.dev = device or torch.device("cuda", torch.cuda.current_device())
         torch.cuda.set_device(self.dev)
         self.cfg = cfg
@@ -97,7 +97,7 @@ class LLMEngine:
         # weights first, then size the block pool from what is left (gpu_memory_utilization of the whole device)
         free0, total = torch.cuda.mem_get_info(self.dev)
         self.model = LlamaModel(cfg, self.dev, num_blocks=1, block_size=block_size, seed=seed, weights_dir=weights_dir,
-                                max_position=self.max_model_len)
+                                max_position=self.max_model_len, kv_dtype=self.kv_dtype)
         del self.model.kv
         if num_blocks is None:
             util = gpu_memory_utilization if gpu_memory_utilization and gpu_memory_utilization > 0 else 0.9
@@ -107,7 +107,7 @@ class LLMEngine:
             act = self.max_num_batched_tokens * (3 * cfg.inter + self.model.qkv_width + 6 * cfg.hidden) * 2 \
                 + max_num_seqs * cfg.vocab * 2 * 2 + (1 << 30)
             budget = int(total * util) - used - act
-            per_block = cfg.kv_bytes_per_token() * block_size
+            per_block = cfg.kv_bytes_per_token(1 if self.kv_dtype == torch.uint8 else 2) * block_size
             want = max_num_seqs * self.max_nb + 64                   # every sequence at max_model_len
             num_blocks = max(min(budget // per_block, want), 0)
             if num_blocks < self.max_nb + 1:
@@ -115,7 +115,7 @@ class LLMEngine:
                                    f"{self.max_model_len} (gpu_memory_utilization {util}, {free1 >> 20} MiB free)")
         self.num_blocks = int(num_blocks)
         self.model.num_blocks = self.num_blocks
-        self.model.kv = torch.zeros(cfg.layers, 2, self.num_blocks, cfg.Hkv, block_size, cfg.d, dtype=torch.bfloat16,
+        self.model.kv = torch.zeros(cfg.layers, 2, self.num_blocks, cfg.Hkv, block_size, cfg.d, dtype=self.kv_dtype,
                                     device=self.dev)
         self.sched = Scheduler(self.num_blocks, block_size, max_num_seqs, self.max_model_len, self.max_num_batched_tokens)
 
@@ -310,7 +310,8 @@ class LLMEngine:
         self._np_bt[:nd, :used] = plan.block_tables[:, :used]
         self._np_temp[:bucket] = 0
         self._np_temp[:nd] = [r.params.temperature for r in reqs]
-        num_splits = ops.plan_num_splits(self._h_i32[B:B + nd], self.cfg.Hq, self.cfg.Hkv, self.cfg.d, self.block_size)
+        num_splits = ops.plan_num_splits(self._h_i32[B:B + nd], self.cfg.Hq, self.cfg.Hkv, self.cfg.d, self.block_size,
+                                         ops.KV_FP8_E4M3 if self.kv_dtype == torch.uint8 else ops.KV_BF16)
         replay = self._decode_graph(bucket, num_splits)
         with torch.cuda.stream(self._stream):
             self._d_i64.copy_(self._h_i64, non_blocking=True)
@@ -369,7 +370,8 @@ class LLMEngine:
         if nd:
             used = (int(plan.seq_lens.max()) + bsz - 1) // bsz
             self._np_bt[:nd, :used] = plan.block_tables[:, :used]
-            num_splits = ops.plan_num_splits(self._hm_meta[:nd], self.cfg.Hq, self.cfg.Hkv, self.cfg.d, bsz)
+            num_splits = ops.plan_num_splits(self._hm_meta[:nd], self.cfg.Hq, self.cfg.Hkv, self.cfg.d, bsz,
+                                                 ops.KV_FP8_E4M3 if self.kv_dtype == torch.uint8 else ops.KV_BF16)
         dev = self.dev
         with torch.cuda.stream(self._stream):
             d_tok = self._hm_tok[:T].to(dev, non_blocking=True)
@@ -384,7 +386,8 @@ class LLMEngine:
                 self._d_bt[:nd, :used].copy_(self._h_bt[:nd, :used], non_blocking=True)
                 dec_bt, dec_sl = self._d_bt[:nd], d_meta[:nd]
             pf = PrefillBatch(cu_q=d_meta[B:B + npf + 1], ctx_start=d_meta[2 * B + 1:2 * B + 1 + npf],
-                              block_tables=d_pbt, total_tokens=Tp)
+                              block_tables=d_pbt, total_tokens=Tp,
+                              kv_lens_host=(plan.prefill_start + plan.prefill_len).tolist())
             logits = self.model.forward(d_tok, d_pos, d_slot, nd, dec_bt, dec_sl, pf, d_aux[B:B + max(ns, 1)], num_splits)
             if ns:
                 out = ops.sample(logits, d_temp[:ns], d_aux[:ns])

@@ -128,6 +128,7 @@ class PrefillBatch:
     ctx_start: torch.Tensor       # int32 [n]
     block_tables: torch.Tensor    # int32 [n, max_nb]
     total_tokens: int
+    kv_lens_host: Optional[list] = None   # [ctx_start[c] + len_c] as host ints (fp8 cache: sizes the bf16 scratch)
 
 
 class LlamaModel:
@@ -231,6 +232,15 @@ class LlamaModel:
         resid = w["embed"].index_select(0, tokens)                       # [T, hidden]  (residual stream, bf16)
         x = ops.rms_norm(resid, w["l0.ln1"], c.eps)
         attn = torch.empty(T, c.Hq, c.d, dtype=torch.bfloat16, device=self.dev)
+        fp8_plan = None
+        if self.k_scale is not None and prefill is not None and prefill.total_tokens:
+            kv_lens = prefill.kv_lens_host
+            if kv_lens is None:      # one device read; the engine passes the scheduler's host copy instead
+                kv_lens = (prefill.ctx_start.long() + (prefill.cu_q[1:] - prefill.cu_q[:-1]).long()).cpu().tolist()
+            src, sbt = ops.fp8_prefill_plan(prefill.block_tables, kv_lens, self.bs)
+            shape = (src.numel(), c.Hkv, self.bs, c.d)
+            fp8_plan = (src, sbt, torch.empty(shape, dtype=torch.bfloat16, device=self.dev),
+                        torch.empty(shape, dtype=torch.bfloat16, device=self.dev))
         for l in range(c.layers):
             if l > 0:
                 x = ops.rms_norm(x, w[f"l{l}.ln1"], c.eps, residual=resid, out=x)
@@ -244,8 +254,15 @@ class LlamaModel:
                                  workspace=self.decode_workspace(n_decode, dec_block_tables.shape[1]),
                                  num_splits=num_splits)
             if prefill is not None and prefill.total_tokens:
-                ops.prefill_attention(q[n_decode:], kc, vc, prefill.block_tables, prefill.cu_q, prefill.ctx_start,
-                                      total_tokens=prefill.total_tokens, out=attn[n_decode:])
+                if fp8_plan is None:
+                    ops.prefill_attention(q[n_decode:], kc, vc, prefill.block_tables, prefill.cu_q, prefill.ctx_start,
+                                          total_tokens=prefill.total_tokens, out=attn[n_decode:])
+                else:
+                    # fp8 cache: the blocks the chunks can see, as bf16, in a scratch cache shared by all layers
+                    ops.dequant_kv_blocks(kc, vc, fp8_plan[0], k_out=fp8_plan[2], v_out=fp8_plan[3])
+                    ops.prefill_attention(q[n_decode:], fp8_plan[2], fp8_plan[3], fp8_plan[1], prefill.cu_q,
+                                          prefill.ctx_start, total_tokens=prefill.total_tokens, out=attn[n_decode:],
+                                          k_scale=self.k_scale, v_scale=self.v_scale)
             o = torch.nn.functional.linear(attn.view(T, c.Hq * c.d), w[f"l{l}.wo"])
             x = ops.rms_norm(o, w[f"l{l}.ln2"], c.eps, residual=resid, out=o)
             gu = torch.nn.functional.linear(x, w[f"l{l}.wgu"])

@@ -186,19 +186,88 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
 # ------------------------------------------------------------------------------------------------
 # prompt-chunk attention and the element-wise ops of a decoder layer
 # ------------------------------------------------------------------------------------------------
+def dequant_kv_blocks(k_cache: torch.Tensor, v_cache: torch.Tensor, src_blocks: torch.Tensor,
+                      k_out: Optional[torch.Tensor] = None, v_out: Optional[torch.Tensor] = None):
+    """bf16 copies of the fp8-e4m3 cache blocks `src_blocks` (device int32 [n]): out block i = float(e4m3) of block
+    src_blocks[i], exact in bf16 and still unscaled (b2_dequant_kv_blocks).  Returns (k_out, v_out),
+    bf16 [n, Hkv, bs, d]; pass the cache's k_scale / v_scale to prefill_attention together with them."""
+    lib = _lib.load()
+    dev = _need_cuda(k_cache=k_cache, v_cache=v_cache, src_blocks=src_blocks, k_out=k_out, v_out=v_out)
+    nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+    if _kv_dtype_of(k_cache) != KV_FP8_E4M3:
+        raise ValueError("dequant_kv_blocks needs an fp8 (uint8) cache")
+    if src_blocks.dtype != torch.int32 or src_blocks.dim() != 1 or not src_blocks.is_contiguous():
+        raise ValueError("src_blocks must be a contiguous int32 [n]")
+    n = src_blocks.numel()
+    shape = (n, Hkv, bs, d)
+    outs = []
+    for o in (k_out, v_out):
+        if o is None:
+            o = torch.empty(shape, dtype=torch.bfloat16, device=dev)
+        elif o.dtype != torch.bfloat16 or tuple(o.shape) != shape or not o.is_contiguous():
+            raise ValueError(f"k_out / v_out must be contiguous bf16 {list(shape)}")
+        outs.append(o)
+    _lib.check(lib.b2_dequant_kv_blocks(_ptr(outs[0]), _ptr(outs[1]), _ptr(k_cache), _ptr(v_cache), _ptr(src_blocks),
+                                        n, Hkv, d, bs, bstride, hstride, _stream(dev)))
+    return outs[0], outs[1]
+
+
+def fp8_prefill_plan(block_tables: torch.Tensor, kv_lens_host, bs: int):
+    """For prompt chunks over an fp8 cache: which cache blocks to dequantise and the block table of the scratch
+    cache they land in.  kv_lens_host[c] = ctx_start[c] + len_c (host ints: the scheduler knows them).
+    Returns (src_blocks device int32 [n], scratch_block_tables device int32 [n_chunks, max nb_c])."""
+    n_chunks = block_tables.shape[0]
+    nbs = [(int(L) + bs - 1) // bs for L in kv_lens_host]
+    if len(nbs) != n_chunks or max(nbs, default=0) > block_tables.shape[1]:
+        raise ValueError("kv_lens_host does not match the chunks / block_tables")
+    dev = block_tables.device
+    rows = torch.repeat_interleave(torch.arange(n_chunks), torch.tensor(nbs, dtype=torch.int64))
+    cols = torch.cat([torch.arange(n) for n in nbs]) if nbs else torch.zeros(0, dtype=torch.int64)
+    src = block_tables[rows.to(dev), cols.to(dev)].contiguous()
+    bt = torch.zeros(n_chunks, max(max(nbs, default=1), 1), dtype=torch.int32)
+    off = 0
+    for c, n in enumerate(nbs):
+        bt[c, :n] = torch.arange(off, off + n, dtype=torch.int32)
+        off += n
+    return src, bt.to(dev)
+
+
+def _prefill_over_fp8(q, k_cache, v_cache, block_tables, cu_q, ctx_start, total_tokens, scale, out, k_scale, v_scale,
+                      kv_lens_host):
+    """fp8 cache: gather + dequantise the blocks each chunk can see into a bf16 scratch cache, then the bf16 kernel.
+    Without kv_lens_host one device read sizes the scratch."""
+    if kv_lens_host is None:
+        kv_lens_host = (ctx_start.to(torch.int64) + (cu_q[1:] - cu_q[:-1]).to(torch.int64)).cpu().tolist()
+    src, bt = fp8_prefill_plan(block_tables, kv_lens_host, k_cache.shape[2])
+    ks, vs = dequant_kv_blocks(k_cache, v_cache, src)
+    return prefill_attention(q, ks, vs, bt, cu_q, ctx_start, total_tokens, scale, out, k_scale, v_scale)
+
+
 def prefill_attention(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_tables: torch.Tensor,
                       cu_q: torch.Tensor, ctx_start: torch.Tensor, total_tokens: Optional[int] = None,
-                      scale: Optional[float] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                      scale: Optional[float] = None, out: Optional[torch.Tensor] = None,
+                      k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None,
+                      kv_lens_host=None) -> torch.Tensor:
     """Causal attention of prompt chunks over the paged cache (b2_prefill_attention).
 
     q / out: bf16 [T, Hq, d] (token stride allowed); chunk c = rows cu_q[c]:cu_q[c+1], positions
     ctx_start[c] + i, blocks block_tables[c].  The chunk's K/V must already be in the cache.
-    `total_tokens` = cu_q[-1] as a host int (defaults to q.shape[0]; it sizes the grid without a device sync)."""
+    `total_tokens` = cu_q[-1] as a host int (defaults to q.shape[0]; it sizes the grid without a device sync).
+    fp8 caches (uint8 + k_scale / v_scale): the visible blocks are dequantised into a bf16 scratch cache first
+    (b2_dequant_kv_blocks); pass kv_lens_host = [ctx_start[c] + len_c] to size it without a device read.
+    bf16 caches with k_scale / v_scale: the cache is taken to hold K / k_scale and V / v_scale (that scratch)."""
     lib = _lib.load()
     dev = _need_cuda(q=q, k_cache=k_cache, v_cache=v_cache, block_tables=block_tables, cu_q=cu_q,
-                     ctx_start=ctx_start, out=out)
+                     ctx_start=ctx_start, out=out, k_scale=k_scale, v_scale=v_scale)
     nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
     kvd = _kv_dtype_of(k_cache)
+    if kvd == KV_FP8_E4M3:
+        if k_scale is None or v_scale is None:
+            raise ValueError("fp8 KV cache needs 1-element fp32 device tensors k_scale / v_scale")
+        if ctx_start.numel() == 0 or q.shape[0] == 0:
+            return out if out is not None else torch.empty_like(q)
+        return _prefill_over_fp8(q, k_cache, v_cache, block_tables, cu_q, ctx_start, total_tokens, scale, out,
+                                 k_scale, v_scale, kv_lens_host)
     if q.dtype != torch.bfloat16 or q.dim() != 3 or q.shape[2] != d or q.stride(2) != 1 or q.stride(1) != d:
         raise ValueError(f"q must be bf16 [T, Hq, {d}] with contiguous head/dim axes")
     T, Hq, _ = q.shape
@@ -225,7 +294,7 @@ def prefill_attention(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
         _ptr(out), _ptr(q), _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(cu_q), _ptr(ctx_start),
         n_chunks, total_tokens, Hq, Hkv, d, bs, block_tables.shape[1], nb,
         q.stride(0) if T > 1 else Hq * d, out.stride(0) if T > 1 else Hq * d, bstride, hstride,
-        float(scale), kvd, None, None, _stream(dev)))
+        float(scale), kvd, _ptr(k_scale), _ptr(v_scale), _stream(dev)))
     return out
 
 

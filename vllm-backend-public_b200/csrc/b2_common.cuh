@@ -44,7 +44,7 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
                             const int32_t* block_tables, const int32_t* cu_q, const int32_t* ctx_start, int n_chunks,
                             int T, int Hq, int Hkv, int bs, int max_nb, int64_t num_blocks, int64_t q_stride,
                             int64_t out_stride, int64_t cache_block_stride, int64_t cache_head_stride, float scale,
-                            void* stream);
+                            const float* k_scale, const float* v_scale, void* stream);
 
 static inline bool b2_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

@@ -48,6 +48,8 @@ struct PrefillParams {
     int n_chunks, Hq, G, bs, max_nb;
     int64_t q_stride, out_stride;
     float scale_log2;
+    const float* k_scale;          // optional device scalars: the cache holds K / k_scale and V / v_scale
+    const float* v_scale;          // (an fp8 cache dequantised into bf16 scratch blocks, exactly)
 };
 
 __device__ __forceinline__ uint32_t tile_addr(uint32_t base, int row, int chunk) {
@@ -159,7 +161,7 @@ prefill_mma_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constan
 #pragma unroll
     for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
     float m_a = -INFINITY, m_b = -INFINITY, l_a = 0.f, l_b = 0.f;
-    const float sl2 = p.scale_log2;
+    const float sl2 = p.scale_log2 * (p.k_scale ? *p.k_scale : 1.f);
     // last visible key of rows a / b (padding rows behave like the tile's last valid row)
     const int lim_a = start + q0 + min(wr + g, rows - 1);
     const int lim_b = start + q0 + min(wr + g + 8, rows - 1);
@@ -269,7 +271,8 @@ prefill_mma_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constan
     l_a += __shfl_xor_sync(0xffffffffu, l_a, 2);
     l_b += __shfl_xor_sync(0xffffffffu, l_b, 1);
     l_b += __shfl_xor_sync(0xffffffffu, l_b, 2);
-    const float inv_a = 1.f / l_a, inv_b = 1.f / l_b;
+    const float vsc = p.v_scale ? *p.v_scale : 1.f;
+    const float inv_a = vsc / l_a, inv_b = vsc / l_b;
     __nv_bfloat16* oa = p.out + (int64_t)(row0 + wr + g) * p.out_stride + (int64_t)hq * D;
     __nv_bfloat16* ob = oa + 8 * p.out_stride;
     const bool va = wr + g < rows, vb = wr + g + 8 < rows;
@@ -292,7 +295,6 @@ extern "C" int b2_prefill_attention(void* out, const void* q, const void* k_cach
                                     int64_t num_blocks, int64_t q_stride, int64_t out_stride,
                                     int64_t cache_block_stride, int64_t cache_head_stride, float scale, int kv_dtype,
                                     const float* k_scale, const float* v_scale, void* stream) {
-    (void)k_scale; (void)v_scale;
     B2_REQUIRE(n_chunks >= 0 && T >= 0 && Hq > 0 && Hkv > 0 && max_nb > 0 && num_blocks > 0, B2_EINVAL,
                "prefill_attention: bad sizes n_chunks=%d T=%d Hq=%d Hkv=%d max_nb=%d", n_chunks, T, Hq, Hkv, max_nb);
     if (n_chunks == 0 || T == 0) return B2_OK;
@@ -317,7 +319,7 @@ extern "C" int b2_prefill_attention(void* out, const void* q, const void* k_cach
     if (!use_mma)
         return b2_internal_prefill_tc5(out, q, k_cache, v_cache, block_tables, cu_q, ctx_start, n_chunks, T, Hq, Hkv, bs,
                                        max_nb, num_blocks, q_stride, out_stride, cache_block_stride, cache_head_stride,
-                                       scale, stream);
+                                       scale, k_scale, v_scale, stream);
 
     CUtensorMap tmK, tmV;
     int rc = b2_internal_make_cache_tmap(&tmK, k_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride);
@@ -339,6 +341,8 @@ extern "C" int b2_prefill_attention(void* out, const void* q, const void* k_cach
     p.q_stride = q_stride;
     p.out_stride = out_stride;
     p.scale_log2 = scale * LOG2E;
+    p.k_scale = k_scale;
+    p.v_scale = v_scale;
 
     static bool attr_set = false;
     if (!attr_set) {

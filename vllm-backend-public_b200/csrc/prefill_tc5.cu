@@ -49,6 +49,8 @@ struct Tc5Params {
     int rows_per_cta;      // 256 (tiles A and B) or 128 (tile A only: small batches fill the 148 SMs better)
     int64_t out_stride;
     float scale_log2;
+    const float* k_scale;  // optional device scalars: the cache holds K / k_scale and V / v_scale (dequantised fp8)
+    const float* v_scale;
 };
 
 // ---- tcgen05 wrappers --------------------------------------------------------------------------
@@ -322,7 +324,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             const uint32_t lane_off = (uint32_t)(wq * 32) << 16;
             const uint32_t s_addr = tmem + lane_off + x * 128, o_addr = tmem + lane_off + 256 + x * 128;
             const int n = nX[x];
-            const float sl2 = p.scale_log2;
+            const float sl2 = p.scale_log2 * (p.k_scale ? *p.k_scale : 1.f);
             const int lim = start + q0 + x * BM + min(row, max(rowsX[x] - 1, 0));   // last key this row may see
             const int lim_min = start + q0 + x * BM;                                 // ... of the tile's first row
             float m = -INFINITY, l = 0.f;
@@ -400,7 +402,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             if (n > 0) {
                 b2::mbar_wait(bar(BAR_PV + x), (n - 1) & 1);
                 tc_fence_after();
-                const float inv = 1.f / l;
+                const float inv = (p.v_scale ? *p.v_scale : 1.f) / l;
                 const bool valid = row < rowsX[x];
                 __nv_bfloat16* orow = p.out + (int64_t)(row0 + x * BM + row) * p.out_stride + (int64_t)hq * D;
 #pragma unroll
@@ -440,7 +442,7 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
                             const int32_t* block_tables, const int32_t* cu_q, const int32_t* ctx_start, int n_chunks,
                             int T, int Hq, int Hkv, int bs, int max_nb, int64_t num_blocks, int64_t q_stride,
                             int64_t out_stride, int64_t cache_block_stride, int64_t cache_head_stride, float scale,
-                            void* stream) {
+                            const float* k_scale, const float* v_scale, void* stream) {
     // 256 query rows per CTA share each K/V stage between two tiles; when that leaves SMs idle, 128 rows per CTA
     static const int n_sm = []() { int dev = 0, n = 148; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); return n; }();
     const int rows_per_cta = ((int64_t)T / (2 * BM) + n_chunks) * Hq < n_sm ? BM : 2 * BM;      // less than one wave
@@ -476,6 +478,8 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
     p.rows_per_cta = rows_per_cta;
     p.out_stride = out_stride;
     p.scale_log2 = scale * LOG2E;
+    p.k_scale = k_scale;
+    p.v_scale = v_scale;
     // share of the softmax weights computed by polynomial (B2_PREFILL_POLY = 0..3 of every 4; A/B knob)
     static const int poly = []() { const char* e = getenv("B2_PREFILL_POLY"); return e && *e ? atoi(e) : 0; }();
     auto kern = poly <= 0 ? prefill_tc5_kernel<0> : poly == 1 ? prefill_tc5_kernel<1> : poly == 2 ? prefill_tc5_kernel<2>

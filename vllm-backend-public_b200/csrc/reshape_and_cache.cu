@@ -76,6 +76,38 @@ reshape_and_cache_kernel(const __nv_bfloat16* __restrict__ k_new,
     }
 }
 
+// fp8 -> bf16 gather of whole cache blocks: out block i = float(e4m3 block src[i]), exact in bf16 (4 significant
+// bits, exponent range inside bf16's); the per-tensor scales are applied by the consumer (b2_prefill_attention).
+// grid (n blocks, K|V); a thread converts 16 cache bytes per trip (one 16-byte load, two 16-byte stores).
+__global__ void __launch_bounds__(256)
+dequant_blocks_kernel(__nv_bfloat16* __restrict__ k_out, __nv_bfloat16* __restrict__ v_out,
+                      const uint8_t* __restrict__ k_cache, const uint8_t* __restrict__ v_cache,
+                      const int32_t* __restrict__ src_blocks, int Hkv, int row_elems /* bs * d */,
+                      int64_t cache_block_stride, int64_t cache_head_stride) {
+    const int64_t i = blockIdx.x;
+    const bool is_v = blockIdx.y != 0;
+    const uint8_t* src = (is_v ? v_cache : k_cache) + (int64_t)src_blocks[i] * cache_block_stride;
+    __nv_bfloat16* dst = (is_v ? v_out : k_out) + i * (int64_t)Hkv * row_elems;
+    const int vec_per_head = row_elems >> 4;
+    for (int v = threadIdx.x; v < Hkv * vec_per_head; v += blockDim.x) {
+        const int h = v / vec_per_head, c = v - h * vec_per_head;
+        const uint4 raw = *reinterpret_cast<const uint4*>(src + (int64_t)h * cache_head_stride + c * 16);
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+        uint32_t o[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                const __half2_raw h2 = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(w[q] >> (16 * hh)), __NV_E4M3);
+                const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&h2));
+                o[q * 2 + hh] = b2::pack_bf16x2(f.x, f.y);
+            }
+        uint4* d4 = reinterpret_cast<uint4*>(dst + (int64_t)h * row_elems + c * 16);
+        d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    }
+}
+
 }  // namespace
 
 extern "C" int b2_reshape_and_cache(const void* k_new, const void* v_new, void* k_cache,
@@ -118,6 +150,27 @@ extern "C" int b2_reshape_and_cache(const void* k_new, const void* v_new, void* 
             kn, vn, k_cache, v_cache, slot_mapping, Hkv, d, bs, k_token_stride, v_token_stride,
             cache_block_stride, cache_head_stride, k_scale, v_scale);
     }
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}
+
+extern "C" int b2_dequant_kv_blocks(void* k_out, void* v_out, const void* k_cache, const void* v_cache,
+                                    const int32_t* src_blocks, int64_t n, int Hkv, int d, int bs,
+                                    int64_t cache_block_stride, int64_t cache_head_stride, void* stream) {
+    B2_REQUIRE(n >= 0 && Hkv > 0 && d > 0 && bs > 0, B2_EINVAL, "dequant_kv_blocks: bad sizes n=%lld Hkv=%d d=%d bs=%d",
+               (long long)n, Hkv, d, bs);
+    if (n == 0) return B2_OK;
+    B2_REQUIRE(k_out && v_out && k_cache && v_cache && src_blocks, B2_EINVAL,
+               "dequant_kv_blocks: null pointer");
+    B2_REQUIRE(((int64_t)bs * d) % 16 == 0, B2_EUNSUPPORTED, "dequant_kv_blocks: bs * d = %d must be a multiple of 16", bs * d);
+    B2_REQUIRE(b2_aligned16(k_out) && b2_aligned16(v_out) && b2_aligned16(k_cache) && b2_aligned16(v_cache), B2_EINVAL,
+               "dequant_kv_blocks: pointers must be 16-byte aligned");
+    B2_REQUIRE(cache_block_stride % 16 == 0 && cache_head_stride % 16 == 0 && cache_head_stride >= (int64_t)bs * d,
+               B2_EINVAL, "dequant_kv_blocks: cache strides must keep 16-byte alignment");
+    B2_REQUIRE(n <= 0x7fffffffLL, B2_EUNSUPPORTED, "dequant_kv_blocks: %lld blocks exceed the grid", (long long)n);
+    dequant_blocks_kernel<<<dim3((unsigned)n, 2), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<__nv_bfloat16*>(k_out), static_cast<__nv_bfloat16*>(v_out), static_cast<const uint8_t*>(k_cache),
+        static_cast<const uint8_t*>(v_cache), src_blocks, Hkv, bs * d, cache_block_stride, cache_head_stride);
     B2_CUDA_OK(cudaGetLastError());
     return B2_OK;
 }
