@@ -19,6 +19,9 @@ ap.add_argument("--skip-model", action="store_true")
 ap.add_argument("--model", default="llama-3-8b")
 ap.add_argument("--steps", type=int, default=100)
 ap.add_argument("--only", choices=["all", "prefill", "ops", "decode"], default="all")
+ap.add_argument("--batch", type=int, default=64)
+ap.add_argument("--ctx", type=int, default=4096)
+ap.add_argument("--kv", choices=["auto", "fp8"], default="auto", help="KV cache dtype of the whole-model decode run")
 a = ap.parse_args()
 dev = torch.device("cuda:0")
 peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
@@ -112,13 +115,18 @@ torch.cuda.empty_cache()
 from b200attn.engine import LLMEngine, SamplingParams  # noqa: E402
 from b200attn.model import resolve_config  # noqa: E402
 cfg = resolve_config(a.model)
-B, ctx = 64, 4096
-eng = LLMEngine(cfg, dev, max_num_seqs=B, max_model_len=ctx + a.steps + 64, max_num_batched_tokens=8192)
+B, ctx = a.batch, a.ctx
+eng = LLMEngine(cfg, dev, max_num_seqs=B, max_model_len=ctx + a.steps + 64, max_num_batched_tokens=8192,
+                kv_cache_dtype=a.kv)
+kv_elem = 1 if a.kv == "fp8" else 2
 import random  # noqa: E402
 rng = random.Random(0)
 t0 = time.perf_counter()
 for i in range(B):
     eng.add_request([rng.randrange(cfg.vocab) for _ in range(ctx - 1)], SamplingParams(max_tokens=a.steps + 40, temperature=0.0))
+if ctx + a.steps + 40 > eng.max_model_len:
+    sys.exit(f"ctx {ctx} + {a.steps + 40} new tokens exceed max_model_len {eng.max_model_len} of {cfg.name} "
+             "(use --model llama-3.1-8b for contexts past 8k)")
 while eng.sched.num_waiting or eng.stats.decode_steps < 5:           # prefill + 5 warm-up decode steps
     eng.step()
 t_prefill = time.perf_counter() - t0
@@ -134,10 +142,10 @@ toks = eng.stats.generated_tokens - n0
 replay = eng._graphs[(B, 1)] if (B, 1) in eng._graphs else list(eng._graphs.values())[-1]
 with torch.cuda.stream(eng._stream):
     med, best = timeit(replay, iters=20)
-kv_bytes = B * ctx * cfg.kv_bytes_per_token()
+kv_bytes = B * ctx * cfg.kv_bytes_per_token(kv_elem)
 w_bytes = eng.model.weight_bytes() - cfg.vocab * cfg.hidden * 2        # the embedding table is gathered, not streamed
 ceiling = B / ((kv_bytes + w_bytes) / (HBM * 1e9))
-emit(op="decode_tok_s", model=cfg.name, B=B, ctx=ctx, steps=a.steps, e2e_tok_s=toks / wall, e2e_ms_per_step=wall / a.steps * 1e3,
+emit(op="decode_tok_s", model=cfg.name, kv_cache=a.kv, B=B, ctx=ctx, steps=a.steps, e2e_tok_s=toks / wall, e2e_ms_per_step=wall / a.steps * 1e3,
      device_ms_per_step=med, device_tok_s=B / med * 1e3, hbm_bytes_per_step=kv_bytes + w_bytes,
      roofline_tok_s_at_measured_hbm=ceiling, frac_of_roofline=(B / med * 1e3) / ceiling,
      achieved_GBps=(kv_bytes + w_bytes) / med / 1e6, prefill_s=t_prefill, prefill_tok_s=B * (ctx - 1) / t_prefill,
