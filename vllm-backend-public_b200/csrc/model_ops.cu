@@ -157,7 +157,7 @@ __device__ __forceinline__ void store_cache8(void* cache, int64_t elem, const fl
 }
 
 template <bool FP8>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)      // <= 48 registers: five CTAs (40 warps) per SM keep the loads in flight
 rope_and_cache_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ positions,
                       const float* __restrict__ cos_sin, int max_pos, void* __restrict__ k_cache,
                       void* __restrict__ v_cache, const int64_t* __restrict__ slot_mapping, int Hq, int Hkv, int d, int bs,
