@@ -270,6 +270,16 @@ def run_ours(args, wl_name, wl):
     kv_bytes = 1 if fp8 else 2
     prob = build_problem(dev, B, Hq_l, Hkv_l, ctx, fp8, seed=rank)
     bytes_rank = algorithmic_bytes(B, Hq_l, Hkv_l, ctx, kv_bytes)
+    if args.ragged:
+        # experiment (not a BASELINE config): sequence lengths log-uniform in [128, ctx], the shape of a serving batch
+        g = torch.Generator().manual_seed(1234)
+        lens = torch.exp(torch.empty(B).uniform_(math.log(128.0), math.log(float(ctx)), generator=g)).to(torch.int32)
+        lens = lens.clamp_(128, ctx)
+        prob["seq_lens"] = lens
+        last = (lens - 1).long()
+        prob["slot_new"] = prob["block_tables"][torch.arange(B), last // BS].to(torch.int64) * BS + last % BS
+        nbs = (lens.long() + BS - 1) // BS
+        bytes_rank = int(lens.long().sum()) * 2 * Hkv_l * D * kv_bytes + 2 * B * Hq_l * D * 2 + int(nbs.sum()) * 4 + B * 4
 
     bt_d = prob["block_tables"].to(dev)
     sl_d = prob["seq_lens"].to(dev)
@@ -397,7 +407,7 @@ def run_ours(args, wl_name, wl):
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
             "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "strong" if args.strong else "weak", "vs_baseline": None,
             "dtype": "bf16" if not fp8 else "fp8_e4m3 KV / bf16 q,out (fp32 accumulate)", "data": "synthetic",
-            "config": {"workload": wl_name, "global_batch": B, "ctx": ctx, "Hq": wl["Hq"], "Hkv": wl["Hkv"], "d": D,
+            "config": {"workload": wl_name + ("+ragged(log-uniform 128..ctx)" if args.ragged else ""), "global_batch": B, "ctx": ctx, "Hq": wl["Hq"], "Hkv": wl["Hkv"], "d": D,
                        "block_size": BS, "kv_dtype": "fp8_e4m3" if fp8 else "bf16",
                        "parallelism": f"kv-head-shard tp{tp}" if tp > 1 else "1 GPU",
                        "collective": "none on the attention path" + (f"; optional NCCL all-gather of out [B, Hq, d]: {allgather_us} us"
@@ -449,6 +459,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--strong", action="store_true", help="N > 1: keep the global batch fixed (strong scaling)")
     ap.add_argument("--batch", type=int, default=0, help="override the workload batch size (experiments only)")
+    ap.add_argument("--ragged", action="store_true",
+                    help="experiment: sequence lengths log-uniform in [128, ctx] instead of all = ctx")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.batch:

@@ -26,6 +26,16 @@ def test_small_or_skewed_batches_take_the_dynamic_schedule():
     assert plan(list(range(100, 6500, 100))) == 0
 
 
+def test_ragged_serving_batches_take_the_dynamic_schedule():
+    """log-uniform 128..ctx lengths: the per-item pipeline ramp of the single-pass grid costs more than the dynamic
+    schedule's ~4 % (measured +9 % / +7 % for configs[3] / configs[1] shapes, scripts/gpu_ragged.sh)."""
+    import math
+    g = torch.Generator().manual_seed(1234)
+    for B, ctx, Hq, Hkv in ((256, 8192, 64, 8), (64, 4096, 32, 8)):
+        lens = torch.exp(torch.empty(B).uniform_(math.log(128.0), math.log(float(ctx)), generator=g)).to(torch.int32)
+        assert b200attn.plan_num_splits(lens.clamp_(128, ctx).contiguous(), Hq, Hkv) == 0
+
+
 def test_bad_arguments():
     import pytest
     with pytest.raises(ValueError):
