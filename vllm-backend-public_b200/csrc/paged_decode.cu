@@ -1348,20 +1348,21 @@ extern "C" int b2_paged_decode_plan_splits(const int32_t* seq_lens_host, int B, 
     // dynamic schedule at 6.1 -- BASELINE configs[3] at tp = 8; the model below rejects the really short grids)
     (void)items;
     constexpr int64_t OVERHEAD_TOK = 128;   // CTA launch + pipeline fill, in streamed-token equivalents
-    std::vector<int64_t> slot((size_t)NC, 0);   // min-heap of slot finish times
+    // The ipb items of a sequence are equal and adjacent in grid order: they are placed together on a group of ipb
+    // slots (NC / ipb groups), which keeps this at one heap operation per sequence -- it runs on the host every step.
+    const int n_groups = NC / ipb > 0 ? NC / ipb : 1;
+    std::vector<int64_t> slot((size_t)n_groups, 0);   // min-heap of group finish times
     auto cmp = [](int64_t a, int64_t b) { return a > b; };
     int64_t total = 0, streamed = 0, makespan = 0;
     for (int b = 0; b < B; ++b) {
         const int64_t L = seq_lens_host[b] > 0 ? seq_lens_host[b] : 0;
-        for (int j = 0; j < ipb; ++j) {
-            std::pop_heap(slot.begin(), slot.end(), cmp);
-            int64_t& t = slot.back();
-            t += L + OVERHEAD_TOK;
-            if (t > makespan) makespan = t;
-            std::push_heap(slot.begin(), slot.end(), cmp);
-            total += L + OVERHEAD_TOK;
-            streamed += L;
-        }
+        std::pop_heap(slot.begin(), slot.end(), cmp);
+        int64_t& t = slot.back();
+        t += L + OVERHEAD_TOK;
+        if (t > makespan) makespan = t;
+        std::push_heap(slot.begin(), slot.end(), cmp);
+        total += (L + OVERHEAD_TOK) * ipb;
+        streamed += L * ipb;
     }
     const double ideal = (double)total / NC;
     // fp8 (three CTAs per SM) is paced by its consumer warps, not by HBM: an idle slot is lost throughput, so the
