@@ -80,6 +80,19 @@ B2_API int b2_reshape_and_cache(const void* k_new, const void* v_new,
                          int kv_dtype, const float* k_scale, const float* v_scale,
                          void* stream);
 
+/* Decode-step form of the KV write for engines that keep block_tables RESIDENT on the device: token t is the
+ * newest token of batch row t (position seq_lens[t] - 1), so besides writing K/V the call records the block its
+ * slot names, block_tables[t][(seq_lens[t] - 1) / bs] = slot_mapping[t] / bs (rows with slot < 0 are skipped).
+ * Rewritten every step (idempotent), so a step's host->device traffic is seq_lens + slot_mapping (O(B) words)
+ * instead of the whole [B, max_nb] table; a row is uploaded in full only when a new sequence takes it.
+ * block_tables: DEVICE int32 [B, max_nb]; seq_lens: DEVICE int32 [B].  Other arguments as b2_reshape_and_cache. */
+B2_API int b2_reshape_and_cache_decode(const void* k_new, const void* v_new, void* k_cache, void* v_cache,
+                                const int64_t* slot_mapping, int32_t* block_tables, const int32_t* seq_lens,
+                                int B, int Hkv, int d, int bs, int max_nb,
+                                int64_t k_token_stride, int64_t v_token_stride,
+                                int64_t cache_block_stride, int64_t cache_head_stride,
+                                int kv_dtype, const float* k_scale, const float* v_scale, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Paged-attention decode.  Replaces vLLM `paged_attention_v1/_v2` (csrc/attention/) for the decode
  * step of the engine behind the reference's launch contract; B <= VLLMConfig.max_num_seqs
@@ -92,6 +105,9 @@ B2_API int b2_reshape_and_cache(const void* k_new, const void* v_new,
  * b2_paged_decode_workspace_bytes(...) bytes for the same B/Hq/d/max_nb/bs/num_splits; it is
  * scratch (no state survives the call) and may be NULL when that size is 0.
  * ------------------------------------------------------------------------------------------- */
+/* The returned size serves every batch size 1..B of the geometry (the automatic schedule cuts smaller batches
+ * into finer chunks, so the need of one batch size alone is not monotone in B): size the workspace once for
+ * max_num_seqs and never reallocate it under captured CUDA graphs. */
 B2_API size_t b2_paged_decode_workspace_bytes(int B, int Hq, int Hkv, int d, int bs, int max_nb,
                                        int num_splits);
 
@@ -116,6 +132,26 @@ B2_API int b2_paged_decode(void* out, const void* q,
                     const float* k_scale, const float* v_scale,
                     void* workspace, size_t workspace_bytes, int num_splits,
                     void* stream);
+
+/* Per-engine decode handle: the same operation as b2_paged_decode with everything that does not change between
+ * steps fixed at creation -- cache pointers / strides (their two TMA descriptors are encoded once, a driver call
+ * each), geometry, scale, kv dtype and scales, the workspace.  A call then is argument checks + kernel launches:
+ * no driver call, no getenv, and two launches instead of three for the dynamic schedule (create zeroes the
+ * workspace header on `stream`; every call leaves it zeroed).  The handle is host memory only; the caller still owns
+ * caches and workspace, which must outlive it and must not be shared with other plans or b2_paged_decode calls
+ * in flight.  workspace_bytes >= b2_paged_decode_workspace_bytes(max_B, ..., 0).  NULL on bad arguments
+ * (b2_last_error).  Single-writer, like every handle of this library.  (vLLM analogue: the attention metadata
+ * builder + `paged_attention_v1/_v2` behind reference benchmark-vllm/vllm_manager.py:371-374.) */
+typedef struct b2_decode_plan b2_decode_plan;
+B2_API b2_decode_plan* b2_decode_plan_create(const void* k_cache, const void* v_cache, int max_B, int Hq, int Hkv,
+                                      int d, int bs, int max_nb, int64_t num_blocks,
+                                      int64_t cache_block_stride, int64_t cache_head_stride,
+                                      float scale, int kv_dtype, const float* k_scale, const float* v_scale,
+                                      void* workspace, size_t workspace_bytes, void* stream);
+B2_API void b2_decode_plan_destroy(b2_decode_plan* plan);
+B2_API int b2_decode_plan_run(b2_decode_plan* plan, void* out, const void* q,
+                       const int32_t* block_tables, const int32_t* seq_lens, int B,
+                       int64_t q_stride, int64_t out_stride, int num_splits, void* stream);
 
 /* Diagnostic / A-B variant kept for the ncu comparison DESIGN.md cites: the same contract as
  * b2_paged_decode, computed by a plain CUDA-core kernel (no TMA, no tensor cores).  Not used by

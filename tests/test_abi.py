@@ -63,6 +63,44 @@ def test_argument_validation_without_gpu():
     assert w > w4 > 256 and (w - hdr(64, 8)) % (8 * 129 * 4) == 0 and (w4 - hdr(4, 8)) % (8 * 129 * 4) == 0
 
 
+def test_workspace_bound_is_monotone_in_batch():
+    """the automatic schedule cuts smaller batches into finer chunks, so the bytes ONE batch size
+    needs are not monotone in B (B=24 needed more than B=32 at max_nb 512).  The exported size must serve every
+    batch 1..B, i.e. never shrink as B grows -- an engine sizes the workspace once for max_num_seqs and captures CUDA
+    graphs for every smaller bucket against that one buffer."""
+    from b200attn import _lib
+    lib = _lib.load()
+    for (Hq, Hkv, bs, max_nb) in [(32, 8, 16, 512), (32, 8, 16, 256), (64, 8, 16, 512), (8, 1, 16, 512), (32, 8, 8, 1024),
+                                  (32, 8, 32, 128), (4, 2, 16, 64)]:
+        prev = 0
+        for B in range(1, 301):
+            w = lib.b2_paged_decode_workspace_bytes(B, Hq, Hkv, 128, bs, max_nb, 0)
+            assert w >= prev, f"workspace bound shrinks at B={B} ({w} < {prev}) for Hq={Hq} Hkv={Hkv} bs={bs} max_nb={max_nb}"
+            prev = w
+    # the r1 counter-example: the bound for 32 must cover what 24 needs (finer chunks, more partial slots)
+    assert lib.b2_paged_decode_workspace_bytes(32, 32, 8, 128, 16, 512, 0) >= 9308896
+
+
+def test_decode_plan_rejects_bad_arguments_without_gpu():
+    from b200attn import _lib
+    lib = _lib.load()
+    assert lib.b2_decode_plan_create(None, None, 8, 8, 2, 128, 16, 32, 100, 4096, 2048, 0.088, 0, None, None, None, 0,
+                                     None) is None
+    assert b"null" in lib.b2_last_error()
+    assert lib.b2_decode_plan_create(16, 16, 0, 8, 2, 128, 16, 32, 100, 4096, 2048, 0.088, 0, None, None, None, 0,
+                                     None) is None
+    assert b"max_B" in lib.b2_last_error()
+    # a workspace smaller than b2_paged_decode_workspace_bytes(max_B, ...) is refused before any CUDA call
+    assert lib.b2_decode_plan_create(16, 16, 8, 8, 2, 128, 16, 32, 100, 4096, 2048, 0.088, 0, None, None, 16, 64,
+                                     None) is None
+    assert b"workspace" in lib.b2_last_error()
+    assert lib.b2_decode_plan_run(None, 16, 16, 16, 16, 1, 1024, 1024, 0, None) == _lib.B2_EINVAL
+    lib.b2_decode_plan_destroy(None)          # a no-op, like free(NULL)
+    rc = lib.b2_reshape_and_cache_decode(16, 16, 16, 16, 16, None, None, 4, 2, 128, 16, 32, 256, 256, 4096, 2048, 0,
+                                         None, None, None)
+    assert rc == _lib.B2_EINVAL and b"block_tables" in lib.b2_last_error()
+
+
 def test_ops_refuse_cpu_tensors():
     import torch
     import b200attn

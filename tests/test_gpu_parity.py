@@ -392,6 +392,7 @@ def test_decode_step_from_host_buffers(cuda, use_graph, zero_copy):
         step.h_qkv[:B, Hq:Hq + Hkv] = k_new
         step.h_qkv[:B, Hq + Hkv:] = v_new
         step.h_block_tables[:B] = inp["block_tables"]
+        step.upload_block_tables()
         step.h_seq_lens[:B] = inp["seq_lens"]
         step.h_slots[:B] = slots
         out = step.run(B).clone()
@@ -399,6 +400,118 @@ def test_decode_step_from_host_buffers(cuda, use_graph, zero_copy):
         ref = R.paged_decode_ref(q, kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
         assert_close(out, ref, what=f"DecodeStep graph={use_graph} step {it}")
     assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref))
+
+
+@pytest.mark.parametrize("fp8", [False, True])
+def test_decode_step_resident_tables_follow_the_sequences(cuda, fp8):
+    """Device-resident block tables: they are uploaded ONCE; then every sequence grows by one token per step across
+    several block boundaries, and the only per-step host->device words are seq_lens and slots.  The decode-step KV
+    write must keep the resident tables current (b2_reshape_and_cache_decode), checked against the oracle, which
+    is given the host-side tables the block manager would hold."""
+    B, Hq, Hkv, bs, ctx, steps = 5, 8, 2, 16, 70, 40
+    inp = R.make_inputs(B, Hq, Hkv, 128, bs, ctx + steps + bs, seed=31, ragged=False, slack_blocks=8)
+    lens = torch.tensor([1, 15, 16, 33, 70], dtype=torch.int32)                 # start lengths (tokens already cached)
+    keep = torch.cat([torch.arange((ctx + steps + bs) * b, (ctx + steps + bs) * b + int(lens[b])) for b in range(B)])
+    inp["k"], inp["v"], inp["slot_mapping"] = inp["k"][keep], inp["v"][keep], inp["slot_mapping"][keep]
+    inp["seq_lens"] = lens.clone()
+    kc, vc, kc_ref, vc_ref, sc = build_caches(inp, cuda, fp8=fp8)
+    okw, skw = {}, {}
+    if fp8:
+        ks, vs, ksd, vsd = sc
+        okw = dict(kv_dtype=R.KV_FP8_E4M3, k_scale=ks, v_scale=vs)
+        skw = dict(k_scale=ksd, v_scale=vsd)
+    full_bt = inp["block_tables"]                      # the blocks each sequence WILL own, in order
+    step = b200attn.DecodeStep(kc, vc, max_batch=8, Hq=Hq, max_nb=inp["max_nb"], **skw)
+    # the resident tables start with only the blocks in use; the rest of each row is poison the kernel must never follow
+    nb0 = (lens.long() + bs - 1) // bs
+    step.h_block_tables.fill_(inp["num_blocks"] + 12345)
+    for b in range(B):
+        step.h_block_tables[b, :int(nb0[b])] = full_bt[b, :int(nb0[b])]
+    step.upload_block_tables()
+    torch.cuda.synchronize()
+    g = torch.Generator().manual_seed(7)
+    cur = lens.clone()
+    for it in range(steps):
+        cur += 1                                       # the step's new token sits at position cur - 1
+        last = cur.long() - 1
+        slots = full_bt[torch.arange(B), last // bs].long() * bs + last % bs
+        k_new = torch.randn(B, Hkv, 128, generator=g).to(torch.bfloat16)
+        v_new = torch.randn(B, Hkv, 128, generator=g).to(torch.bfloat16)
+        q = torch.randn(B, Hq, 128, generator=g).to(torch.bfloat16)
+        step.h_qkv[:B, :Hq], step.h_qkv[:B, Hq:Hq + Hkv], step.h_qkv[:B, Hq + Hkv:] = q, k_new, v_new
+        step.h_seq_lens[:B] = cur
+        step.h_slots[:B] = slots
+        out = step.run(B, num_splits=(0, 1, 3)[it % 3]).clone()
+        if fp8:
+            R.reshape_and_cache_ref(k_new, v_new, kc_ref, vc_ref, slots, R.KV_FP8_E4M3, ks, vs)
+        else:
+            R.reshape_and_cache_ref(k_new, v_new, kc_ref, vc_ref, slots)
+        ref = R.paged_decode_ref(q, kc_ref, vc_ref, full_bt, cur, return_f32=True, **okw)
+        assert_close(out, ref, what=f"resident tables step {it} fp8={fp8}")
+    nb1 = (cur.long() + bs - 1) // bs
+    dt = step.d_block_tables.cpu()
+    for b in range(B):
+        assert torch.equal(dt[b, :int(nb1[b])], full_bt[b, :int(nb1[b])]), f"row {b}: resident table != block manager's"
+    assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref))
+    assert step.h2d_bytes == step.h_qkv.numel() * 2 + step.h_meta.numel() * 4 and step.h_meta.numel() <= 3 * 8 + 1
+
+
+@pytest.mark.parametrize("fp8", [False, True])
+def test_decode_plan_handle_matches_stateless_call(cuda, fp8):
+    """b2_decode_plan_run == b2_paged_decode, call after call on one workspace (the dynamic schedule's claim counter
+    must be back at zero after every call: a stale count would skip chunks), for every schedule and for batch sizes
+    below the plan's max_B."""
+    inp = R.make_inputs(12, 32, 8, 128, 16, 700, seed=41, ragged=True)
+    kc, vc, kc_ref, vc_ref, sc = build_caches(inp, cuda, fp8=fp8, poison=True)
+    kw = dict(k_scale=sc[2], v_scale=sc[3]) if fp8 else {}
+    okw = dict(kv_dtype=R.KV_FP8_E4M3, k_scale=sc[0], v_scale=sc[1]) if fp8 else {}
+    plan = b200attn.ops.DecodePlan(kc, vc, 16, 32, inp["max_nb"], **kw)
+    q, bt, sl = inp["q"].to(cuda), inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda)
+    for B in (12, 5, 1):
+        ref = R.paged_decode_ref(inp["q"][:B], kc_ref, vc_ref, inp["block_tables"][:B], inp["seq_lens"][:B],
+                                 return_f32=True, **okw)     # (reads only tokens < seq_len: the poison stays out)
+        for splits in (0, 0, 1, 0, 4, 0):
+            out = torch.full((B, 32, 128), float("nan"), dtype=torch.bfloat16, device=cuda)
+            plan.run(q[:B], bt[:B].contiguous(), sl[:B].contiguous(), out, num_splits=splits)
+            assert_close(out, ref, what=f"plan handle B={B} splits={splits} fp8={fp8}")
+            stateless = b200attn.paged_decode(q[:B], kc, vc, bt[:B].contiguous(), sl[:B].contiguous(), num_splits=splits, **kw)
+            assert torch.equal(bits(out), bits(stateless)), "plan handle and stateless call differ bitwise"
+    with pytest.raises(b200attn.B2Error):
+        plan.run(inp["q"].repeat(2, 1, 1).to(cuda), bt.repeat(2, 1), sl.repeat(2),
+                 torch.empty(24, 32, 128, dtype=torch.bfloat16, device=cuda))
+    plan.close()
+
+
+def test_decode_two_box_fallback_map(cuda, monkeypatch):
+    """B2_TWO_BOX=1 builds the bf16 stage image from two TMA boxes per tile (the path taken when a driver refuses the
+    one-box [64][row][half] map): same shared-memory layout, so the same bits."""
+    inp = R.make_inputs(6, 16, 2, 128, 16, 500, seed=43, ragged=True)
+    kc, vc, kc_ref, vc_ref, _ = build_caches(inp, cuda)
+    ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], inp["seq_lens"], return_f32=True)
+    outs = {}
+    for two in ("0", "1"):
+        monkeypatch.setenv("B2_TWO_BOX", two)
+        for splits in (0, 1):
+            outs[two, splits] = run_decode(inp, kc, vc, cuda, num_splits=splits)
+            assert_close(outs[two, splits], ref, what=f"two_box={two} splits={splits}")
+    for splits in (0, 1):
+        assert torch.equal(bits(outs["0", splits]), bits(outs["1", splits]))
+
+
+def test_workspace_for_max_batch_serves_every_smaller_batch(cuda):
+    """one workspace sized for max_num_seqs = 32 at max_model_len 8192 must be accepted by every
+    batch size below it under the dynamic schedule (B = 24 needs more partial slots than B = 32)."""
+    Hq, Hkv, bs, max_nb = 32, 8, 16, 512
+    ws = torch.empty(b200attn.decode_workspace_bytes(32, Hq, Hkv, 128, bs, max_nb, 0), dtype=torch.uint8, device=cuda)
+    kc = torch.zeros(64, Hkv, bs, 128, dtype=torch.bfloat16, device=cuda)
+    vc = torch.zeros_like(kc)
+    for B in range(1, 33):
+        q = torch.zeros(B, Hq, 128, dtype=torch.bfloat16, device=cuda)
+        bt = torch.zeros(B, max_nb, dtype=torch.int32, device=cuda)
+        sl = torch.full((B,), 40, dtype=torch.int32, device=cuda)
+        out = b200attn.paged_decode(q, kc, vc, bt, sl, workspace=ws, num_splits=0)
+        assert float(out.float().abs().max()) == 0.0
+    torch.cuda.synchronize()
 
 
 # ------------------------------------------------------------------------------------------

@@ -34,11 +34,16 @@ SIGNATURES = {
     "b2_version": (i32, []),
     "b2_last_error": (C.c_char_p, []),
     "b2_reshape_and_cache": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i32, vp, vp, vp]),
+    "b2_reshape_and_cache_decode": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i64, i32,
+                                          vp, vp, vp]),
     "b2_paged_decode_workspace_bytes": (sz, [i32, i32, i32, i32, i32, i32, i32]),
     "b2_paged_decode_auto_splits": (i32, [i32, i32, i32, i32, i32, i32, i32]),
     "b2_paged_decode_plan_splits": (i32, [vp, i32, i32, i32, i32, i32, i32]),
     "b2_paged_decode": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
                               f32, i32, vp, vp, vp, sz, i32, vp]),
+    "b2_decode_plan_create": (vp, [vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, f32, i32, vp, vp, vp, sz, vp]),
+    "b2_decode_plan_destroy": (None, [vp]),
+    "b2_decode_plan_run": (i32, [vp, vp, vp, vp, vp, i32, i64, i64, i32, vp]),
     "b2_paged_decode_simt": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64,
                                    f32, i32, vp, vp, vp]),
     "b2_prefill_attention": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64,

@@ -98,6 +98,42 @@ def reshape_and_cache(k_new: torch.Tensor, v_new: torch.Tensor, k_cache: torch.T
         bstride, hstride, kvd, _ptr(k_scale), _ptr(v_scale), _stream(dev)))
 
 
+def reshape_and_cache_decode(k_new: torch.Tensor, v_new: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                             slot_mapping: torch.Tensor, block_tables: torch.Tensor, seq_lens: torch.Tensor,
+                             k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None) -> None:
+    """Decode-step KV write over DEVICE-RESIDENT block tables (b2_reshape_and_cache_decode): token b is the newest
+    token of batch row b, and its slot also names the block of table column (seq_lens[b] - 1) // bs, which is
+    written in the same pass -- so a step uploads seq_lens + slots instead of the [B, max_nb] table."""
+    lib = _lib.load()
+    dev = _need_cuda(k_new=k_new, v_new=v_new, k_cache=k_cache, v_cache=v_cache, slot_mapping=slot_mapping,
+                     block_tables=block_tables, seq_lens=seq_lens, k_scale=k_scale, v_scale=v_scale)
+    nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+    kvd = _kv_dtype_of(k_cache)
+    if k_new.dtype != torch.bfloat16 or v_new.dtype != torch.bfloat16:
+        raise ValueError("k_new / v_new must be bf16")
+    if k_new.dim() != 3 or k_new.shape != v_new.shape or k_new.shape[1:] != (Hkv, d):
+        raise ValueError(f"k_new / v_new must be [B, {Hkv}, {d}]")
+    for t in (k_new, v_new):
+        if t.stride(2) != 1 or t.stride(1) != d:
+            raise ValueError("k_new / v_new: head and dim axes must be contiguous")
+    B = k_new.shape[0]
+    if slot_mapping.dtype != torch.int64 or slot_mapping.shape != (B,) or not slot_mapping.is_contiguous():
+        raise ValueError("slot_mapping must be a contiguous int64 [B]")
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B \
+            or block_tables.stride(1) != 1 or (B > 1 and block_tables.stride(0) != block_tables.shape[1]):
+        raise ValueError("block_tables must be a contiguous int32 [B, max_nb]")
+    if seq_lens.dtype != torch.int32 or seq_lens.shape != (B,) or not seq_lens.is_contiguous():
+        raise ValueError("seq_lens must be a contiguous int32 [B]")
+    if kvd == KV_FP8_E4M3:
+        for s in (k_scale, v_scale):
+            if s is None or s.dtype != torch.float32 or s.numel() != 1:
+                raise ValueError("fp8 KV cache needs 1-element fp32 device tensors k_scale / v_scale")
+    _lib.check(lib.b2_reshape_and_cache_decode(
+        _ptr(k_new), _ptr(v_new), _ptr(k_cache), _ptr(v_cache), _ptr(slot_mapping), _ptr(block_tables), _ptr(seq_lens),
+        B, Hkv, d, bs, block_tables.shape[1], k_new.stride(0) if B else Hkv * d, v_new.stride(0) if B else Hkv * d,
+        bstride, hstride, kvd, _ptr(k_scale), _ptr(v_scale), _stream(dev)))
+
+
 def decode_workspace_bytes(B: int, Hq: int, Hkv: int, d: int, bs: int, max_nb: int, num_splits: int = 0) -> int:
     return int(_lib.load().b2_paged_decode_workspace_bytes(B, Hq, Hkv, d, bs, max_nb, num_splits))
 
@@ -181,6 +217,72 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
         B, Hq, Hkv, d, bs, max_nb, nb, qs, os_, bstride, hstride, float(scale), kvd,
         _ptr(k_scale), _ptr(v_scale), _ptr(workspace), wbytes, num_splits, _stream(dev)))
     return out
+
+
+class DecodePlan:
+    """Per-engine decode handle (b2_decode_plan_*): caches, geometry, scales and workspace are fixed at creation, where
+    the two TMA descriptors are encoded and the workspace header is zeroed; run() is then argument checks + launches
+    (no driver call, no getenv; two launches for the dynamic schedule).  The caller keeps caches and workspace alive."""
+
+    def __init__(self, k_cache: torch.Tensor, v_cache: torch.Tensor, max_batch: int, Hq: int, max_nb: int,
+                 scale: Optional[float] = None, k_scale: Optional[torch.Tensor] = None,
+                 v_scale: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None):
+        self._lib = _lib.load()
+        self._h = None
+        dev = _need_cuda(k_cache=k_cache, v_cache=v_cache, k_scale=k_scale, v_scale=v_scale, workspace=workspace)
+        nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+        kvd = _kv_dtype_of(k_cache)
+        need = max(int(self._lib.b2_paged_decode_workspace_bytes(max_batch, Hq, Hkv, d, bs, max_nb, 0)), 256)
+        if workspace is None:
+            workspace = torch.zeros(need, dtype=torch.uint8, device=dev)
+        elif workspace.numel() * workspace.element_size() < need:
+            raise ValueError(f"workspace holds {workspace.numel() * workspace.element_size()} bytes, {need} required")
+        self.dev, self.Hq, self.Hkv, self.d, self.bs, self.max_nb, self.max_batch = dev, Hq, Hkv, d, bs, max_nb, max_batch
+        # the handle stores raw pointers: keep every tensor behind them alive
+        self._keep = (k_cache, v_cache, k_scale, v_scale, workspace)
+        self.workspace = workspace
+        if scale is None:
+            scale = 1.0 / math.sqrt(d)
+        h = self._lib.b2_decode_plan_create(
+            _ptr(k_cache), _ptr(v_cache), max_batch, Hq, Hkv, d, bs, max_nb, nb, bstride, hstride, float(scale), kvd,
+            _ptr(k_scale), _ptr(v_scale), _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(dev))
+        if not h:
+            raise _lib.B2Error(_lib.B2_EINVAL, self._lib.b2_last_error().decode("utf-8", "replace"))
+        self._h = h
+        self._run = self._lib.b2_decode_plan_run
+
+    def run(self, q: torch.Tensor, block_tables: torch.Tensor, seq_lens: torch.Tensor, out: torch.Tensor,
+            num_splits: int = 0) -> torch.Tensor:
+        """q / out: bf16 [B, Hq, d] (row stride allowed; pinned host memory allowed); block_tables int32 [B, max_nb]
+        and seq_lens int32 [B] on the device.  Shapes are the creator's; only the cheap checks are repeated here."""
+        B = q.shape[0]
+        if q.dtype != torch.bfloat16 or out.dtype != torch.bfloat16 or q.shape[1:] != (self.Hq, self.d) \
+                or out.shape != q.shape or q.stride(1) != self.d or out.stride(1) != self.d:
+            raise ValueError(f"q / out must be bf16 [B, {self.Hq}, {self.d}] with contiguous head/dim axes")
+        if block_tables.dtype != torch.int32 or block_tables.shape != (B, self.max_nb) or not block_tables.is_cuda \
+                or block_tables.stride(1) != 1 or (B > 1 and block_tables.stride(0) != self.max_nb):
+            raise ValueError(f"block_tables must be a device int32 [B, {self.max_nb}]")
+        if seq_lens.dtype != torch.int32 or seq_lens.shape != (B,) or not seq_lens.is_cuda:
+            raise ValueError("seq_lens must be a device int32 [B]")
+        for name, t in (("q", q), ("out", out)):
+            if not t.is_cuda and not t.is_pinned():
+                raise ValueError(f"{name} must be a CUDA tensor or a pinned host tensor (b200attn has no CPU path)")
+        qs = q.stride(0) if B > 1 else self.Hq * self.d
+        os_ = out.stride(0) if B > 1 else self.Hq * self.d
+        _lib.check(self._run(self._h, out.data_ptr(), q.data_ptr(), block_tables.data_ptr(), seq_lens.data_ptr(), B,
+                             qs, os_, num_splits, _stream(self.dev)))
+        return out
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.b2_decode_plan_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 # ------------------------------------------------------------------------------------------------

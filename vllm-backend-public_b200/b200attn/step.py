@@ -1,15 +1,23 @@
 """One decode step of one layer, driven from HOST buffers: the call an engine loop makes.
 
     step = DecodeStep(k_cache, v_cache, max_batch=B, Hq=32, max_nb=256)
-    step.h_qkv[...] = ...; step.h_block_tables[...] = ...; step.h_seq_lens[...] = ...; step.h_slots[...] = ...
+    step.h_block_tables[...] = ...; step.upload_block_tables()      # when sequences are placed into batch rows
+    step.h_qkv[...] = ...; step.h_seq_lens[...] = ...; step.h_slots[...] = ...      # every step
     out = step.run(B)            # pinned bf16 [B, Hq, d], valid when run() returns
 
+The block tables are RESIDENT on the device.  A decode step appends one token per sequence, so at most one table
+entry per row changes, and its value is already in the step's slot mapping: b2_reshape_and_cache_decode writes
+block_tables[b][(seq_len - 1) // bs] = slot // bs in the same pass as the KV write.  A row is uploaded in full only
+when a new sequence takes it (upload_block_tables).  Per-step host->device traffic is therefore the step's q|k|v rows
+plus seq_lens and slots -- O(B) words, not the [B, max_nb] table.
+
 What run() enqueues (captured once per (B, schedule) in a CUDA graph, then replayed):
-    1 H2D copy  fused q|k|v rows of the step's tokens      pinned [B, Hq + 2 Hkv, d] bf16
-    1 H2D copy  block_tables | seq_lens | slot_mapping     pinned int32 words
-    b2_reshape_and_cache   (k, v are strided views of the fused buffer: no split copy)
-    b2_paged_decode        (q is a strided view; `out` is the PINNED host tensor: the kernels store the result
-                            rows straight into host memory over PCIe, so there is no separate D2H copy)
+    1 H2D copy  seq_lens | slot_mapping                    pinned int32 words, 12 B per sequence
+    (dynamic schedule only: 1 H2D copy of the fused q|k|v rows; the grid schedules read them in place, below)
+    b2_reshape_and_cache_decode   k, v are strided views of the PINNED fused q|k|v buffer: the kernel reads the rows
+                                  over PCIe itself (the H2D leg, no staging copy)
+    b2_decode_plan_run            q likewise; `out` is the PINNED host tensor: result rows leave as 16-byte vector
+                                  stores straight into host memory (the D2H leg, no separate copy)
 and then synchronises the stream.  The schedule (single-pass grid or dynamic persistent) is chosen on the host
 from h_seq_lens by b2_paged_decode_plan_splits, as an engine's scheduler would.
 
@@ -38,32 +46,41 @@ class DecodeStep:
         self.use_graph = use_graph
         # True: no H2D copy of the q|k|v rows; reshape_and_cache and paged_decode read them from the pinned buffer
         self.zero_copy_inputs = zero_copy_inputs
+        self.kv_dtype = ops.KV_FP8_E4M3 if k_cache.dtype == torch.uint8 else ops.KV_BF16
         B, H = max_batch, Hq + 2 * self.Hkv
         self.h_qkv = torch.zeros(B, H, self.d, dtype=torch.bfloat16).pin_memory()
         self.d_qkv = torch.zeros(B, H, self.d, dtype=torch.bfloat16, device=self.dev)
-        # int32 words: block_tables [B*max_nb] | seq_lens [B] | pad to even | slots as int64 [B]
-        self._off_sl = B * max_nb
-        self._off_slot = (self._off_sl + B + 1) // 2 * 2
+        # per-step words: seq_lens [B] int32 | pad to even | slots as int64 [B]
+        self._off_slot = (B + 1) // 2 * 2
         n_words = self._off_slot + 2 * B
         self.h_meta = torch.zeros(n_words, dtype=torch.int32).pin_memory()
         self.d_meta = torch.zeros(n_words, dtype=torch.int32, device=self.dev)
-        self.h_block_tables = self.h_meta[: self._off_sl].view(B, max_nb)
-        self.h_seq_lens = self.h_meta[self._off_sl: self._off_sl + B]
+        self.h_seq_lens = self.h_meta[:B]
         self.h_slots = self.h_meta[self._off_slot: self._off_slot + 2 * B].view(torch.int64)
+        # resident tables: host staging (filled by the caller when sequences are placed) + the device copy
+        self.h_block_tables = torch.zeros(B, max_nb, dtype=torch.int32).pin_memory()
+        self.d_block_tables = torch.zeros(B, max_nb, dtype=torch.int32, device=self.dev)
         self.h_out = torch.zeros(B, Hq, self.d, dtype=torch.bfloat16).pin_memory()
-        ws = max(ops.decode_workspace_bytes(B, Hq, self.Hkv, self.d, self.bs, max_nb, 0), 16)
-        self.workspace = torch.zeros(ws, dtype=torch.uint8, device=self.dev)
+        self.plan_handle = ops.DecodePlan(k_cache, v_cache, B, Hq, max_nb, k_scale=k_scale, v_scale=v_scale)
+        self.workspace = self.plan_handle.workspace
         self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
         self._stream = torch.cuda.Stream(self.dev)
 
     # ------------------------------------------------------------------------------------------
     @property
     def h2d_bytes(self) -> int:
-        return self.h_qkv.numel() * 2 + self.h_meta.numel() * 4   # zero-copy moves the same bytes, inside the kernels
+        """Per step: q|k|v rows + seq_lens + slots (zero-copy moves the same bytes, inside the kernels)."""
+        return self.h_qkv.numel() * 2 + self.h_meta.numel() * 4
 
     @property
     def d2h_bytes(self) -> int:
         return self.h_out.numel() * 2
+
+    def upload_block_tables(self, rows: Optional[slice] = None) -> None:
+        """Copy h_block_tables (all rows, or `rows`) to the resident device tables.  Needed when a sequence is placed
+        into a batch row; decode steps keep the tables current by themselves (see the module docstring)."""
+        rows = slice(0, self.max_batch) if rows is None else rows
+        self.d_block_tables[rows].copy_(self.h_block_tables[rows], non_blocking=True)
 
     def _views(self, B: int, zero_copy: bool):
         Hq, Hkv = self.Hq, self.Hkv
@@ -71,10 +88,9 @@ class DecodeStep:
         q = src[:B, :Hq]
         k = src[:B, Hq:Hq + Hkv]
         v = src[:B, Hq + Hkv:]
-        bt = self.d_meta[: self._off_sl].view(self.max_batch, self.max_nb)[:B]
-        sl = self.d_meta[self._off_sl: self._off_sl + B]
+        sl = self.d_meta[:B]
         slots = self.d_meta[self._off_slot: self._off_slot + 2 * self.max_batch].view(torch.int64)[:B]
-        return q, k, v, bt, sl, slots
+        return q, k, v, self.d_block_tables[:B], sl, slots
 
     def _enqueue(self, B: int, num_splits: int) -> None:
         # the dynamic schedule fetches a run's q rows with every run it starts: a PCIe round trip each would sit on
@@ -84,13 +100,11 @@ class DecodeStep:
             self.d_qkv.copy_(self.h_qkv, non_blocking=True)
         self.d_meta.copy_(self.h_meta, non_blocking=True)
         q, k, v, bt, sl, slots = self._views(B, zero_copy)
-        ops.reshape_and_cache(k, v, self.k_cache, self.v_cache, slots, self.k_scale, self.v_scale)
-        ops.paged_decode(q, self.k_cache, self.v_cache, bt, sl, k_scale=self.k_scale, v_scale=self.v_scale,
-                         out=self.h_out[:B], workspace=self.workspace, num_splits=num_splits)
+        ops.reshape_and_cache_decode(k, v, self.k_cache, self.v_cache, slots, bt, sl, self.k_scale, self.v_scale)
+        self.plan_handle.run(q, bt, sl, self.h_out[:B], num_splits)
 
     def plan(self, B: int) -> int:
-        return ops.plan_num_splits(self.h_seq_lens[:B], self.Hq, self.Hkv, self.d, self.bs,
-                                   ops.KV_FP8_E4M3 if self.k_cache.dtype == torch.uint8 else ops.KV_BF16)
+        return ops.plan_num_splits(self.h_seq_lens[:B], self.Hq, self.Hkv, self.d, self.bs, self.kv_dtype)
 
     def run(self, B: Optional[int] = None, num_splits: Optional[int] = None) -> torch.Tensor:
         """Run the step for the first B rows of the host buffers; returns the pinned output rows (valid on return)."""

@@ -28,6 +28,7 @@
 
 #include <stdlib.h>
 #include <algorithm>
+#include <new>
 #include <vector>
 
 namespace {
@@ -64,6 +65,7 @@ struct DecodeParams {
     const float* v_scale;
     int B, Hq, Hkv, G, HG, max_nb, num_splits, split_tokens;
     int chunk_tokens, static_pct;   // dynamic schedule: claim granularity, share of chunks dealt statically
+    int two_box;                    // bf16: the cache map holds one 128-byte half per box (driver refused the one-box map)
     uint32_t* counter;              // dynamic schedule: claim counter (workspace header)
     int64_t q_stride, out_stride;
     float scale_log2;  // softmax scale * log2(e)
@@ -71,6 +73,7 @@ struct DecodeParams {
 
 template <int BS, bool FP8, int NT, int NSTAGE>
 struct Cfg {
+    static constexpr int BSZ = BS;
     static constexpr int ESZ = FP8 ? 1 : 2;
     static constexpr int ROWB = D * ESZ;           // bytes per token row
     static constexpr int TILE_BYTES = TOK * ROWB;  // one K (or V) stage tile
@@ -135,25 +138,34 @@ __device__ __forceinline__ void mma_kv(float (&c)[4], uint32_t a0, uint32_t a1, 
 }
 __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(NCW * 32) : "memory"); }
 
-// One KV block of one kv head -> stage slot j.  The (block, head) tile is bs x d contiguous in HBM and is fetched
-// by ONE box per tensor: bf16 rows are 256 B = two 128-byte swizzle lines, so the tile is viewed as
-// [row][half][64 elements] (5-D map) and lands as 2*bs consecutive lines; fp8 rows are one line (4-D map).
+// One KV block of one kv head -> stage slot j.  The (block, head) tile is bs x d contiguous in HBM.  fp8 rows are one
+// 128-byte swizzle line (4-D map, one box).  bf16 rows are 256 B = two lines: the tile is viewed as
+// [half][row][64 elements] (5-D map whose row stride is larger than its half stride), so ONE box lands as bs lines of
+// the low halves followed by bs lines of the high halves -- the 8 rows of an ldmatrix then sit on 8 consecutive lines
+// and the 128-byte swizzle makes them conflict-free (r1 landed [row][half]: lines 2r + h, a 2-way conflict on every
+// K and V fragment load).  two_box: same shared-memory image from two boxes of one half each (fallback map).
 template <class C, bool FP8>
 __device__ __forceinline__ void issue_block(const CUtensorMap* tmK, const CUtensorMap* tmV, uint32_t kdst, uint32_t vdst,
-                                            int j, uint32_t bar, int kvh, int blk, uint64_t pol) {
+                                            int j, uint32_t bar, int kvh, int blk, uint64_t pol, int two_box) {
     const uint32_t off = j * C::BOX_BYTES;
     if (FP8) {
         b2::tma_load_4d(kdst + off, tmK, bar, 0, 0, kvh, blk, pol);
         b2::tma_load_4d(vdst + off, tmV, bar, 0, 0, kvh, blk, pol);
-    } else {
+    } else if (!two_box) {
         b2::tma_load_5d(kdst + off, tmK, bar, 0, 0, 0, kvh, blk, pol);
         b2::tma_load_5d(vdst + off, tmV, bar, 0, 0, 0, kvh, blk, pol);
+    } else {
+        b2::tma_load_5d(kdst + off, tmK, bar, 0, 0, 0, kvh, blk, pol);
+        b2::tma_load_5d(kdst + off + C::BOX_BYTES / 2, tmK, bar, 0, 1, 0, kvh, blk, pol);
+        b2::tma_load_5d(vdst + off, tmV, bar, 0, 0, 0, kvh, blk, pol);
+        b2::tma_load_5d(vdst + off + C::BOX_BYTES / 2, tmV, bar, 0, 1, 0, kvh, blk, pol);
     }
 }
 // shared-memory address of 16-byte chunk `chunk` (0..15 bf16, 0..7 fp8) of token row `row` inside a K or V stage tile
-template <bool FP8>
+template <bool FP8, int BS>
 __device__ __forceinline__ uint32_t tile_addr(uint32_t base, int row, int chunk) {
-    const int line = FP8 ? row : 2 * row + (chunk >> 3);           // 128-byte swizzle line
+    // 128-byte swizzle line: fp8 = the row; bf16 = [block][half][row in block]
+    const int line = FP8 ? row : (row / BS) * (2 * BS) + (chunk >> 3) * BS + (row % BS);
     return base + line * 128 + (((chunk & 7) ^ (line & 7)) << 4);
 }
 
@@ -164,7 +176,7 @@ template <class C, int NSTAGE>
 __device__ __forceinline__ void produce_segment(const CUtensorMap* tmK, const CUtensorMap* tmV,
                                                 const int32_t* __restrict__ bt, int n_blk, int kvh,
                                                 uint32_t ring, uint32_t bar_full, uint32_t bar_empty,
-                                                uint32_t& it, int lane, uint64_t pol) {
+                                                uint32_t& it, int lane, uint64_t pol, int two_box) {
     const int n_stage = (n_blk + C::BLK_PER_STAGE - 1) / C::BLK_PER_STAGE;
     int cur = (lane < n_blk) ? bt[lane] : 0;            // 32 table entries per batch
     int nxt = (32 + lane < n_blk) ? bt[32 + lane] : 0;  // next batch, prefetched
@@ -183,7 +195,7 @@ __device__ __forceinline__ void produce_segment(const CUtensorMap* tmK, const CU
             const int src = gi & 31;
             const int blk = __shfl_sync(0xffffffffu, cur, src);
             if (j < nb_stage && lane == 0)
-                issue_block<C, C::ESZ == 1>(tmK, tmV, kdst, vdst, j, bar_full + s * 8, kvh, blk, pol);
+                issue_block<C, C::ESZ == 1>(tmK, tmV, kdst, vdst, j, bar_full + s * 8, kvh, blk, pol, two_box);
             if (src == 31) {  // warp-uniform: this batch of 32 entries is used up
                 cur = nxt;
                 nxt = (gi + 33 + lane < n_blk) ? bt[gi + 33 + lane] : 0;
@@ -339,7 +351,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const QFrags<NT>&
 #pragma unroll
         for (int kc = 0; kc < 8; ++kc) {
             const int chunk = 2 * kc + (mi >> 1);        // 16-byte chunk of the 256-byte row
-            const uint32_t addr = tile_addr<false>(kbase, row, chunk);
+            const uint32_t addr = tile_addr<false, C::BSZ>(kbase, row, chunk);
             uint32_t a0, a1, a2, a3;
             b2::ldmatrix_x4(addr, a0, a1, a2, a3);
 #pragma unroll
@@ -352,7 +364,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const QFrags<NT>&
 #pragma unroll
         for (int kc2 = 0; kc2 < 4; ++kc2) {
             const int chunk = 2 * kc2 + (mi >> 1);
-            const uint32_t addr = tile_addr<true>(kbase, row, chunk);
+            const uint32_t addr = tile_addr<true, C::BSZ>(kbase, row, chunk);
             uint32_t r0, r1, r2, r3;
             b2::ldmatrix_x4(addr, r0, r1, r2, r3);
             const uint32_t a0 = e4m3x2_to_f16x2(r0), a1 = e4m3x2_to_f16x2(r1);
@@ -435,7 +447,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const QFrags<NT>&
 #pragma unroll
         for (int dt = 0; dt < 8; ++dt) {
             const int chunk = 2 * dt + (mi & 1);
-            const uint32_t addr = tile_addr<false>(vbase, row, chunk);
+            const uint32_t addr = tile_addr<false, C::BSZ>(vbase, row, chunk);
             uint32_t a0, a1, a2, a3;
             b2::ldmatrix_x4_trans(addr, a0, a1, a2, a3);
             a0 &= mk_lo; a1 &= mk_lo; a2 &= mk_hi; a3 &= mk_hi;
@@ -454,7 +466,7 @@ __device__ __forceinline__ void consume_slab(WarpAcc<NT>& acc, const QFrags<NT>&
 #pragma unroll
         for (int dt2 = 0; dt2 < 4; ++dt2) {
             const int chunk = 2 * dt2 + (mi >> 1);
-            const uint32_t addr = tile_addr<true>(vbase, row, chunk);
+            const uint32_t addr = tile_addr<true, C::BSZ>(vbase, row, chunk);
             uint32_t r0, r1, r2, r3;
             b2::ldmatrix_x4_trans(addr, r0, r1, r2, r3);
             r0 = __byte_perm(r0, 0, 0x3120); r1 = __byte_perm(r1, 0, 0x3120);
@@ -514,12 +526,21 @@ __device__ __forceinline__ void merge_warps(WarpAcc<NT>& acc, float* scratch, in
 
 // Warp 0 writes the merged result: final bf16 rows, or a normalised fp32 partial + log2-sum-exp.
 // MMA row r of d-tile dt <-> d = 16dt + r (bf16) or rows g / g+8 <-> d = 16dt + 2g / 2g+1 (fp8).
+// The fragment layout scatters one head's row over the warp, so the rows are first laid out in shared memory
+// (`stage`: the whole merge scratch, free once merge_warps has returned; padded row strides keep the scatter
+// conflict-free) and leave as 16-byte vectors, 256 contiguous bytes per head: full sectors in HBM and, when `out`
+// is pinned host memory (the engine step's D2H leg), full-size PCIe writes instead of 2-byte ones.
+// The caller keeps the other consumer warps off the scratch until warp 0 is done (consumer_bar).
+constexpr int OUT_STAGE_STRIDE = D * 2 + 16;    // bytes per staged bf16 row
+constexpr int PART_STAGE_STRIDE = D * 4 + 16;   // bytes per staged fp32 row
 template <bool FP8, int NT>
 __device__ __forceinline__ void write_result(const WarpAcc<NT>& acc, int nheads, float vs, float sl2,
                                              __nv_bfloat16* out_rows /* [head][D] or null */,
                                              float* part_o /* [head][D] */, float* part_lse /* [head] */,
-                                             int lane) {
+                                             float* stage, int lane) {
+    static_assert(8 * NT * PART_STAGE_STRIDE <= 2 * (32 * NT * 32 + 4 * NT * 4) * 4, "staged rows must fit the merge scratch");
     const int g = lane >> 2, t4 = lane & 3;
+    uint8_t* sb = reinterpret_cast<uint8_t*>(stage);
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
@@ -534,15 +555,31 @@ __device__ __forceinline__ void write_result(const WarpAcc<NT>& acc, int nheads,
                 const int d_hi = FP8 ? d_lo + 1 : d_lo + 8;
                 const float v_lo = acc.o[nt][dt][j] * inv, v_hi = acc.o[nt][dt][j + 2] * inv;
                 if (out_rows) {
-                    out_rows[h * D + d_lo] = __float2bfloat16(v_lo);
-                    out_rows[h * D + d_hi] = __float2bfloat16(v_hi);
+                    if (FP8) {
+                        *reinterpret_cast<uint32_t*>(sb + h * OUT_STAGE_STRIDE + d_lo * 2) = b2::pack_bf16x2(v_lo, v_hi);
+                    } else {
+                        *reinterpret_cast<__nv_bfloat16*>(sb + h * OUT_STAGE_STRIDE + d_lo * 2) = __float2bfloat16(v_lo);
+                        *reinterpret_cast<__nv_bfloat16*>(sb + h * OUT_STAGE_STRIDE + d_hi * 2) = __float2bfloat16(v_hi);
+                    }
                 } else {
-                    part_o[h * D + d_lo] = v_lo;
-                    part_o[h * D + d_hi] = v_hi;
+                    *reinterpret_cast<float*>(sb + h * PART_STAGE_STRIDE + d_lo * 4) = v_lo;
+                    *reinterpret_cast<float*>(sb + h * PART_STAGE_STRIDE + d_hi * 4) = v_hi;
                 }
             }
             if (!out_rows && g == 0) part_lse[h] = L > 0.f ? fmaf(acc.m[nt][j], sl2, log2f(L)) : -INFINITY;
         }
+    __syncwarp();
+    if (out_rows) {
+        for (int i = lane; i < nheads * (D / 8); i += 32) {        // 16 vectors of 8 bf16 per head row
+            const int h = i >> 4, c = i & 15;
+            *reinterpret_cast<uint4*>(out_rows + h * D + c * 8) = *reinterpret_cast<const uint4*>(sb + h * OUT_STAGE_STRIDE + c * 16);
+        }
+    } else {
+        for (int i = lane; i < nheads * (D / 4); i += 32) {        // 32 vectors of 4 floats per head row
+            const int h = i >> 5, c = i & 31;
+            *reinterpret_cast<float4*>(part_o + h * D + c * 4) = *reinterpret_cast<const float4*>(sb + h * PART_STAGE_STRIDE + c * 16);
+        }
+    }
 }
 
 __device__ __forceinline__ void init_pipeline(uint32_t bar_full, uint32_t bar_empty, int nstage, int tid) {
@@ -603,7 +640,7 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         }
         const uint64_t pol = b2::policy_evict_first();
         produce_segment<C, NSTAGE>(&tmK, &tmV, p.block_tables + (int64_t)b * p.max_nb + t_begin / BS,
-                                   (n_tok + BS - 1) / BS, kvh, ring, bar_full, bar_empty, it, lane, pol);
+                                   (n_tok + BS - 1) / BS, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
         B2_TRACE_AT(cta_lin, 4);
     } else {
         if (warp == 0) B2_TRACE_AT(cta_lin, 1);
@@ -622,7 +659,7 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         if (warp == 0) {
             if (p.num_splits == 1) {
                 write_result<FP8, NT>(acc, nheads, vs, sl2, p.out + b * p.out_stride + (int64_t)head0 * D, nullptr,
-                                      nullptr, lane);
+                                      nullptr, scratch, lane);
             } else {
                 // partial of q head (head0 + h) lives at ((b*Hq + head0 + h)*num_splits + split)
                 const int g = lane >> 2, t4 = lane & 3;
@@ -969,7 +1006,7 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
                 for (int j = 0; j < C::BLK_PER_STAGE; ++j) {
                     const int blk = __shfl_sync(0xffffffffu, tbl, (st * C::BLK_PER_STAGE + j) & 31);
                     if (j < nb_stage && lane == 0)
-                        issue_block<C, FP8>(&tmK, &tmV, kdst, vdst, j, bar_full + s * 8, kvh, blk, pol);
+                        issue_block<C, FP8>(&tmK, &tmV, kdst, vdst, j, bar_full + s * 8, kvh, blk, pol, p.two_box);
                 }
             }
             run_first = !cont;
@@ -1039,13 +1076,14 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
                 if (warp == 0) {
                     if (m.w & META_DIRECT) {
                         write_result<FP8, NT>(acc, nheads, vs, sl2, p.out + cb * p.out_stride + (int64_t)head0 * D,
-                                              nullptr, nullptr, lane);
+                                              nullptr, nullptr, scratch, lane);
                     } else {
                         const int64_t slot = (int64_t)((uint32_t)m.w >> 4);
                         write_result<FP8, NT>(acc, nheads, vs, sl2, nullptr, p.ws_o + slot * (C::HEADS * D),
-                                              p.ws_lse + slot * C::HEADS, lane);
+                                              p.ws_lse + slot * C::HEADS, scratch, lane);
                     }
                 }
+                consumer_bar();   // warp 0 has read its staged rows: the scratch is free for the next run's merge
             }
         }
     }
@@ -1064,7 +1102,7 @@ template <int HEADS>
 __global__ void __launch_bounds__(128)
 merge_chunks_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ ws_o,
                     const float* __restrict__ ws_lse, const int32_t* __restrict__ seq_lens, int B, int Hkv, int G,
-                    int HG, int64_t out_stride, int ct, int static_pct, uint32_t NC) {
+                    int HG, int64_t out_stride, int ct, int static_pct, uint32_t NC, uint32_t* counter) {
     __shared__ uint32_t s_red[2][4];
     const int tid = threadIdx.x, b = blockIdx.y, j = blockIdx.x;
     const int IPB = Hkv * HG;
@@ -1088,6 +1126,9 @@ merge_chunks_kernel(__nv_bfloat16* __restrict__ out, const float* __restrict__ w
     total = s_red[1][0] + s_red[1][1] + s_red[1][2] + s_red[1][3];
     // every block waits for the decode grid, so "merge finished" implies "decode finished" for later work
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    // the decode grid is complete: leave the claim counter at zero for the next call on this workspace
+    // (b2_decode_plan_run relies on it and launches no zeroing kernel; b2_paged_decode zeroes it itself)
+    if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) *counter = 0u;
     const uint32_t nck = chunks_of(seq_lens[b], ct);
     if (nck <= 1) return;                                 // a single chunk is always written directly
     const uint32_t S = dyn_static_chunks(total, NC, static_pct);
@@ -1120,6 +1161,7 @@ EncodeTiledFn get_encode_tiled() {
     return fn;
 }
 
+// Legacy view ([row][half] landing order) -- what prefill_attention.cu's mma.sync kernel addresses.
 // fp8: cache viewed as [num_blocks][Hkv][bs][128 B]; bf16: [num_blocks][Hkv][bs][2 halves][64 elements].
 // One box = one whole (block, head) tile, contiguous in HBM.
 int make_cache_tmap(CUtensorMap* tm, const void* cache, int kv_dtype, int64_t num_blocks, int Hkv,
@@ -1153,18 +1195,83 @@ int env_int(const char* name, int dflt) {
     return (s && *s) ? atoi(s) : dflt;
 }
 
+// Diagnostic knobs (environment): read once per b2_decode_plan, per call by the stateless b2_paged_decode.
+struct Knobs {
+    int chunk_tokens;   // B2_CHUNK_TOKENS: claim granularity of the dynamic schedule (0 = automatic)
+    int static_pct;     // B2_STATIC_PCT: share of the chunks dealt statically
+    int fp8_ctas;       // B2_FP8_CTAS: 3 (default) or 2 resident CTAs per SM for the fp8 kernels
+    int two_box;        // B2_TWO_BOX=1: force the two-boxes-per-tile bf16 map (the fallback path)
+};
+Knobs read_knobs() {
+    Knobs k;
+    k.chunk_tokens = env_int("B2_CHUNK_TOKENS", 0);
+    int pct = env_int("B2_STATIC_PCT", 85);
+    k.static_pct = pct < 0 ? 0 : (pct > 100 ? 100 : pct);
+    k.fp8_ctas = env_int("B2_FP8_CTAS", 3) == 3 ? 3 : 2;
+    k.two_box = env_int("B2_TWO_BOX", 0) != 0;
+    return k;
+}
+
+// The decode kernels' view of the cache.  fp8: as above.  bf16: ONE box per (block, head) tile with the dimensions
+// ordered [64 el][row][half] (row stride 256 B, half stride 128 B), so the tile lands as [half][row][64] -- see
+// issue_block.  Should a driver refuse a map whose strides do not grow with the dimension index, the same image is
+// built from two boxes of one half each (two_box = 1).
+struct CacheMaps {
+    CUtensorMap k, v;
+    int two_box;
+};
+int make_decode_maps(CacheMaps* m, const void* k_cache, const void* v_cache, int kv_dtype, int64_t num_blocks, int Hkv,
+                     int bs, int64_t block_stride, int64_t head_stride, bool force_two_box) {
+    m->two_box = 0;
+    if (kv_dtype == B2_KV_FP8_E4M3) {
+        int rc = make_cache_tmap(&m->k, k_cache, kv_dtype, num_blocks, Hkv, bs, block_stride, head_stride);
+        if (rc != B2_OK) return rc;
+        return make_cache_tmap(&m->v, v_cache, kv_dtype, num_blocks, Hkv, bs, block_stride, head_stride);
+    }
+    EncodeTiledFn enc = get_encode_tiled();
+    B2_REQUIRE(enc != nullptr, B2_ECUDA, "cuTensorMapEncodeTiled entry point not available");
+    static int one_box_refused = 0;   // remembered per process: the answer depends on the driver only
+    const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    if (!force_two_box && !one_box_refused) {
+        const cuuint64_t dims[5] = {64, (cuuint64_t)bs, 2, (cuuint64_t)Hkv, (cuuint64_t)num_blocks};
+        const cuuint64_t strides[4] = {(cuuint64_t)D * 2, 128, (cuuint64_t)head_stride * 2, (cuuint64_t)block_stride * 2};
+        const cuuint32_t box[5] = {64, (cuuint32_t)bs, 2, 1, 1};
+        CUresult rk = enc(&m->k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(k_cache), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        CUresult rv = rk != CUDA_SUCCESS ? rk
+                                         : enc(&m->v, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(v_cache), dims,
+                                               strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (rk == CUDA_SUCCESS && rv == CUDA_SUCCESS) return B2_OK;
+        one_box_refused = 1;
+    }
+    m->two_box = 1;
+    const cuuint64_t dims[5] = {64, 2, (cuuint64_t)bs, (cuuint64_t)Hkv, (cuuint64_t)num_blocks};
+    const cuuint64_t strides[4] = {128, (cuuint64_t)D * 2, (cuuint64_t)head_stride * 2, (cuuint64_t)block_stride * 2};
+    const cuuint32_t box[5] = {64, 1, (cuuint32_t)bs, 1, 1};
+    for (int i = 0; i < 2; ++i) {
+        CUresult r = enc(i ? &m->v : &m->k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(i ? v_cache : k_cache), dims,
+                         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        B2_REQUIRE(r == CUDA_SUCCESS, B2_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    }
+    return B2_OK;
+}
+
 // resident CTAs per SM (shared-memory bound): 2, or 3 for the shallow-ring fp8 variants (B2_FP8_CTAS=2 for A/B runs)
 // (G > 8 serves 16 q heads per CTA: its accumulators do not fit the 128-register budget of three CTAs)
-int ctas_per_sm(bool fp8, int G) { return fp8 && G <= 8 && env_int("B2_FP8_CTAS", 3) == 3 ? 3 : 2; }
+int ctas_per_sm(bool fp8, int G, int fp8_ctas) { return fp8 && G <= 8 && fp8_ctas == 3 ? 3 : 2; }
 
-int persistent_grid(int per_sm) {
+int sm_count() {
     static int sms = []() {
         int dev = 0, n = 148;
         if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
         return n;
     }();
-    return per_sm * sms;
+    return sms;
 }
+int persistent_grid(int per_sm) { return per_sm * sm_count(); }
 
 struct Plan {
     int nt;            // n-tiles of 8 q heads per CTA
@@ -1179,10 +1286,12 @@ struct Plan {
 };
 
 // dynamic schedule: workspace header (claim counter)
-size_t ws_header_bytes(int, int) { return 256; }
+constexpr size_t WS_HEADER_BYTES = 256;
+
+int dyn_ct_max(int bs) { return bs * 32 < 512 ? bs * 32 : 512; }   // <= 32 blocks per chunk
 
 // per_sm: CTAs per SM of the kernel that will run (3 also bounds the workspace of every variant from above)
-void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_splits, int per_sm) {
+void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_splits, int per_sm, const Knobs& kn) {
     pl->nt = G <= 8 ? 1 : 2;
     const int hpc = 8 * pl->nt;
     pl->hg = (G + hpc - 1) / hpc;
@@ -1195,23 +1304,20 @@ void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_spli
     pl->nc = 0;
     const int64_t max_ctx = (int64_t)max_nb * bs;
     if (num_splits <= 0) {
-        // diagnostic overrides, read per call (cheap): B2_CHUNK_TOKENS, B2_STATIC_PCT
         const int NC = persistent_grid(per_sm);
         const int ipb = Hkv * pl->hg;
-        const int ct_max = bs * 32 < 512 ? bs * 32 : 512;   // <= 32 blocks per chunk
+        const int ct_max = dyn_ct_max(bs);
         // aim for >= 8 chunks per CTA (run boundaries cost more than a slightly longer tail), within [64, ct_max] tokens
         const int64_t total_tok = (int64_t)B * ipb * max_ctx;
         int ct = TOK;
         while (ct * 2 <= ct_max && total_tok / (ct * 2) >= (int64_t)8 * NC) ct *= 2;
-        const int ect = env_int("B2_CHUNK_TOKENS", 0);
+        const int ect = kn.chunk_tokens;
         if (ect >= TOK && ect <= ct_max && ect % TOK == 0 && ect % bs == 0) ct = ect;
-        int pct = env_int("B2_STATIC_PCT", 85);
-        pct = pct < 0 ? 0 : (pct > 100 ? 100 : pct);
         pl->chunk_tokens = ct;
         pl->nc = NC;
-        pl->static_pct = pct;
+        pl->static_pct = kn.static_pct;
         const int64_t ctot_max = (int64_t)B * ipb * ((max_ctx + ct - 1) / ct);
-        pl->slots = 2 * (int64_t)NC + ctot_max * (100 - pct) / 100 + NC + 2;
+        pl->slots = 2 * (int64_t)NC + ctot_max * (100 - kn.static_pct) / 100 + NC + 2;
         return;
     }
     int64_t st = (max_ctx + num_splits - 1) / num_splits;
@@ -1223,17 +1329,41 @@ void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_spli
 
 size_t plan_workspace(const Plan& pl, int B, int Hq) {
     if (pl.num_splits == 0) {
-        return ws_header_bytes(B, pl.ipb) + (size_t)pl.slots * (8 * pl.nt) * (D + 1) * sizeof(float);
+        return WS_HEADER_BYTES + (size_t)pl.slots * (8 * pl.nt) * (D + 1) * sizeof(float);
     }
     if (pl.num_splits == 1) return 0;
     return (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
 }
 
+// Bytes that serve EVERY batch size 1..B of this geometry.  The dynamic plan's chunk size grows with the batch, so
+// its slot count is not monotone in B (a smaller batch may cut finer chunks and need more partial slots): within one
+// chunk-size regime the need grows with B, so the maximum sits at B or at the last batch size of a smaller regime.
+size_t workspace_bound(int B, int Hq, int Hkv, int bs, int max_nb, int num_splits, const Knobs& kn) {
+    Plan pl;
+    make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits, 3, kn);
+    size_t best = plan_workspace(pl, B, Hq);
+    if (num_splits > 0) return best;                       // grid split: monotone in B
+    const int NC = persistent_grid(3);
+    const int64_t per_seq = (int64_t)pl.ipb * max_nb * bs;  // streamed tokens one sequence adds
+    for (int ct = TOK; ct * 2 <= dyn_ct_max(bs); ct *= 2) {
+        // the plan leaves chunk size ct for 2*ct once B * per_seq >= 16 * NC * ct
+        const int64_t first_bigger = ((int64_t)16 * NC * ct + per_seq - 1) / per_seq;
+        const int64_t b = first_bigger - 1;
+        if (b >= 1 && b < B) {
+            make_plan(&pl, (int)b, Hkv, Hq / Hkv, bs, max_nb, 0, 3, kn);
+            best = std::max(best, plan_workspace(pl, (int)b, Hq));
+        }
+    }
+    return best;
+}
+
 // NSTAGE / NSTAGE_D: ring depth of the grid-split / dynamic kernel.  bf16: 3 x 32 KiB, two CTAs per SM.
 // fp8 (16 KiB stages): 4 / 3 stages with three CTAs per SM (default), or 6 / 5 with two.
+// zero_first: launch the tiny kernel that zeroes the claim counter (stateless API); a b2_decode_plan zeroes it once
+// at creation and every merge kernel leaves it at zero, so its calls are two launches.
 template <int BS, bool FP8, int NT, int NSTAGE, int NSTAGE_D>
 int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, const Plan& pl,
-                  cudaStream_t st) {
+                  bool zero_first, cudaStream_t st) {
     using C = Cfg<BS, FP8, NT, NSTAGE>;
     if (pl.num_splits == 0) {
         using C = Cfg<BS, FP8, NT, NSTAGE_D>;
@@ -1245,8 +1375,10 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         }
         const int grid = persistent_grid(C::CTAS_DYN);
         B2_REQUIRE(grid == pl.nc, B2_EINVAL, "paged_decode: plan made for %d CTAs, kernel runs %d", pl.nc, grid);
-        zero_counter_kernel<<<1, 32, 0, st>>>(p.counter);
-        B2_CUDA_OK(cudaGetLastError());
+        if (zero_first) {
+            zero_counter_kernel<<<1, 32, 0, st>>>(p.counter);
+            B2_CUDA_OK(cudaGetLastError());
+        }
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
@@ -1255,8 +1387,10 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         cfg.blockDim = dim3(NTHREADS);
         cfg.dynamicSmemBytes = C::DYN_SMEM_BYTES;
         cfg.stream = st;
+        // without the zeroing kernel in front the grid is ordered after the stream's earlier work (the KV write of
+        // this step) in the ordinary way: no programmatic overlap with it
         cfg.attrs = at;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = zero_first ? 1 : 0;
         B2_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmK, tmV, p));
         cudaLaunchConfig_t cfg2 = {};
         cfg2.gridDim = dim3(p.Hkv * p.HG, p.B);
@@ -1266,7 +1400,7 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         cfg2.numAttrs = 1;
         B2_CUDA_OK(cudaLaunchKernelEx(&cfg2, merge_chunks_kernel<8 * NT>, p.out, (const float*)p.ws_o,
                                       (const float*)p.ws_lse, p.seq_lens, p.B, p.Hkv, p.G, p.HG, p.out_stride,
-                                      p.chunk_tokens, p.static_pct, (uint32_t)grid));
+                                      p.chunk_tokens, p.static_pct, (uint32_t)grid, p.counter));
         return B2_OK;
     }
     auto kern = paged_decode_split_kernel<BS, FP8, NT, NSTAGE>;
@@ -1288,17 +1422,100 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
 
 template <int BS>
 int dispatch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodeParams& p, const Plan& pl, bool fp8,
-                    cudaStream_t st) {
+                    int fp8_ctas, bool zero_first, cudaStream_t st) {
     if (!fp8)
-        return pl.nt == 1 ? launch_decode<BS, false, 1, 3, 3>(tmK, tmV, p, pl, st)
-                          : launch_decode<BS, false, 2, 3, 3>(tmK, tmV, p, pl, st);
-    if (ctas_per_sm(true, p.G) == 3) return launch_decode<BS, true, 1, 4, 3>(tmK, tmV, p, pl, st);
-    return pl.nt == 1 ? launch_decode<BS, true, 1, 6, 5>(tmK, tmV, p, pl, st)
-                      : launch_decode<BS, true, 2, 6, 5>(tmK, tmV, p, pl, st);
+        return pl.nt == 1 ? launch_decode<BS, false, 1, 3, 3>(tmK, tmV, p, pl, zero_first, st)
+                          : launch_decode<BS, false, 2, 3, 3>(tmK, tmV, p, pl, zero_first, st);
+    if (ctas_per_sm(true, p.G, fp8_ctas) == 3) return launch_decode<BS, true, 1, 4, 3>(tmK, tmV, p, pl, zero_first, st);
+    return pl.nt == 1 ? launch_decode<BS, true, 1, 6, 5>(tmK, tmV, p, pl, zero_first, st)
+                      : launch_decode<BS, true, 2, 6, 5>(tmK, tmV, p, pl, zero_first, st);
 }
 
 bool shape_ok(int B, int Hq, int Hkv, int d, int bs, int max_nb) {
     return B > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && bs > 0 && max_nb > 0 && d == D;
+}
+
+// everything of a decode call that does not change from step to step
+struct DecodeGeom {
+    int Hq, Hkv, bs, max_nb, kv_dtype;
+    float scale;
+    const float* k_scale;
+    const float* v_scale;
+    void* workspace;
+    size_t workspace_bytes;
+};
+
+int check_geom(int Hq, int Hkv, int d, int bs, int max_nb, int64_t num_blocks, const void* k_cache, const void* v_cache,
+               int64_t cache_block_stride, int64_t cache_head_stride, float scale, int kv_dtype, const float* k_scale,
+               const float* v_scale) {
+    B2_REQUIRE(Hq > 0 && Hkv > 0 && bs > 0 && max_nb > 0 && num_blocks > 0, B2_EINVAL,
+               "paged_decode: bad sizes Hq=%d Hkv=%d bs=%d max_nb=%d num_blocks=%lld", Hq, Hkv, bs, max_nb,
+               (long long)num_blocks);
+    B2_REQUIRE(k_cache && v_cache, B2_EINVAL, "paged_decode: null pointer");
+    B2_REQUIRE(d == D, B2_EUNSUPPORTED, "paged_decode: head_dim %d unsupported (kernels are built for 128)", d);
+    B2_REQUIRE(Hq % Hkv == 0, B2_EINVAL, "paged_decode: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
+    B2_REQUIRE(bs == 8 || bs == 16 || bs == 32, B2_EUNSUPPORTED, "paged_decode: block_size %d unsupported (8/16/32)", bs);
+    B2_REQUIRE(kv_dtype == B2_KV_BF16 || kv_dtype == B2_KV_FP8_E4M3, B2_EUNSUPPORTED, "paged_decode: kv_dtype %d", kv_dtype);
+    B2_REQUIRE(b2_aligned16(k_cache) && b2_aligned16(v_cache), B2_EINVAL, "paged_decode: pointers must be 16-byte aligned");
+    B2_REQUIRE(cache_block_stride % 16 == 0 && cache_head_stride % 16 == 0 && cache_head_stride >= (int64_t)bs * D,
+               B2_EINVAL, "paged_decode: cache strides must keep 16-byte alignment");
+    B2_REQUIRE(scale > 0.f, B2_EINVAL, "paged_decode: scale must be positive");
+    if (kv_dtype == B2_KV_FP8_E4M3) B2_REQUIRE(k_scale && v_scale, B2_EINVAL, "paged_decode: fp8 needs k_scale/v_scale");
+    B2_REQUIRE((int64_t)Hkv * ((Hq / Hkv + 15) / 16) <= 65535, B2_EUNSUPPORTED, "paged_decode: grid too large");
+    return B2_OK;
+}
+
+// one call: validate the per-step arguments, plan, launch
+int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool zero_first, void* out, const void* q,
+               const int32_t* block_tables, const int32_t* seq_lens, int B, int64_t q_stride, int64_t out_stride,
+               int num_splits, cudaStream_t st) {
+    B2_REQUIRE(out && q && block_tables && seq_lens, B2_EINVAL, "paged_decode: null pointer");
+    B2_REQUIRE(b2_aligned16(out) && b2_aligned16(q), B2_EINVAL, "paged_decode: pointers must be 16-byte aligned");
+    B2_REQUIRE(q_stride % 8 == 0 && out_stride % 8 == 0 && q_stride >= (int64_t)g.Hq * D && out_stride >= (int64_t)g.Hq * D,
+               B2_EINVAL, "paged_decode: q/out strides");
+    B2_REQUIRE(num_splits >= 0, B2_EINVAL, "paged_decode: num_splits must be >= 0");
+    B2_REQUIRE(B <= 65535, B2_EUNSUPPORTED, "paged_decode: grid too large");
+    B2_REQUIRE((int64_t)B * g.max_nb * g.Hkv * ((g.Hq / g.Hkv + 7) / 8) < (1LL << 31), B2_EUNSUPPORTED,
+               "paged_decode: more than 2^31 block units");
+    const int G = g.Hq / g.Hkv;
+    const bool fp8 = g.kv_dtype == B2_KV_FP8_E4M3;
+    Plan pl;
+    make_plan(&pl, B, g.Hkv, G, g.bs, g.max_nb, num_splits, ctas_per_sm(fp8, G, kn.fp8_ctas), kn);
+
+    DecodeParams p;
+    p.out = static_cast<__nv_bfloat16*>(out);
+    p.q = static_cast<const __nv_bfloat16*>(q);
+    p.block_tables = block_tables;
+    p.seq_lens = seq_lens;
+    p.k_scale = g.k_scale;
+    p.v_scale = g.v_scale;
+    p.B = B; p.Hq = g.Hq; p.Hkv = g.Hkv; p.G = G; p.HG = pl.hg; p.max_nb = g.max_nb;
+    p.num_splits = pl.num_splits; p.split_tokens = pl.split_tokens;
+    p.q_stride = q_stride; p.out_stride = out_stride;
+    p.scale_log2 = g.scale * LOG2E;
+    p.ws_o = nullptr; p.ws_lse = nullptr;
+    p.counter = nullptr;
+    p.chunk_tokens = pl.chunk_tokens;
+    p.static_pct = pl.static_pct;
+    p.two_box = maps.two_box;
+    const size_t need = plan_workspace(pl, B, g.Hq);
+    if (need) {
+        B2_REQUIRE(g.workspace && g.workspace_bytes >= need && b2_aligned16(g.workspace), B2_ENOMEM,
+                   "paged_decode: workspace %zu bytes < required %zu", g.workspace_bytes, need);
+        size_t body = need;
+        char* base = static_cast<char*>(g.workspace);
+        if (pl.num_splits == 0) {
+            B2_REQUIRE(pl.slots < (1LL << 27), B2_EUNSUPPORTED, "paged_decode: %lld partial slots", (long long)pl.slots);
+            p.counter = reinterpret_cast<uint32_t*>(base);
+            base += WS_HEADER_BYTES;
+            body -= WS_HEADER_BYTES;
+        }
+        p.ws_o = reinterpret_cast<float*>(base);
+        p.ws_lse = p.ws_o + body / sizeof(float) / (D + 1) * D;
+    }
+    if (g.bs == 8) return dispatch_decode<8>(maps.k, maps.v, p, pl, fp8, kn.fp8_ctas, zero_first, st);
+    if (g.bs == 16) return dispatch_decode<16>(maps.k, maps.v, p, pl, fp8, kn.fp8_ctas, zero_first, st);
+    return dispatch_decode<32>(maps.k, maps.v, p, pl, fp8, kn.fp8_ctas, zero_first, st);
 }
 
 }  // namespace
@@ -1342,27 +1559,38 @@ extern "C" int b2_paged_decode_plan_splits(const int32_t* seq_lens_host, int B, 
     const int G = Hq / Hkv;
     const int hpc = G <= 8 ? 8 : 16;
     const int ipb = Hkv * ((G + hpc - 1) / hpc);
-    const int NC = persistent_grid(ctas_per_sm(kv_dtype == B2_KV_FP8_E4M3, G));
-    const int64_t items = (int64_t)B * ipb;
-    // (fewer items than slots is not special: 256 equal items on 296 slots stream at 6.7 TB/s in one wave, the
-    // dynamic schedule at 6.1 -- BASELINE configs[3] at tp = 8; the model below rejects the really short grids)
-    (void)items;
+    static const int fp8_ctas = read_knobs().fp8_ctas;   // the planner runs every step: no getenv on that path
+    const int NC = persistent_grid(ctas_per_sm(kv_dtype == B2_KV_FP8_E4M3, G, fp8_ctas));
     constexpr int64_t OVERHEAD_TOK = 128;   // CTA launch + pipeline fill, in streamed-token equivalents
     // The ipb items of a sequence are equal and adjacent in grid order: they are placed together on a group of ipb
     // slots (NC / ipb groups), which keeps this at one heap operation per sequence -- it runs on the host every step.
+    // (fewer items than slots is not special: 256 equal items on 296 slots stream at 6.7 TB/s in one wave, the
+    // dynamic schedule at 6.1 -- BASELINE configs[3] at tp = 8; the model below rejects the really short grids)
     const int n_groups = NC / ipb > 0 ? NC / ipb : 1;
-    std::vector<int64_t> slot((size_t)n_groups, 0);   // min-heap of group finish times
+    static thread_local std::vector<int64_t> slot;     // min-heap of group finish times (reused: no allocation per step)
+    slot.assign((size_t)n_groups, 0);
     auto cmp = [](int64_t a, int64_t b) { return a > b; };
     int64_t total = 0, streamed = 0, makespan = 0;
-    for (int b = 0; b < B; ++b) {
-        const int64_t L = seq_lens_host[b] > 0 ? seq_lens_host[b] : 0;
-        std::pop_heap(slot.begin(), slot.end(), cmp);
-        int64_t& t = slot.back();
-        t += L + OVERHEAD_TOK;
-        if (t > makespan) makespan = t;
-        std::push_heap(slot.begin(), slot.end(), cmp);
-        total += (L + OVERHEAD_TOK) * ipb;
-        streamed += L * ipb;
+    // uniform batches (the common steady state) need no heap: round-robin placement is exact
+    bool uniform = true;
+    for (int b = 1; b < B; ++b) uniform = uniform && seq_lens_host[b] == seq_lens_host[0];
+    if (uniform) {
+        const int64_t L = seq_lens_host[0] > 0 ? seq_lens_host[0] : 0;
+        const int64_t rounds = ((int64_t)B + n_groups - 1) / n_groups;
+        makespan = rounds * (L + OVERHEAD_TOK);
+        total = (int64_t)B * (L + OVERHEAD_TOK) * ipb;
+        streamed = (int64_t)B * L * ipb;
+    } else {
+        for (int b = 0; b < B; ++b) {
+            const int64_t L = seq_lens_host[b] > 0 ? seq_lens_host[b] : 0;
+            std::pop_heap(slot.begin(), slot.end(), cmp);
+            int64_t& t = slot.back();
+            t += L + OVERHEAD_TOK;
+            if (t > makespan) makespan = t;
+            std::push_heap(slot.begin(), slot.end(), cmp);
+            total += (L + OVERHEAD_TOK) * ipb;
+            streamed += L * ipb;
+        }
     }
     const double ideal = (double)total / NC;
     // fp8 (three CTAs per SM) is paced by its consumer warps, not by HBM: an idle slot is lost throughput, so the
@@ -1379,9 +1607,7 @@ extern "C" int b2_paged_decode_plan_splits(const int32_t* seq_lens_host, int B, 
 extern "C" size_t b2_paged_decode_workspace_bytes(int B, int Hq, int Hkv, int d, int bs, int max_nb,
                                                   int num_splits) {
     if (!shape_ok(B, Hq, Hkv, d, bs, max_nb)) return 0;
-    Plan pl;
-    make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits, 3);   // no kv_dtype here: the bound for every variant
-    return plan_workspace(pl, B, Hq);
+    return workspace_bound(B, Hq, Hkv, bs, max_nb, num_splits, read_knobs());   // no kv_dtype here: the bound for every variant
 }
 
 extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, const void* v_cache,
@@ -1391,74 +1617,85 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
                                int64_t cache_head_stride, float scale, int kv_dtype,
                                const float* k_scale, const float* v_scale, void* workspace,
                                size_t workspace_bytes, int num_splits, void* stream) {
-    B2_REQUIRE(B >= 0 && Hq > 0 && Hkv > 0 && bs > 0 && max_nb > 0 && num_blocks > 0, B2_EINVAL,
-               "paged_decode: bad sizes B=%d Hq=%d Hkv=%d bs=%d max_nb=%d num_blocks=%lld", B, Hq, Hkv, bs,
-               max_nb, (long long)num_blocks);
+    B2_REQUIRE(B >= 0, B2_EINVAL, "paged_decode: bad batch size %d", B);
     if (B == 0) return B2_OK;
-    B2_REQUIRE(out && q && k_cache && v_cache && block_tables && seq_lens, B2_EINVAL, "paged_decode: null pointer");
-    B2_REQUIRE(d == D, B2_EUNSUPPORTED, "paged_decode: head_dim %d unsupported (kernels are built for 128)", d);
-    B2_REQUIRE(Hq % Hkv == 0, B2_EINVAL, "paged_decode: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
-    B2_REQUIRE(bs == 8 || bs == 16 || bs == 32, B2_EUNSUPPORTED, "paged_decode: block_size %d unsupported (8/16/32)", bs);
-    B2_REQUIRE(kv_dtype == B2_KV_BF16 || kv_dtype == B2_KV_FP8_E4M3, B2_EUNSUPPORTED, "paged_decode: kv_dtype %d", kv_dtype);
-    B2_REQUIRE(b2_aligned16(out) && b2_aligned16(q) && b2_aligned16(k_cache) && b2_aligned16(v_cache), B2_EINVAL,
-               "paged_decode: pointers must be 16-byte aligned");
-    B2_REQUIRE(q_stride % 8 == 0 && out_stride % 8 == 0 && q_stride >= (int64_t)Hq * D && out_stride >= (int64_t)Hq * D,
-               B2_EINVAL, "paged_decode: q/out strides");
-    B2_REQUIRE(cache_block_stride % 16 == 0 && cache_head_stride % 16 == 0 && cache_head_stride >= (int64_t)bs * D,
-               B2_EINVAL, "paged_decode: cache strides must keep 16-byte alignment");
-    B2_REQUIRE(scale > 0.f, B2_EINVAL, "paged_decode: scale must be positive");
-    B2_REQUIRE(num_splits >= 0, B2_EINVAL, "paged_decode: num_splits must be >= 0");
-    if (kv_dtype == B2_KV_FP8_E4M3) B2_REQUIRE(k_scale && v_scale, B2_EINVAL, "paged_decode: fp8 needs k_scale/v_scale");
-    B2_REQUIRE((int64_t)Hkv * ((Hq / Hkv + 15) / 16) <= 65535 && B <= 65535, B2_EUNSUPPORTED, "paged_decode: grid too large");
-    B2_REQUIRE((int64_t)B * max_nb * Hkv * ((Hq / Hkv + 7) / 8) < (1LL << 31), B2_EUNSUPPORTED,
-               "paged_decode: more than 2^31 block units");
+    int rc = check_geom(Hq, Hkv, d, bs, max_nb, num_blocks, k_cache, v_cache, cache_block_stride, cache_head_stride, scale,
+                        kv_dtype, k_scale, v_scale);
+    if (rc != B2_OK) return rc;
+    const Knobs kn = read_knobs();
+    CacheMaps maps;
+    rc = make_decode_maps(&maps, k_cache, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride,
+                          kn.two_box != 0);
+    if (rc != B2_OK) return rc;
+    const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
+    return run_decode(g, maps, kn, /*zero_first=*/true, out, q, block_tables, seq_lens, B, q_stride, out_stride, num_splits,
+                      static_cast<cudaStream_t>(stream));
+}
 
-    const int G = Hq / Hkv;
-    Plan pl;
-    make_plan(&pl, B, Hkv, G, bs, max_nb, num_splits, ctas_per_sm(kv_dtype == B2_KV_FP8_E4M3, G));
+// ---------------------------------------------------------------------------------------------
+// b2_decode_plan: the per-engine handle.  Everything that does not change between decode steps -- the two encoded
+// tensor maps (a driver call each), the environment knobs, the zeroed claim counter -- is set up once, so a step is
+// argument checks + the launches, with no driver call and no getenv on the way (host memory only; nothing on the device
+// is owned by the handle).
+// ---------------------------------------------------------------------------------------------
+struct b2_decode_plan {
+    DecodeGeom g;
+    CacheMaps maps;
+    Knobs kn;
+    int max_B;
+};
 
-    DecodeParams p;
-    p.out = static_cast<__nv_bfloat16*>(out);
-    p.q = static_cast<const __nv_bfloat16*>(q);
-    p.block_tables = block_tables;
-    p.seq_lens = seq_lens;
-    p.k_scale = k_scale;
-    p.v_scale = v_scale;
-    p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.G = G; p.HG = pl.hg; p.max_nb = max_nb;
-    p.num_splits = pl.num_splits; p.split_tokens = pl.split_tokens;
-    p.q_stride = q_stride; p.out_stride = out_stride;
-    p.scale_log2 = scale * LOG2E;
-    p.ws_o = nullptr; p.ws_lse = nullptr;
-    const size_t need = plan_workspace(pl, B, Hq);
-    p.counter = nullptr;
-    p.chunk_tokens = pl.chunk_tokens;
-    p.static_pct = pl.static_pct;
-    if (need) {
-        B2_REQUIRE(workspace && workspace_bytes >= need && b2_aligned16(workspace), B2_ENOMEM,
-                   "paged_decode: workspace %zu bytes < required %zu", workspace_bytes, need);
-        size_t body = need;
-        char* base = static_cast<char*>(workspace);
-        if (pl.num_splits == 0) {
-            B2_REQUIRE(pl.slots < (1LL << 27), B2_EUNSUPPORTED, "paged_decode: %lld partial slots", (long long)pl.slots);
-            p.counter = reinterpret_cast<uint32_t*>(base);
-            base += ws_header_bytes(B, pl.ipb);
-            body -= ws_header_bytes(B, pl.ipb);
-        }
-        p.ws_o = reinterpret_cast<float*>(base);
-        p.ws_lse = p.ws_o + body / sizeof(float) / (D + 1) * D;
+extern "C" b2_decode_plan* b2_decode_plan_create(const void* k_cache, const void* v_cache, int max_B, int Hq, int Hkv, int d,
+                                                 int bs, int max_nb, int64_t num_blocks, int64_t cache_block_stride,
+                                                 int64_t cache_head_stride, float scale, int kv_dtype,
+                                                 const float* k_scale, const float* v_scale, void* workspace,
+                                                 size_t workspace_bytes, void* stream) {
+    if (max_B <= 0) {
+        b2_set_error("decode_plan_create: bad max_B %d", max_B);
+        return nullptr;
     }
+    if (check_geom(Hq, Hkv, d, bs, max_nb, num_blocks, k_cache, v_cache, cache_block_stride, cache_head_stride, scale,
+                   kv_dtype, k_scale, v_scale) != B2_OK)
+        return nullptr;
+    const Knobs kn = read_knobs();
+    const size_t need = workspace_bound(max_B, Hq, Hkv, bs, max_nb, 0, kn);
+    if (!workspace || workspace_bytes < need || !b2_aligned16(workspace)) {
+        b2_set_error("decode_plan_create: workspace %zu bytes < required %zu (b2_paged_decode_workspace_bytes)",
+                     workspace_bytes, need);
+        return nullptr;
+    }
+    b2_decode_plan* pl = new (std::nothrow) b2_decode_plan();
+    if (!pl) {
+        b2_set_error("decode_plan_create: out of host memory");
+        return nullptr;
+    }
+    pl->g = DecodeGeom{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
+    pl->kn = kn;
+    pl->max_B = max_B;
+    if (make_decode_maps(&pl->maps, k_cache, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride,
+                         cache_head_stride, kn.two_box != 0) != B2_OK) {
+        delete pl;
+        return nullptr;
+    }
+    // the claim counter starts at zero; every dynamic-schedule call leaves it at zero again (merge_chunks_kernel)
+    if (cudaMemsetAsync(workspace, 0, WS_HEADER_BYTES, static_cast<cudaStream_t>(stream)) != cudaSuccess) {
+        b2_set_error("decode_plan_create: cudaMemsetAsync of the workspace header failed");
+        delete pl;
+        return nullptr;
+    }
+    return pl;
+}
 
-    CUtensorMap tmK, tmV;
-    int rc = make_cache_tmap(&tmK, k_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride);
-    if (rc != B2_OK) return rc;
-    rc = make_cache_tmap(&tmV, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride);
-    if (rc != B2_OK) return rc;
+extern "C" void b2_decode_plan_destroy(b2_decode_plan* pl) { delete pl; }
 
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool fp8 = kv_dtype == B2_KV_FP8_E4M3;
-    if (bs == 8) return dispatch_decode<8>(tmK, tmV, p, pl, fp8, st);
-    if (bs == 16) return dispatch_decode<16>(tmK, tmV, p, pl, fp8, st);
-    return dispatch_decode<32>(tmK, tmV, p, pl, fp8, st);
+extern "C" int b2_decode_plan_run(b2_decode_plan* pl, void* out, const void* q, const int32_t* block_tables,
+                                  const int32_t* seq_lens, int B, int64_t q_stride, int64_t out_stride, int num_splits,
+                                  void* stream) {
+    B2_REQUIRE(pl != nullptr, B2_EINVAL, "decode_plan_run: null plan");
+    B2_REQUIRE(B >= 0 && B <= pl->max_B, B2_EINVAL, "decode_plan_run: B=%d outside [0, %d]", B, pl->max_B);
+    if (B == 0) return B2_OK;
+    return run_decode(pl->g, pl->maps, pl->kn, /*zero_first=*/false, out, q, block_tables, seq_lens, B, q_stride,
+                      out_stride, num_splits, static_cast<cudaStream_t>(stream));
 }
 
 #ifdef B2_TRACE

@@ -22,12 +22,19 @@ reshape_and_cache_kernel(const __nv_bfloat16* __restrict__ k_new,
                          int Hkv, int d, int bs,
                          int64_t k_token_stride, int64_t v_token_stride,
                          int64_t cache_block_stride, int64_t cache_head_stride,
-                         const float* __restrict__ k_scale, const float* __restrict__ v_scale) {
+                         const float* __restrict__ k_scale, const float* __restrict__ v_scale,
+                         int32_t* __restrict__ block_tables, const int32_t* __restrict__ seq_lens, int max_nb) {
     const int t = blockIdx.x;
     const int64_t slot = slot_mapping[t];
     if (slot < 0) return;  // padding token
     const int64_t blk = slot / bs;
     const int off = static_cast<int>(slot - blk * bs);
+    // decode step with device-resident block tables: token t is the newest token of batch row t, at position
+    // seq_lens[t] - 1, so its slot names the block of that table column (idempotent: rewritten every step)
+    if (block_tables && threadIdx.x == 0) {
+        const int L = seq_lens[t];
+        if (L > 0 && (L - 1) / bs < max_nb) block_tables[(int64_t)t * max_nb + (L - 1) / bs] = static_cast<int32_t>(blk);
+    }
     const int vec_per_head = d >> 3;
     const int nvec = Hkv * vec_per_head;
 
@@ -108,14 +115,12 @@ dequant_blocks_kernel(__nv_bfloat16* __restrict__ k_out, __nv_bfloat16* __restri
     }
 }
 
-}  // namespace
-
-extern "C" int b2_reshape_and_cache(const void* k_new, const void* v_new, void* k_cache,
-                                    void* v_cache, const int64_t* slot_mapping, int T, int Hkv,
-                                    int d, int bs, int64_t k_token_stride, int64_t v_token_stride,
-                                    int64_t cache_block_stride, int64_t cache_head_stride,
-                                    int kv_dtype, const float* k_scale, const float* v_scale,
-                                    void* stream) {
+int reshape_and_cache_impl(const void* k_new, const void* v_new, void* k_cache,
+                           void* v_cache, const int64_t* slot_mapping, int T, int Hkv,
+                           int d, int bs, int64_t k_token_stride, int64_t v_token_stride,
+                           int64_t cache_block_stride, int64_t cache_head_stride,
+                           int kv_dtype, const float* k_scale, const float* v_scale,
+                           int32_t* block_tables, const int32_t* seq_lens, int max_nb, void* stream) {
     B2_REQUIRE(T >= 0 && Hkv > 0 && d > 0 && bs > 0, B2_EINVAL,
                "reshape_and_cache: bad sizes T=%d Hkv=%d d=%d bs=%d", T, Hkv, d, bs);
     if (T == 0) return B2_OK;
@@ -144,14 +149,39 @@ extern "C" int b2_reshape_and_cache(const void* k_new, const void* v_new, void* 
     if (kv_dtype == B2_KV_BF16) {
         reshape_and_cache_kernel<false><<<T, threads, 0, st>>>(
             kn, vn, k_cache, v_cache, slot_mapping, Hkv, d, bs, k_token_stride, v_token_stride,
-            cache_block_stride, cache_head_stride, nullptr, nullptr);
+            cache_block_stride, cache_head_stride, nullptr, nullptr, block_tables, seq_lens, max_nb);
     } else {
         reshape_and_cache_kernel<true><<<T, threads, 0, st>>>(
             kn, vn, k_cache, v_cache, slot_mapping, Hkv, d, bs, k_token_stride, v_token_stride,
-            cache_block_stride, cache_head_stride, k_scale, v_scale);
+            cache_block_stride, cache_head_stride, k_scale, v_scale, block_tables, seq_lens, max_nb);
     }
     B2_CUDA_OK(cudaGetLastError());
     return B2_OK;
+}
+
+}  // namespace
+
+extern "C" int b2_reshape_and_cache(const void* k_new, const void* v_new, void* k_cache,
+                                    void* v_cache, const int64_t* slot_mapping, int T, int Hkv,
+                                    int d, int bs, int64_t k_token_stride, int64_t v_token_stride,
+                                    int64_t cache_block_stride, int64_t cache_head_stride,
+                                    int kv_dtype, const float* k_scale, const float* v_scale,
+                                    void* stream) {
+    return reshape_and_cache_impl(k_new, v_new, k_cache, v_cache, slot_mapping, T, Hkv, d, bs, k_token_stride,
+                                  v_token_stride, cache_block_stride, cache_head_stride, kv_dtype, k_scale, v_scale,
+                                  nullptr, nullptr, 0, stream);
+}
+
+extern "C" int b2_reshape_and_cache_decode(const void* k_new, const void* v_new, void* k_cache, void* v_cache,
+                                           const int64_t* slot_mapping, int32_t* block_tables, const int32_t* seq_lens,
+                                           int B, int Hkv, int d, int bs, int max_nb, int64_t k_token_stride,
+                                           int64_t v_token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
+                                           int kv_dtype, const float* k_scale, const float* v_scale, void* stream) {
+    B2_REQUIRE(B == 0 || (block_tables && seq_lens && max_nb > 0), B2_EINVAL,
+               "reshape_and_cache_decode: block_tables / seq_lens / max_nb");
+    return reshape_and_cache_impl(k_new, v_new, k_cache, v_cache, slot_mapping, B, Hkv, d, bs, k_token_stride,
+                                  v_token_stride, cache_block_stride, cache_head_stride, kv_dtype, k_scale, v_scale,
+                                  block_tables, seq_lens, max_nb, stream);
 }
 
 extern "C" int b2_dequant_kv_blocks(void* k_out, void* v_out, const void* k_cache, const void* v_cache,
