@@ -354,6 +354,7 @@ def run_ours(args, wl_name, wl):
     step.h_qkv[:, Hq_l:Hq_l + Hkv_l].copy_(prob["k_new"].cpu())
     step.h_qkv[:, Hq_l + Hkv_l:].copy_(prob["v_new"].cpu())
     step.h_block_tables.copy_(prob["block_tables"])
+    step.upload_block_tables()          # resident tables: uploaded once, kept current by the decode-step KV write
     step.h_seq_lens.copy_(prob["seq_lens"])
     step.h_slots.copy_(prob["slot_new"])
     h2d, d2h = step.h2d_bytes, step.d2h_bytes

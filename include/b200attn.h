@@ -139,7 +139,9 @@ B2_API int b2_paged_decode(void* out, const void* q,
  * no driver call, no getenv, and two launches instead of three for the dynamic schedule (create zeroes the
  * workspace header on `stream`; every call leaves it zeroed).  The handle is host memory only; the caller still owns
  * caches and workspace, which must outlive it and must not be shared with other plans or b2_paged_decode calls
- * in flight.  workspace_bytes >= b2_paged_decode_workspace_bytes(max_B, ..., 0).  NULL on bad arguments
+ * in flight.  workspace_bytes >= b2_paged_decode_workspace_bytes(max_B, ..., 0); the first 256 bytes stay reserved
+ * for the claim counter, so a call with num_splits > 1 needs b2_paged_decode_workspace_bytes(B, ..., num_splits) + 256
+ * (B2_ENOMEM otherwise).  NULL on bad arguments
  * (b2_last_error).  Single-writer, like every handle of this library.  (vLLM analogue: the attention metadata
  * builder + `paged_attention_v1/_v2` behind reference benchmark-vllm/vllm_manager.py:371-374.) */
 typedef struct b2_decode_plan b2_decode_plan;

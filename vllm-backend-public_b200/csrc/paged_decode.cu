@@ -1498,18 +1498,20 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
     p.chunk_tokens = pl.chunk_tokens;
     p.static_pct = pl.static_pct;
     p.two_box = maps.two_box;
-    const size_t need = plan_workspace(pl, B, g.Hq);
-    if (need) {
+    // a plan handle keeps its zeroed claim counter in the workspace header: the partials of every schedule start
+    // behind it (the stateless call re-zeroes the counter itself and uses the header only for the dynamic schedule)
+    const bool header = pl.num_splits == 0 || !zero_first;
+    const size_t body = plan_workspace(pl, B, g.Hq) - (pl.num_splits == 0 ? WS_HEADER_BYTES : 0);
+    if (body) {
+        const size_t need = body + (header ? WS_HEADER_BYTES : 0);
         B2_REQUIRE(g.workspace && g.workspace_bytes >= need && b2_aligned16(g.workspace), B2_ENOMEM,
                    "paged_decode: workspace %zu bytes < required %zu", g.workspace_bytes, need);
-        size_t body = need;
         char* base = static_cast<char*>(g.workspace);
         if (pl.num_splits == 0) {
             B2_REQUIRE(pl.slots < (1LL << 27), B2_EUNSUPPORTED, "paged_decode: %lld partial slots", (long long)pl.slots);
             p.counter = reinterpret_cast<uint32_t*>(base);
-            base += WS_HEADER_BYTES;
-            body -= WS_HEADER_BYTES;
         }
+        if (header) base += WS_HEADER_BYTES;
         p.ws_o = reinterpret_cast<float*>(base);
         p.ws_lse = p.ws_o + body / sizeof(float) / (D + 1) * D;
     }
