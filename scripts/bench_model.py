@@ -117,47 +117,7 @@ if a.only not in ("all", "decode"):
     sys.exit(0)
 kc = vc = q = out = gu = oo = logits = None
 torch.cuda.empty_cache()
-from b200attn.engine import LLMEngine, SamplingParams  # noqa: E402
-from b200attn.model import resolve_config  # noqa: E402
-cfg = resolve_config(a.model)
-B, ctx = a.batch, a.ctx
-# sequences decode while later prompts are still being prefilled (decode-first schedule): give every request enough
-# new tokens to still be running when the timed steps start
-max_new = a.steps + 40 + B * ((ctx + 8191) // 8192 + 1)
-eng = LLMEngine(cfg, dev, max_num_seqs=B, max_model_len=ctx + max_new + 64, max_num_batched_tokens=8192,
-                kv_cache_dtype=a.kv)
-kv_elem = 1 if a.kv == "fp8" else 2
-import random  # noqa: E402
-rng = random.Random(0)
-t0 = time.perf_counter()
-for i in range(B):
-    eng.add_request([rng.randrange(cfg.vocab) for _ in range(ctx - 1)], SamplingParams(max_tokens=max_new, temperature=0.0))
-if ctx + max_new > eng.max_model_len:
-    sys.exit(f"ctx {ctx} + {max_new} new tokens exceed max_model_len {eng.max_model_len} of {cfg.name} "
-             "(use --model llama-3.1-8b for contexts past 8k)")
-while eng.sched.num_waiting or eng.stats.decode_steps < 5:           # prefill + 5 warm-up decode steps
-    eng.step()
-t_prefill = time.perf_counter() - t0
-torch.cuda.synchronize()
-n0 = eng.stats.generated_tokens
-t0 = time.perf_counter()
-for _ in range(a.steps):
-    eng.step()
-torch.cuda.synchronize()
-wall = time.perf_counter() - t0
-toks = eng.stats.generated_tokens - n0
-# device time of the graph replay alone (inputs resident)
-replay = next((g for (b, _), g in eng._graphs.items() if b == B), None) or list(eng._graphs.values())[-1]
-with torch.cuda.stream(eng._stream):
-    med, best = timeit(replay, iters=20)
-n_run = eng.sched.num_running if hasattr(eng.sched, "num_running") else B
-avg_ctx = ctx + max(eng.stats.generated_tokens // max(B, 1) - a.steps // 2, 0)   # sequences grew while others prefilled
-kv_bytes = B * avg_ctx * cfg.kv_bytes_per_token(kv_elem)
-w_bytes = eng.model.weight_bytes() - cfg.vocab * cfg.hidden * 2        # the embedding table is gathered, not streamed
-ceiling = B / ((kv_bytes + w_bytes) / (HBM * 1e9))
-emit(op="decode_tok_s", model=cfg.name, kv_cache=a.kv, B=B, ctx=ctx, avg_ctx_during_timing=avg_ctx, running=n_run, steps=a.steps, e2e_tok_s=toks / wall, e2e_ms_per_step=wall / a.steps * 1e3,
-     device_ms_per_step=med, device_tok_s=B / med * 1e3, hbm_bytes_per_step=kv_bytes + w_bytes,
-     roofline_tok_s_at_measured_hbm=ceiling, frac_of_roofline=(B / med * 1e3) / ceiling,
-     achieved_GBps=(kv_bytes + w_bytes) / med / 1e6, prefill_s=t_prefill, prefill_tok_s=B * (ctx - 1) / t_prefill,
-     note="e2e = engine.step() incl. scheduler, H2D of the step rows, graph replay, D2H of the sampled ids, sync; "
-          "device = CUDA-graph replay alone (32 layers + lm_head + sample)")
+sys.path.insert(0, str(ROOT))
+import bench_legs  # noqa: E402
+rec = bench_legs.decode_tok_s_leg(dev, model=a.model, B=a.batch, ctx=a.ctx, steps=a.steps, kv=a.kv)
+emit(op="decode_tok_s", **rec)

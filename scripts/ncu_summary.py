@@ -135,7 +135,12 @@ def main():
             out.append(f"| **traffic = dram read + write** | {rd + wr:.0f} | byte |")
             out.append("")
             if k < len(args.workloads):
-                traffic[args.workloads[k]] = int(rd + wr)
+                # bench.py reports the number only for the per-GPU shape it was captured on
+                sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+                from bench import WORKLOADS
+                w = WORKLOADS[args.workloads[k]]
+                traffic[args.workloads[k]] = {"per_gpu": {"B": w["B"], "Hq": w["Hq"], "Hkv": w["Hkv"]},
+                                              "dram_bytes_per_launch": int(rd + wr), "capture": args.title or rep.name}
         st = stall_summary(rep)
         if st and st["stalls"]:
             out.append("warp-state samples by stall reason (source page, summed over instructions):\n")

@@ -33,6 +33,17 @@ CASES = {
     "ragged_b16_hq32_hkv8_ctx700": (dict(B=16, Hq=32, Hkv=8, d=128, bs=16, ctx=700, seed=3, ragged=True), False),
     "ragged_b8_hq64_hkv8_ctx1100": (dict(B=8, Hq=64, Hkv=8, d=128, bs=16, ctx=1100, seed=5, ragged=True), False),
     "fp8_b8_hq32_hkv8_ctx600": (dict(B=8, Hq=32, Hkv=8, d=128, bs=16, ctx=600, seed=4, ragged=True), True),
+    # r2 (VERDICT r1 "the vLLM pin is thin"): other block sizes, contexts long enough that v2 really partitions
+    # (512-token partitions), G = 1 and G = 16, single-token sequences, a long fp8 case
+    "bs8_b6_hq8_hkv2_ctx300": (dict(B=6, Hq=8, Hkv=2, d=128, bs=8, ctx=300, seed=6, ragged=True), False),
+    "bs32_b6_hq32_hkv8_ctx900": (dict(B=6, Hq=32, Hkv=8, d=128, bs=32, ctx=900, seed=7, ragged=True), False),
+    "long_b4_hq32_hkv8_ctx4500": (dict(B=4, Hq=32, Hkv=8, d=128, bs=16, ctx=4500, seed=8, ragged=False), False),
+    "longragged_b6_hq32_hkv8_ctx5000": (dict(B=6, Hq=32, Hkv=8, d=128, bs=16, ctx=5000, seed=9, ragged=True), False),
+    "g1_b5_hq4_hkv4_ctx400": (dict(B=5, Hq=4, Hkv=4, d=128, bs=16, ctx=400, seed=10, ragged=True), False),
+    "g16_b5_hq16_hkv1_ctx600": (dict(B=5, Hq=16, Hkv=1, d=128, bs=16, ctx=600, seed=11, ragged=True), False),
+    "len1_b3_hq8_hkv2": (dict(B=3, Hq=8, Hkv=2, d=128, bs=16, ctx=1, seed=12, ragged=False), False),
+    "fp8_bs32_b4_hq32_hkv8_ctx4200": (dict(B=4, Hq=32, Hkv=8, d=128, bs=32, ctx=4200, seed=13, ragged=True), True),
+    "fp8_bs8_g16_b4_hq16_hkv1_ctx700": (dict(B=4, Hq=16, Hkv=1, d=128, bs=8, ctx=700, seed=14, ragged=True), True),
 }
 
 

@@ -283,7 +283,7 @@ def test_decode_fp8_q_range(cuda, qmul):
 # ------------------------------------------------------------------------------------------
 # full-size configs: oracle on a subset + size-independent properties
 # ------------------------------------------------------------------------------------------
-def _full_size(cuda, B, Hq, Hkv, ctx, fp8, seed, n_oracle=2):
+def _full_size(cuda, B, Hq, Hkv, ctx, fp8, seed, n_oracle=8):
     inp = R.make_inputs(B, Hq, Hkv, 128, 16, ctx, seed=seed)
     dev_k, dev_v = inp["k"].to(cuda), inp["v"].to(cuda)
     shape = (inp["num_blocks"], Hkv, 16, 128)
@@ -308,17 +308,26 @@ def _full_size(cuda, B, Hq, Hkv, ctx, fp8, seed, n_oracle=2):
     # (2) two independent kernels agree on every row
     out_simt = b200attn.paged_decode(q, kc, vc, bt, sl, impl="simt", **kw)
     assert_close(out_auto, out_simt.float(), what="tma vs simt")
-    # (3) the oracle on the first n_oracle sequences (it reads the device-written cache, copied back)
-    sub = slice(0, n_oracle)
-    need = torch.unique(inp["block_tables"][sub].flatten()).long()
+    # (3) the oracle on n_oracle sequences drawn across the batch: the first and last rows, the row that owns the
+    #     highest block id of the pool, and random ones.  The oracle builds ITS OWN cache from the same tokens
+    #     (reshape_and_cache_ref), and the device cache is compared with it bit for bit on every block those rows own:
+    #     the KV write is checked at full size against the oracle, not read back from the device.
+    g = torch.Generator().manual_seed(seed + 100)
+    top_row = int((inp["block_tables"].max(dim=1).values).argmax())
+    rows = sorted({0, B - 1, top_row} | set(torch.randperm(B, generator=g)[:max(n_oracle - 3, 0)].tolist()))
+    tok0 = torch.cat([torch.zeros(1, dtype=torch.int64), torch.cumsum(inp["seq_lens"].long(), 0)])
+    tok = torch.cat([torch.arange(int(tok0[b]), int(tok0[b + 1])) for b in rows])
     kc_ref = torch.zeros(shape, dtype=kc.dtype)
     vc_ref = torch.zeros_like(kc_ref)
-    kc_ref[need] = kc[need.to(cuda)].cpu()
-    vc_ref[need] = vc[need.to(cuda)].cpu()
     okw = dict(kv_dtype=R.KV_FP8_E4M3, k_scale=ks, v_scale=vs) if fp8 else {}
-    ref = R.paged_decode_ref(inp["q"][sub], kc_ref, vc_ref, inp["block_tables"][sub], inp["seq_lens"][sub],
+    R.reshape_and_cache_ref(inp["k"][tok], inp["v"][tok], kc_ref, vc_ref, inp["slot_mapping"][tok],
+                            *((R.KV_FP8_E4M3, ks, vs) if fp8 else ()))
+    need = torch.unique(inp["block_tables"][rows].flatten()).long()
+    assert torch.equal(bits(kc[need.to(cuda)]), bits(kc_ref[need])), "full-size KV write differs from the oracle (K)"
+    assert torch.equal(bits(vc[need.to(cuda)]), bits(vc_ref[need])), "full-size KV write differs from the oracle (V)"
+    ref = R.paged_decode_ref(inp["q"][rows], kc_ref, vc_ref, inp["block_tables"][rows], inp["seq_lens"][rows],
                              return_f32=True, **okw)
-    assert_close(out_auto[sub], ref, what="oracle subset")
+    assert_close(out_auto[torch.tensor(rows, device=cuda)], ref, what=f"oracle rows {rows}")
     # (4) permuting which sequence sits in which batch row permutes the output rows
     perm = torch.randperm(B, generator=torch.Generator().manual_seed(1)).to(cuda)
     out_p = b200attn.paged_decode(q[perm].contiguous(), kc, vc, bt[perm].contiguous(), sl[perm].contiguous(), **kw)
@@ -333,12 +342,44 @@ def test_full_size_config2_llama3_8b_b64_ctx4k(cuda):
 
 def test_full_size_config3_fp8_b128_ctx8k(cuda):
     """BASELINE.json configs[2]: fp8 e4m3 KV, batch 128, ctx 8192."""
-    _full_size(cuda, 128, 32, 8, 8192, fp8=True, seed=1, n_oracle=1)
+    _full_size(cuda, 128, 32, 8, 8192, fp8=True, seed=1)
 
 
 def test_full_size_config4_per_gpu_shard_tp8(cuda):
     """BASELINE.json configs[3] as seen by one of 8 ranks: 8 q / 1 kv head, batch 256, ctx 8192."""
-    _full_size(cuda, 256, 8, 1, 8192, fp8=False, seed=2, n_oracle=1)
+    _full_size(cuda, 256, 8, 1, 8192, fp8=False, seed=2)
+
+
+def test_full_size_config4_tp1_llama3_70b_b256_ctx8k(cuda):
+    """BASELINE.json configs[3] unsharded: 64 q / 8 kv heads (G = 8), batch 256, ctx 8192, bf16 KV -- 8.6 GB of cache.
+    The problem is generated on the device (bench.build_problem: per-sequence seeds); the oracle regenerates the tokens
+    of 8 rows (first, last, random), builds its own cache from them and is compared on the KV bits and on the output."""
+    import bench
+    B, Hq, Hkv, ctx, seed = 256, 64, 8, 8192, 4
+    prob = bench.build_problem(cuda, B, Hq, Hkv, ctx, False, seed=seed)
+    kc, vc = prob["k_cache"], prob["v_cache"]
+    bt, sl = prob["block_tables"].to(cuda), prob["seq_lens"].to(cuda)
+    out_auto = b200attn.paged_decode(prob["q"], kc, vc, bt, sl)
+    out_one = b200attn.paged_decode(prob["q"], kc, vc, bt, sl, num_splits=1)
+    out_dyn = b200attn.paged_decode(prob["q"], kc, vc, bt, sl, num_splits=0)
+    assert_close(out_one, out_auto.float(), what="config 4 tp1: single pass vs planner's schedule")
+    assert_close(out_dyn, out_auto.float(), what="config 4 tp1: dynamic vs planner's schedule")
+    g = torch.Generator().manual_seed(9)
+    rows = sorted({0, B - 1, int(prob["block_tables"].max(dim=1).values.argmax())} | set(torch.randperm(B, generator=g)[:5].tolist()))
+    shape = tuple(kc.shape)
+    kc_ref = torch.zeros(shape[0], Hkv, 16, 128, dtype=torch.bfloat16)     # 8.6 GB of zeros on the host: lazily paged
+    vc_ref = torch.zeros_like(kc_ref)
+    pos = torch.arange(ctx)
+    for b in rows:
+        k, v = bench.gen_sequence_kv(cuda, seed, b, ctx, Hkv)
+        slots = prob["block_tables"][b, pos // 16].long() * 16 + pos % 16
+        R.reshape_and_cache_ref(k.cpu(), v.cpu(), kc_ref, vc_ref, slots)
+    need = torch.unique(prob["block_tables"][rows].flatten()).long()
+    assert torch.equal(bits(kc[need.to(cuda)]), bits(kc_ref[need])), "config 4 tp1: KV write differs from the oracle (K)"
+    assert torch.equal(bits(vc[need.to(cuda)]), bits(vc_ref[need])), "config 4 tp1: KV write differs from the oracle (V)"
+    ref = R.paged_decode_ref(prob["q"][rows].cpu(), kc_ref, vc_ref, prob["block_tables"][rows], prob["seq_lens"][rows],
+                             return_f32=True)
+    assert_close(out_auto[torch.tensor(rows, device=cuda)], ref, what=f"config 4 tp1 oracle rows {rows}")
 
 
 # ------------------------------------------------------------------------------------------

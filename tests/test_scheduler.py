@@ -162,3 +162,53 @@ def test_repeated_preemption_of_the_same_request():
     st = drive(s, reqs)
     assert st["done"] == set(reqs) and st["preemptions"] >= 4
     assert all(st["sampled"][i] == 50 for i in reqs)
+
+
+def test_request_that_outgrows_the_whole_pool_ends_by_length_instead_of_livelocking():
+    """4 blocks of 16, prompt 40, 100 new tokens -- alone in the running set the request used to be
+    preempted, recomputed and preempted again for ever (175 preemptions in 200 steps, generated stuck at 25).
+    Its budget is now cut to what the pool can hold (64 cached tokens = 40 + 25 - 1) and it finishes by length."""
+    s = make(4, 16, 2, 4096, 64)
+    reqs = {1: (40, 100)}
+    kv, sampled, finished, pre = 0, 0, False, 0
+    s.add_request(1, 40, 100)
+    for _ in range(200):
+        plan = s.step()
+        pre += len(plan.preempted_ids)
+        if 1 in plan.finished_ids:
+            finished = True
+            break
+        sampled += len(plan.decode_ids) + int((plan.prefill_last == 1).sum())
+    assert finished and pre == 0
+    assert sampled == 64 - 40 + 1                      # the pool holds 64 tokens: 40 prompt + 24 generated cached, 25 sampled
+    assert s.num_free_blocks == 4 and s.num_running == 0 and s.num_waiting == 0
+    # and a second request behind it is served
+    st = drive(s, {2: (10, 5)})
+    assert st["done"] == {2}
+
+
+def test_memory_pressure_does_not_thrash_preempted_requests():
+    """8 requests (prompts ~100 tokens, 400 new tokens) on a 64-block pool.  A victim used to be re-admitted
+    in the very step that preempted it, on the blocks it had just freed, and be evicted again at the next block
+    boundary: 171 preemptions and 26 176 prefill tokens scheduled for 908 prompt tokens.  Now a step that preempts
+    admits nothing, and a preempted request returns only when its whole recompute fits."""
+    s = make(64, 16, 8, 1024, 2048)
+    rng = random.Random(3)
+    reqs = {i: (rng.randint(90, 130), 400) for i in range(8)}
+    prompt_tokens = sum(p for p, _ in reqs.values())
+    prefill_tokens = [0]
+    orig_step = s.step
+
+    def counting_step():
+        plan = orig_step()
+        prefill_tokens[0] += int(plan.prefill_len.sum())
+        assert not (len(plan.preempted_ids) and set(plan.preempted_ids.tolist()) & set(plan.prefill_ids.tolist())), \
+            "a request preempted in this step was re-admitted in the same step"
+        return plan
+
+    s.step = counting_step
+    st = drive(s, reqs)
+    assert st["done"] == set(reqs) and all(st["sampled"][i] == 400 for i in reqs)
+    # 64 blocks = 1024 token slots for 8 x ~500 tokens: preemption is unavoidable, thrashing is not
+    assert st["preemptions"] <= 40, st["preemptions"]
+    assert prefill_tokens[0] <= 12 * prompt_tokens, (prefill_tokens[0], prompt_tokens)

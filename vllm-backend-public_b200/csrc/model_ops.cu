@@ -46,7 +46,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 // ---------------------------------------------------------------------------------------------
 template <int VPT>
 __global__ void __launch_bounds__(256)
-rms_norm_kernel(__nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ x,
+rms_norm_kernel(__nv_bfloat16* out, const __nv_bfloat16* x,   // out may alias x (in-place norm): no __restrict__ on these two
                 __nv_bfloat16* __restrict__ residual, const __nv_bfloat16* __restrict__ weight,
                 int H, int64_t x_stride, int64_t out_stride, int64_t res_stride, float eps) {
     const int row = blockIdx.x;

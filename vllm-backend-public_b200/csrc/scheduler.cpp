@@ -109,7 +109,13 @@ extern "C" int b2_sched_add_request(b2_scheduler* s, int64_t req_id, int prompt_
     r.id = req_id;
     r.prompt_len = prompt_len;
     r.orig_prompt = prompt_len;
-    r.max_new = max_new_tokens;
+    // A sequence caches prompt + generated - 1 tokens.  One that would outgrow the WHOLE pool can never finish: alone
+    // in the running set it would be preempted, recomputed and preempted again for ever (a --num-gpu-blocks-override
+    // or a direct b2_sched_create can make the pool smaller than one max_model_len sequence).  Its budget is cut to
+    // what the pool can hold; it then finishes by length like any other request.
+    const int64_t pool_tokens = s->num_blocks * (int64_t)s->bs;
+    const int64_t fit_new = pool_tokens - prompt_len + 1;          // >= 2: the prompt + 1 fits (checked above)
+    r.max_new = (int)std::min<int64_t>(max_new_tokens, fit_new);
     s->reqs.emplace(req_id, r);
     s->waiting.push_back(req_id);
     return B2_OK;
@@ -189,6 +195,16 @@ extern "C" int b2_sched_step(b2_scheduler* s, b2_step_plan* plan) {
             need += blocks_for(len + 1, bs) - blocks_for(len, bs);
         }
         if (need <= b2_bm_num_free(s->bm) || s->running.empty()) break;
+        if (s->running.size() == 1) {
+            // the only running sequence holds every used block and still cannot grow: preempting it would only
+            // recompute it into the same wall.  End it by length (reported in finished_ids of this plan).
+            Req& sole = s->reqs.at(s->running.back());
+            const int64_t id = sole.id;
+            sched_release(s, sole);
+            s->reqs.erase(id);
+            s->finished.push_back(id);
+            break;
+        }
         sched_preempt(s, s->reqs.at(s->running.back()));
     }
     for (int64_t id : s->running) {
@@ -255,10 +271,20 @@ extern "C" int b2_sched_step(b2_scheduler* s, b2_step_plan* plan) {
         Req& r = s->reqs.at(s->running[i]);
         if (r.computed < r.prompt_len) plan_chunk(r);
     }
-    while (budget > 0 && !s->waiting.empty() && (int)s->running.size() < s->max_num_seqs) {
+    // A step that had to preempt admits nothing (vLLM's rule): the victim sits at the head of the queue and would take the
+    // blocks just freed, shrink its chunk to them and be evicted again at the next block boundary.
+    const bool admit = s->preempted.empty();
+    const int64_t watermark = std::max<int64_t>(1, s->num_blocks / 100);
+    while (admit && budget > 0 && !s->waiting.empty() && (int)s->running.size() < s->max_num_seqs) {
         Req& r = s->reqs.at(s->waiting.front());
         // do not start a prompt whose first chunk cannot take at least one block's worth (or all of it)
         if (b2_bm_num_free(s->bm) == 0) break;
+        // a preempted request comes back only when its whole recompute fits, with room left for the running
+        // sequences' next block crossings -- otherwise it is admitted on the freed blocks and evicted again
+        if (r.resumed) {
+            const int64_t want = blocks_for((int64_t)r.prompt_len + 1, bs) + (s->running.empty() ? 0 : watermark);
+            if (b2_bm_num_free(s->bm) < want) break;
+        }
         s->waiting.pop_front();
         if (!plan_chunk(r)) {
             s->waiting.push_front(r.id);
