@@ -285,3 +285,24 @@ def test_process_template_placeholders():
         env = yaml.safe_load(rendered)["spec"]["template"]["spec"]["containers"][0]["env"]
         ep = next(e["value"] for e in env if e["name"] == "VLLM_MODEL_ENDPOINT")
         assert ep == url + "/v1/completions" and ep.split("/v1/")[0] == url
+
+
+def test_chat_uses_the_models_own_template_when_the_tokenizer_ships_one(tmp_path):
+    """/v1/chat/completions must prompt instruct weights with THEIR chat template (tokenizer_config.json),
+    not a hard-coded format; the byte tokenizer (random-init weights) has none and keeps the plain fallback."""
+    import json
+    from tokenizers import Tokenizer, models, pre_tokenizers
+    from b200attn.tokenizer import ByteTokenizer, HFTokenizer
+    vocab = {"<s>": 0, "</s>": 1, "[INST]": 2, "[/INST]": 3, "hi": 4, "there": 5, "<unk>": 6}
+    tok = Tokenizer(models.WordLevel(vocab, unk_token="<unk>"))
+    tok.pre_tokenizer = pre_tokenizers.WhitespaceSplit()
+    tok.save(str(tmp_path / "tokenizer.json"))
+    (tmp_path / "tokenizer_config.json").write_text(json.dumps({
+        "bos_token": {"content": "<s>"}, "eos_token": "</s>",
+        "chat_template": "{{ bos_token }} {% for m in messages %}{% if m['role'] == 'user' %}[INST] {{ m['content'] }} [/INST] "
+                         "{% else %}{{ m['content'] }} {{ eos_token }} {% endif %}{% endfor %}"}))
+    t = HFTokenizer(tmp_path)
+    text = t.apply_chat_template([{"role": "user", "content": "hi"}, {"role": "assistant", "content": "there"},
+                                  {"role": "user", "content": "hi there"}])
+    assert t.encode_rendered(text) == [0, 2, 4, 3, 5, 1, 2, 4, 5, 3]
+    assert not hasattr(ByteTokenizer(300), "apply_chat_template")

@@ -113,6 +113,11 @@ class LLMEngine:
             if num_blocks < self.max_nb + 1:
                 raise RuntimeError(f"KV pool of {num_blocks} blocks cannot hold one sequence of max_model_len "
                                    f"{self.max_model_len} (gpu_memory_utilization {util}, {free1 >> 20} MiB free)")
+        if int(num_blocks) < self.max_nb + 1:
+            # also for --num-gpu-blocks-override: a pool that cannot hold one max_model_len sequence would end long
+            # requests early (the scheduler cuts their budget to the pool) -- refuse it at start-up instead
+            raise RuntimeError(f"KV pool of {num_blocks} blocks cannot hold one sequence of max_model_len "
+                               f"{self.max_model_len} ({self.max_nb + 1} blocks of {block_size} tokens needed)")
         self.num_blocks = int(num_blocks)
         self.model.num_blocks = self.num_blocks
         self.model.kv = torch.zeros(cfg.layers, 2, self.num_blocks, cfg.Hkv, block_size, cfg.d, dtype=self.kv_dtype,
@@ -138,7 +143,7 @@ class LLMEngine:
         self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
         self._buckets = _buckets(B)
         self._stream = torch.cuda.Stream(self.dev)
-        self.model.decode_workspace(B, self.max_nb)
+        self.model.prepare_decode(B, self.max_nb)     # workspace sized once for max_num_seqs + per-layer decode plans
         self._launches_per_layer = 7          # rms, rope+cache, attention(+merge), rms, silu, (GEMMs are cuBLAS)
 
         self.requests: Dict[int, Request] = {}
@@ -147,6 +152,8 @@ class LLMEngine:
         self._incoming: List[Request] = []
         self._aborts: List[int] = []
         self.stats = EngineStats()
+        self.metrics: Dict[str, int] = {}
+        self._publish_metrics()
         torch.cuda.synchronize(self.dev)
 
     # ------------------------------------------------------------------------------------ requests
@@ -188,6 +195,13 @@ class LLMEngine:
         self.requests.pop(r.id, None)
         if r.on_token:
             r.on_token(r, None)
+
+    def _publish_metrics(self) -> None:
+        """Engine thread only: a fresh dict swapped in whole, read by the HTTP thread (/metrics)."""
+        s = self.stats
+        self.metrics = {"running": self.sched.num_running, "waiting": self.sched.num_waiting,
+                        "free_blocks": self.sched.num_free_blocks, "prompt_tokens": s.prompt_tokens,
+                        "generated_tokens": s.generated_tokens, "steps": s.steps, "preemptions": s.preemptions}
 
     # ------------------------------------------------------------------------------------ one step
     def _admit(self) -> None:
@@ -231,7 +245,17 @@ class LLMEngine:
             if r is not None:
                 r.n_preempted += 1
                 self.stats.preemptions += 1
+        for rid in plan.finished_ids:
+            # normally the engine has already finished these itself (same length rule); a request the scheduler had
+            # to end (its KV outgrew the whole pool) is still live here: close it
+            r = self.requests.get(int(rid))
+            if r is not None:
+                r.finished, r.finish_reason, r.t_done = True, "length", time.perf_counter()
+                self.requests.pop(r.id, None)
+                if r.on_token:
+                    r.on_token(r, None)
         if plan.empty:
+            self._publish_metrics()
             return []
         nd, npf = len(plan.decode_ids), len(plan.prefill_ids)
         if npf == 0:
@@ -259,6 +283,7 @@ class LLMEngine:
                 self._finish(r, "length")
         self.stats.steps += 1
         self.stats.busy_s += time.perf_counter() - t0
+        self._publish_metrics()
         return out
 
     # ------------------------------------------------------------------------------------ decode-only step

@@ -157,6 +157,7 @@ class LlamaModel:
             self.k_scale = torch.ones(1, dtype=torch.float32, device=device)
             self.v_scale = torch.ones(1, dtype=torch.float32, device=device)
         self._ws: Optional[torch.Tensor] = None
+        self._plans: Optional[list] = None      # per-layer b2_decode_plan handles (prepare_decode)
 
     # ------------------------------------------------------------------ weights
     def _random_init(self, seed: int) -> None:
@@ -217,10 +218,24 @@ class LlamaModel:
 
     # ------------------------------------------------------------------ forward
     def decode_workspace(self, max_batch: int, max_nb: int) -> torch.Tensor:
-        need = max(ops.decode_workspace_bytes(max_batch, self.cfg.Hq, self.cfg.Hkv, self.cfg.d, self.bs, max_nb, 0), 16)
-        if self._ws is None or self._ws.numel() < need:
+        """The decode scratch, allocated ONCE for the largest batch (b2_paged_decode_workspace_bytes serves every batch
+        size up to it).  Captured CUDA graphs hold its address, so it is never replaced: a larger request is a bug."""
+        need = max(ops.decode_workspace_bytes(max_batch, self.cfg.Hq, self.cfg.Hkv, self.cfg.d, self.bs, max_nb, 0), 256)
+        if self._ws is None:
             self._ws = torch.zeros(need, dtype=torch.uint8, device=self.dev)
+        elif self._ws.numel() < need:
+            raise RuntimeError(f"decode workspace holds {self._ws.numel()} bytes but batch {max_batch} x {max_nb} blocks "
+                               f"needs {need}: size it once for max_num_seqs / max_model_len (prepare_decode)")
         return self._ws
+
+    def prepare_decode(self, max_batch: int, max_nb: int) -> None:
+        """One b2_decode_plan per layer over that layer's K/V pool, all sharing the one workspace (the layers run one
+        after the other on one stream): the TMA descriptors are encoded here, not in every step."""
+        ws = self.decode_workspace(max_batch, max_nb)
+        self._plans = [ops.DecodePlan(self.kv[l, 0], self.kv[l, 1], max_batch, self.cfg.Hq, max_nb,
+                                      k_scale=self.k_scale, v_scale=self.v_scale, workspace=ws)
+                       for l in range(self.cfg.layers)]
+        self._plan_shape = (max_batch, max_nb)
 
     def forward(self, tokens: torch.Tensor, positions: torch.Tensor, slots: torch.Tensor, n_decode: int,
                 dec_block_tables: Optional[torch.Tensor], dec_seq_lens: Optional[torch.Tensor],
@@ -249,10 +264,14 @@ class LlamaModel:
             ops.rope_and_cache(qkv, positions, self.cos_sin, kc, vc, slots, c.Hq, self.k_scale, self.v_scale)
             q = qkv.view(T, c.Hq + 2 * c.Hkv, c.d)[:, : c.Hq]
             if n_decode:
-                ops.paged_decode(q[:n_decode], kc, vc, dec_block_tables, dec_seq_lens, k_scale=self.k_scale,
-                                 v_scale=self.v_scale, out=attn[:n_decode],
-                                 workspace=self.decode_workspace(n_decode, dec_block_tables.shape[1]),
-                                 num_splits=num_splits)
+                if self._plans is not None and n_decode <= self._plan_shape[0] \
+                        and dec_block_tables.shape[1] == self._plan_shape[1]:
+                    self._plans[l].run(q[:n_decode], dec_block_tables, dec_seq_lens, attn[:n_decode], num_splits)
+                else:
+                    ops.paged_decode(q[:n_decode], kc, vc, dec_block_tables, dec_seq_lens, k_scale=self.k_scale,
+                                     v_scale=self.v_scale, out=attn[:n_decode],
+                                     workspace=self.decode_workspace(n_decode, dec_block_tables.shape[1]),
+                                     num_splits=num_splits)
             if prefill is not None and prefill.total_tokens:
                 if fp8_plan is None:
                     ops.prefill_attention(q[n_decode:], kc, vc, prefill.block_tables, prefill.cu_q, prefill.ctx_start,

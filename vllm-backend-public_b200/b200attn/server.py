@@ -87,7 +87,9 @@ class EngineRunner:
                     import traceback
                     traceback.print_exc()
                     self.failed = f"{type(e).__name__}: {e}"
-                    for r in list(eng.requests.values()):
+                    with eng._lock:                               # requests queued but never admitted must end too
+                        queued, eng._incoming = eng._incoming, []
+                    for r in list(eng.requests.values()) + queued:
                         r.finished, r.finish_reason = True, "error"
                         if r.on_token:
                             r.on_token(r, None)
@@ -197,6 +199,8 @@ class _Choice:
         tok = await self.queue.get()
         if tok is None:
             reason = self.req.finish_reason or "stop"
+            if reason.startswith("error:"):                 # refused at admission (it can never fit): the request's fault
+                raise ApiError(400, reason[6:].strip(), param="prompt")
             if reason.startswith("error"):
                 raise ApiError(500, reason, "server_error")
             self.finish_reason = "length" if reason == "length" else "stop"
@@ -271,12 +275,14 @@ def create_app(runner: EngineRunner):
         lines = [f"b200attn_http_requests_total {counters['requests']}", f"b200attn_http_errors_total {counters['errors']}"]
         eng = runner.engine
         if eng is not None:
-            s = eng.stats
-            lines += [f"b200attn_num_requests_running {eng.sched.num_running}",
-                      f"b200attn_num_requests_waiting {eng.sched.num_waiting}",
-                      f"b200attn_kv_blocks_free {eng.sched.num_free_blocks}", f"b200attn_kv_blocks_total {eng.num_blocks}",
-                      f"b200attn_prompt_tokens_total {s.prompt_tokens}", f"b200attn_generation_tokens_total {s.generated_tokens}",
-                      f"b200attn_engine_steps_total {s.steps}", f"b200attn_preemptions_total {s.preemptions}"]
+            # a snapshot the engine thread publishes after every step: the C++ scheduler is single-writer and is never
+            # read from the event loop
+            m = eng.metrics
+            lines += [f"b200attn_num_requests_running {m['running']}",
+                      f"b200attn_num_requests_waiting {m['waiting']}",
+                      f"b200attn_kv_blocks_free {m['free_blocks']}", f"b200attn_kv_blocks_total {eng.num_blocks}",
+                      f"b200attn_prompt_tokens_total {m['prompt_tokens']}", f"b200attn_generation_tokens_total {m['generated_tokens']}",
+                      f"b200attn_engine_steps_total {m['steps']}", f"b200attn_preemptions_total {m['preemptions']}"]
         return PlainTextResponse("\n".join(lines) + "\n")
 
     def check_model(body):
@@ -296,6 +302,9 @@ def create_app(runner: EngineRunner):
                                f"{len(p)}", param="prompt", code="context_length_exceeded")
             if max(p) >= eng.cfg.vocab or min(p) < 0:
                 raise ApiError(400, f"token id outside the vocabulary [0, {eng.cfg.vocab})", param="prompt")
+            if (len(p) + eng.block_size) // eng.block_size > eng.num_blocks:
+                raise ApiError(400, f"a prompt of {len(p)} tokens cannot fit the KV pool of {eng.num_blocks} blocks",
+                               param="prompt", code="context_length_exceeded")
         loop = asyncio.get_running_loop()
         echo = bool(body.get("echo", False)) and not chat
         choices: List[_Choice] = []
@@ -416,8 +425,14 @@ def create_app(runner: EngineRunner):
             msgs = body.get("messages")
             if not (isinstance(msgs, list) and msgs and all(isinstance(m, dict) and "role" in m for m in msgs)):
                 raise ApiError(400, "messages must be a non-empty list of {role, content}", param="messages")
-            text = "".join(f"<|{m['role']}|>\n{m.get('content') or ''}\n" for m in msgs) + "<|assistant|>\n"
-            return await run_completion(body, [runner.tokenizer.encode(text)], chat=True)
+            tok = runner.tokenizer
+            text = tok.apply_chat_template(msgs) if hasattr(tok, "apply_chat_template") else None
+            if text is not None:                          # the model's own template (instruct weights from an HF directory)
+                ids = tok.encode_rendered(text)
+            else:                                         # no template shipped (byte tokenizer, random-init weights)
+                text = "".join(f"<|{m['role']}|>\n{m.get('content') or ''}\n" for m in msgs) + "<|assistant|>\n"
+                ids = tok.encode(text)
+            return await run_completion(body, [ids], chat=True)
         except ApiError as e:
             return err(e)
         except ValueError as e:

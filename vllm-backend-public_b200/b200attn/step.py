@@ -30,7 +30,7 @@ from typing import Dict, Optional, Tuple
 
 import torch
 
-from . import ops
+from . import _lib, ops
 
 
 class DecodeStep:
@@ -65,6 +65,8 @@ class DecodeStep:
         self.workspace = self.plan_handle.workspace
         self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
         self._stream = torch.cuda.Stream(self.dev)
+        self._plan_fn = _lib.load().b2_paged_decode_plan_splits
+        self._sl_ptr = self.h_seq_lens.data_ptr()
 
     # ------------------------------------------------------------------------------------------
     @property
@@ -104,7 +106,11 @@ class DecodeStep:
         self.plan_handle.run(q, bt, sl, self.h_out[:B], num_splits)
 
     def plan(self, B: int) -> int:
-        return ops.plan_num_splits(self.h_seq_lens[:B], self.Hq, self.Hkv, self.d, self.bs, self.kv_dtype)
+        # straight ctypes call on the pinned buffer's address: this runs on the host every step, before the launch
+        rc = self._plan_fn(self._sl_ptr, B, self.Hq, self.Hkv, self.d, self.bs, self.kv_dtype)
+        if rc < 0:
+            _lib.check(rc)
+        return rc
 
     def run(self, B: Optional[int] = None, num_splits: Optional[int] = None) -> torch.Tensor:
         """Run the step for the first B rows of the host buffers; returns the pinned output rows (valid on return)."""
