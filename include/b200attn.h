@@ -316,6 +316,47 @@ B2_API int64_t b2_sched_num_running(const b2_scheduler* s);
 B2_API int64_t b2_sched_num_free_blocks(const b2_scheduler* s);
 B2_API int64_t b2_sched_generated(const b2_scheduler* s, int64_t req_id);   /* tokens sampled so far; < 0 unknown */
 
+/* ---------------------------------------------------------------------------------------------
+ * Tensor-parallel exchange over NVLink peer memory: what `--tensor-parallel-size N` (VLLMConfig.tensor_parallel_size,
+ * reference benchmark-vllm/models.py:11 -> vllm_templates.py:55,226; resources x tp :459-461) adds to a decoder
+ * layer.  Heads and MLP columns are sharded over tp GPUs (one process per GPU); o_proj / down_proj leave a PARTIAL
+ * [T, hidden] sum on every rank.  vLLM runs an all-reduce (NCCL or its custom all-reduce -- which the reference
+ * switches off with --disable-custom-all-reduce, vllm_templates.py:62) followed by fused_add_rms_norm; here one kernel
+ * does both over peer-mapped buffers (csrc/comm.cu).
+ *
+ * b2_comm_alloc / open / close / free   a cudaMalloc region plus its 64-byte CUDA IPC handle (the ONE place the
+ *     library allocates device memory: the region must be exportable).  Every rank allocates one region of
+ *     b2_comm_region_bytes(...) bytes, exchanges handles out of band, opens the peers' handles.
+ * b2_comm_create   handle over the tp regions (regions[rank] = this rank's own pointer), tp in {1, 2, 4, 8}.
+ *     max_rows x H = the largest partial sum that takes the one-shot path; gather_rows x gather_cols = the [T, V]
+ *     logits buffer.
+ * b2_comm_input(comm, slot)   device pointer of this rank's partial-sum buffer `slot` (0 after o_proj, 1 after
+ *     down_proj), bf16 [max_rows, H] contiguous: the GEMM writes its output there.
+ * b2_comm_allreduce_rms_norm   h = bf16(sum_r partial_r (+ residual)) -> residual (when given);
+ *     out = weight ? bf16(weight * h * rsqrt(mean(h^2) + eps)) : h.  The sum runs in rank order in fp32, so every
+ *     rank computes the same bits.  Every rank must call it with the same (slot, T) in the same order, and
+ *     alternate the slots (that is what makes buffer reuse safe, see comm.cu).
+ * b2_comm_allgather_cols   gathered[t][rank*cols + c] = local[t][c] on every rank (b2_comm_gathered: bf16
+ *     [gather_rows, tp*cols]); the vocab-parallel lm_head.
+ * Both only enqueue on `stream`; they are CUDA-graph capturable (the barrier epoch is device state).  A peer that
+ * never arrives traps the waiting kernel after ~10 s (B2_ECUDA at the next sync) instead of hanging the GPU.
+ * ------------------------------------------------------------------------------------------- */
+#define B2_COMM_HANDLE_BYTES 64
+#define B2_COMM_MAX_RANKS 8
+B2_API int b2_comm_alloc(size_t bytes, void** ptr, void* handle /* B2_COMM_HANDLE_BYTES out */);
+B2_API int b2_comm_open(const void* handle, void** ptr);
+B2_API int b2_comm_close(void* ptr);
+B2_API int b2_comm_free(void* ptr);
+B2_API size_t b2_comm_region_bytes(int max_rows, int H, int gather_rows, int gather_cols);
+B2_API void* b2_comm_create(int rank, int tp, void* const* regions, size_t region_bytes, int max_rows, int H,
+                            int gather_rows, int gather_cols);
+B2_API void b2_comm_destroy(void* comm);
+B2_API void* b2_comm_input(void* comm, int slot);
+B2_API void* b2_comm_gathered(void* comm);
+B2_API int b2_comm_allreduce_rms_norm(void* comm, int slot, void* out, void* residual, const void* weight, int T,
+                                      int64_t out_stride, int64_t res_stride, float eps, void* stream);
+B2_API int b2_comm_allgather_cols(void* comm, const void* local, int64_t local_stride, int T, int cols, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

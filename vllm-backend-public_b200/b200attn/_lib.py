@@ -73,6 +73,17 @@ SIGNATURES = {
     "b2_sched_num_running": (i64, [vp]),
     "b2_sched_num_free_blocks": (i64, [vp]),
     "b2_sched_generated": (i64, [vp, i64]),
+    "b2_comm_alloc": (i32, [sz, vp, vp]),
+    "b2_comm_open": (i32, [vp, vp]),
+    "b2_comm_close": (i32, [vp]),
+    "b2_comm_free": (i32, [vp]),
+    "b2_comm_region_bytes": (sz, [i32, i32, i32, i32]),
+    "b2_comm_create": (vp, [i32, i32, vp, sz, i32, i32, i32, i32]),
+    "b2_comm_destroy": (None, [vp]),
+    "b2_comm_input": (vp, [vp, i32]),
+    "b2_comm_gathered": (vp, [vp]),
+    "b2_comm_allreduce_rms_norm": (i32, [vp, i32, vp, vp, vp, i32, i64, i64, f32, vp]),
+    "b2_comm_allgather_cols": (i32, [vp, vp, i64, i32, i32, vp]),
 }
 
 _lib = None
