@@ -623,6 +623,17 @@ def run_ours(args, wl_name, wl):
                 "collective": "none on the attention path", "clocks": clk4}
             line["sharded_parity"] = parity
 
+    # ---------------- the served engine at --tensor-parallel-size N (rows a4 / n1): parity, exchange cost, tok/s ------
+    if extras and world > 1:
+        import bench_legs
+        from b200attn.tp import TPGroup
+        group = TPGroup(dev)
+        tp_rec = {"parity": bench_legs.tp_parity_leg(dev, group),
+                  "exchange": bench_legs.tp_comm_leg(dev, group),
+                  "decode_tok_s": bench_legs.tp_decode_leg(dev, group, steps=max(20, min(K, 50)))}
+        if rank == 0:
+            line["tp_serving"] = tp_rec
+
     if rank == 0:
         if world == 1 and not args.no_cpu:
             n_seq = 8

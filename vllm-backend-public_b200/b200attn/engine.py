@@ -14,6 +14,7 @@ plan's seq_lens (b2_paged_decode_plan_splits).
 from __future__ import annotations
 
 import itertools
+import os
 import threading
 import time
 from dataclasses import dataclass, field
@@ -63,6 +64,8 @@ class EngineStats:
     preemptions: int = 0
     gpu_launches: int = 0
     busy_s: float = 0.0
+    device_ms: float = 0.0          # CUDA-event time of the decode-step replays (only with engine.time_device)
+    device_steps: int = 0
 
 
 def _buckets(max_batch: int) -> List[int]:
@@ -77,7 +80,10 @@ class LLMEngine:
                  max_model_len: int = 8192, block_size: int = 16, gpu_memory_utilization: float = 0.9,
                  max_num_batched_tokens: int = 8192, num_blocks: Optional[int] = None, seed: int = 0,
                  weights_dir=None, eos_token_id: Optional[int] = None, enforce_eager: bool = False,
-                 kv_cache_dtype: str = "auto"):
+                 kv_cache_dtype: str = "auto", tp=None):
+        """`tp`: b200attn.tp.TPGroup when the engine runs tensor-parallel (one engine per rank, all built with the same
+        arguments).  Rank 0 owns the request queue and publishes admissions / aborts before every step; the other ranks
+        mirror its steps from `worker_loop()`."""
         if not torch.cuda.is_available():
             raise RuntimeError("b200attn engine needs a CUDA device: there is no CPU path")
         if kv_cache_dtype not in ("auto", "bfloat16", "bf16", "fp8", "fp8_e4m3"):
@@ -85,6 +91,10 @@ class LLMEngine:
         self.kv_dtype = torch.uint8 if kv_cache_dtype.startswith("fp8") else torch.bfloat16
         self.dev = device or torch.device("cuda", torch.cuda.current_device())
         torch.cuda.set_device(self.dev)
+        self.tp = tp if tp is not None and tp.size > 1 else None
+        self.tp_size = self.tp.size if self.tp is not None else 1
+        self.is_driver = self.tp is None or self.tp.rank == 0
+        self._worker_msg = None
         self.cfg = cfg
         self.block_size = block_size
         self.max_num_seqs = max_num_seqs
@@ -97,8 +107,13 @@ class LLMEngine:
         # weights first, then size the block pool from what is left (gpu_memory_utilization of the whole device)
         free0, total = torch.cuda.mem_get_info(self.dev)
         self.model = LlamaModel(cfg, self.dev, num_blocks=1, block_size=block_size, seed=seed, weights_dir=weights_dir,
-                                max_position=self.max_model_len, kv_dtype=self.kv_dtype)
+                                max_position=self.max_model_len, kv_dtype=self.kv_dtype, tp=self.tp)
         del self.model.kv
+        if self.tp is not None:
+            # peer-mapped exchange buffers (csrc/comm.cu): partial sums of up to max(max_num_seqs, 256) rows take the
+            # one-shot path; the gathered logits hold one row per sequence
+            self.tp.setup_comm(max(max_num_seqs, 256), cfg.hidden, max_num_seqs if self.model.vocab_parallel else 0,
+                               cfg.vocab if self.model.vocab_parallel else 0)
         if num_blocks is None:
             util = gpu_memory_utilization if gpu_memory_utilization and gpu_memory_utilization > 0 else 0.9
             torch.cuda.synchronize(self.dev)
@@ -107,9 +122,11 @@ class LLMEngine:
             act = self.max_num_batched_tokens * (3 * cfg.inter + self.model.qkv_width + 6 * cfg.hidden) * 2 \
                 + max_num_seqs * cfg.vocab * 2 * 2 + (1 << 30)
             budget = int(total * util) - used - act
-            per_block = cfg.kv_bytes_per_token(1 if self.kv_dtype == torch.uint8 else 2) * block_size
+            per_block = cfg.kv_bytes_per_token(1 if self.kv_dtype == torch.uint8 else 2, self.tp_size) * block_size
             want = max_num_seqs * self.max_nb + 64                   # every sequence at max_model_len
             num_blocks = max(min(budget // per_block, want), 0)
+            if self.tp is not None:
+                num_blocks = self.tp.min_int(num_blocks)             # every rank runs the same scheduler on the same pool
             if num_blocks < self.max_nb + 1:
                 raise RuntimeError(f"KV pool of {num_blocks} blocks cannot hold one sequence of max_model_len "
                                    f"{self.max_model_len} (gpu_memory_utilization {util}, {free1 >> 20} MiB free)")
@@ -120,8 +137,8 @@ class LLMEngine:
                                f"{self.max_model_len} ({self.max_nb + 1} blocks of {block_size} tokens needed)")
         self.num_blocks = int(num_blocks)
         self.model.num_blocks = self.num_blocks
-        self.model.kv = torch.zeros(cfg.layers, 2, self.num_blocks, cfg.Hkv, block_size, cfg.d, dtype=self.kv_dtype,
-                                    device=self.dev)
+        self.model.kv = torch.zeros(cfg.layers, 2, self.num_blocks, self.model.Hkv, block_size, cfg.d,
+                                    dtype=self.kv_dtype, device=self.dev)
         self.sched = Scheduler(self.num_blocks, block_size, max_num_seqs, self.max_model_len, self.max_num_batched_tokens)
 
         # pinned staging + static device inputs of the decode graph
@@ -143,8 +160,12 @@ class LLMEngine:
         self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
         self._buckets = _buckets(B)
         self._stream = torch.cuda.Stream(self.dev)
+        self.time_device = False                 # bench: CUDA events around every decode replay -> stats.device_ms
+        self._ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
         self.model.prepare_decode(B, self.max_nb)     # workspace sized once for max_num_seqs + per-layer decode plans
         self._launches_per_layer = 7          # rms, rope+cache, attention(+merge), rms, silu, (GEMMs are cuBLAS)
+        # what the decode-schedule planner sees: this rank's heads
+        self._plan_heads = (self.model.Hq, self.model.Hkv)
 
         self.requests: Dict[int, Request] = {}
         self._ids = itertools.count(1)
@@ -205,9 +226,16 @@ class LLMEngine:
 
     # ------------------------------------------------------------------------------------ one step
     def _admit(self) -> None:
-        with self._lock:
-            incoming, self._incoming = self._incoming, []
-            aborts, self._aborts = self._aborts, []
+        if self.is_driver:
+            with self._lock:
+                incoming, self._incoming = self._incoming, []
+                aborts, self._aborts = self._aborts, []
+            if self.tp is not None:                       # tell the other ranks what this step admits / aborts
+                from . import tp as _tp
+                self.tp.channel.send(_tp.encode_step(incoming, aborts))
+        else:
+            incoming, aborts = self._worker_msg
+            self._worker_msg = None
         for r in incoming:
             try:
                 self.sched.add_request(r.id, len(r.prompt_ids), r.params.max_tokens)
@@ -335,7 +363,7 @@ class LLMEngine:
         self._np_bt[:nd, :used] = plan.block_tables[:, :used]
         self._np_temp[:bucket] = 0
         self._np_temp[:nd] = [r.params.temperature for r in reqs]
-        num_splits = ops.plan_num_splits(self._h_i32[B:B + nd], self.cfg.Hq, self.cfg.Hkv, self.cfg.d, self.block_size,
+        num_splits = ops.plan_num_splits(self._h_i32[B:B + nd], *self._plan_heads, self.cfg.d, self.block_size,
                                          ops.KV_FP8_E4M3 if self.kv_dtype == torch.uint8 else ops.KV_BF16)
         replay = self._decode_graph(bucket, num_splits)
         with torch.cuda.stream(self._stream):
@@ -343,9 +371,16 @@ class LLMEngine:
             self._d_i32.copy_(self._h_i32, non_blocking=True)
             self._d_bt[:nd, :used].copy_(self._h_bt[:nd, :used], non_blocking=True)
             self._d_temp.copy_(self._h_temp, non_blocking=True)
+            if self.time_device:
+                self._ev[0].record(self._stream)
             replay()
+            if self.time_device:
+                self._ev[1].record(self._stream)
             self._h_out[:bucket].copy_(self._d_out[:bucket], non_blocking=True)
         self._stream.synchronize()
+        if self.time_device:
+            self.stats.device_ms += self._ev[0].elapsed_time(self._ev[1])
+            self.stats.device_steps += 1
         self.stats.gpu_launches += self.cfg.layers * self._launches_per_layer + 3
         return reqs, self._h_out[:nd].tolist()
 
@@ -395,7 +430,7 @@ class LLMEngine:
         if nd:
             used = (int(plan.seq_lens.max()) + bsz - 1) // bsz
             self._np_bt[:nd, :used] = plan.block_tables[:, :used]
-            num_splits = ops.plan_num_splits(self._hm_meta[:nd], self.cfg.Hq, self.cfg.Hkv, self.cfg.d, bsz,
+            num_splits = ops.plan_num_splits(self._hm_meta[:nd], *self._plan_heads, self.cfg.d, bsz,
                                                  ops.KV_FP8_E4M3 if self.kv_dtype == torch.uint8 else ops.KV_BF16)
         dev = self.dev
         with torch.cuda.stream(self._stream):
@@ -422,7 +457,11 @@ class LLMEngine:
         return sample_reqs, (self._h_out[:ns].tolist() if ns else [])
 
     def capture_all(self) -> int:
-        """Capture the decode graph of every (batch bucket, schedule) now instead of at first use (server start-up)."""
+        """Capture the decode graph of every (batch bucket, schedule) now instead of at first use (server start-up).
+        Tensor parallel: rank 0's call makes every rank capture (the warm-up runs exchange over NVLink in lockstep)."""
+        if self.tp is not None and self.is_driver:
+            from . import tp as _tp
+            self.tp.channel.send(_tp.encode_step([], [], _tp.MSG_CAPTURE))
         n = 0
         if self.use_graphs:
             for b in self._buckets:
@@ -430,6 +469,42 @@ class LLMEngine:
                     self._decode_graph(b, splits)
                     n += 1
         return n
+
+    # ------------------------------------------------------------------------------------ tensor-parallel ranks
+    def worker_loop(self) -> None:
+        """Ranks 1..tp-1: mirror rank 0 step by step.  Each message carries what rank 0 admitted / aborted before its
+        step; the plan, the schedule, the CUDA graph and the sampled ids then follow from identical state."""
+        from . import tp as _tp
+        assert self.tp is not None and not self.is_driver
+        parent = os.getppid()
+        while True:
+            try:
+                payload = self.tp.channel.recv(timeout=5.0)
+            except TimeoutError:
+                if os.getppid() != parent:            # the launcher is gone: do not keep a GPU spinning
+                    return
+                continue
+            cmd, reqs, aborts = _tp.decode_step(payload)
+            if cmd == _tp.MSG_SHUTDOWN:
+                return
+            if cmd == _tp.MSG_CAPTURE:
+                self.capture_all()
+                continue
+            incoming = [Request(rid, list(prompt), params, seed=seed) for rid, prompt, params, seed in reqs]
+            self._worker_msg = (incoming, aborts)
+            self.step()
+
+    def shutdown_workers(self) -> None:
+        """Rank 0: release the other ranks from worker_loop()."""
+        if self.tp is not None and self.is_driver:
+            from . import tp as _tp
+            self.tp.channel.send(_tp.encode_step([], [], _tp.MSG_SHUTDOWN))
+
+    def close(self) -> None:
+        """Drop the CUDA graphs and the peer-mapped buffers (tensor parallel: call on every rank)."""
+        self._graphs.clear()
+        if self.tp is not None:
+            self.tp.close()
 
     # ------------------------------------------------------------------------------------ loops
     def run_until_idle(self, max_steps: int = 10 ** 9) -> None:

@@ -193,9 +193,9 @@ class EngineArgs:
         """Arguments of b200attn.engine.LLMEngine, with the notes of the module docstring applied."""
         if self.pipeline_parallel_size != 1:
             raise ValueError("pipeline_parallel_size > 1 is not supported (one process per GPU, KV-head sharding only)")
-        if self.tensor_parallel_size != 1:
-            raise ValueError("the serving engine runs on one GPU; KV-head sharded attention for tensor_parallel_size "
-                             "> 1 is provided by b200attn.parallel (SURVEY.md section 8(e))")
+        if self.tensor_parallel_size not in (1, 2, 4, 8):
+            raise ValueError(f"tensor_parallel_size {self.tensor_parallel_size}: one process per GPU of one node, "
+                             "1, 2, 4 or 8 (b200attn.tp)")
         if self.block_size not in (8, 16, 32):
             raise ValueError(f"block_size {self.block_size}: the kernels are built for 8, 16 and 32")
         kw = dict(max_num_seqs=self.max_num_seqs, block_size=self.block_size,

@@ -64,6 +64,7 @@ REGISTRY: Dict[str, ModelConfig] = {
     # test-sized geometries (same head_dim, same op sequence)
     "tiny": ModelConfig("tiny", 512, 2, 4, 2, 1024, 1024, max_position=8192),
     "small": ModelConfig("small", 1024, 4, 8, 2, 2816, 32000, max_position=32768),
+    "tiny8": ModelConfig("tiny8", 1024, 2, 16, 8, 2048, 2048, max_position=8192),      # 8 kv heads: shards over tp <= 8
 }
 
 _ALIASES = {
@@ -136,14 +137,24 @@ class LlamaModel:
 
     def __init__(self, cfg: ModelConfig, device: torch.device, num_blocks: int, block_size: int = 16,
                  seed: int = 0, weights_dir: Optional[Path] = None, max_position: Optional[int] = None,
-                 kv_dtype: torch.dtype = torch.bfloat16):
+                 kv_dtype: torch.dtype = torch.bfloat16, tp=None):
+        """`tp`: a b200attn.tp.TPGroup (or None).  With tp.size > 1 this instance holds rank tp.rank's shard: q / kv
+        heads and MLP columns split over the ranks (column-parallel wqkv / wgu, row-parallel wo / wdown), the
+        lm_head split over the vocabulary, embedding and norms replicated; the KV pool holds Hkv / tp heads."""
         if cfg.d != 128:
             raise ValueError(f"head_dim {cfg.d}: the attention kernels are built for 128")
         if device.type != "cuda":
             raise ValueError("LlamaModel needs a CUDA device (b200attn has no CPU path)")
         self.cfg, self.dev, self.bs, self.num_blocks = cfg, device, block_size, num_blocks
+        self.tp = tp if tp is not None and tp.size > 1 else None
+        self.tp_size, self.tp_rank = (tp.size, tp.rank) if self.tp is not None else (1, 0)
+        n = self.tp_size
+        if cfg.Hkv % n or cfg.Hq % n or cfg.inter % (8 * n):
+            raise ValueError(f"tensor_parallel_size {n} must divide Hkv={cfg.Hkv}, Hq={cfg.Hq} and inter={cfg.inter} / 8")
+        self.Hq, self.Hkv, self.inter = cfg.Hq // n, cfg.Hkv // n, cfg.inter // n          # this rank's share
+        self.vocab_parallel = n > 1 and cfg.vocab % (8 * n) == 0
         self.max_position = max_position or cfg.max_position
-        self.qkv_width = (cfg.Hq + 2 * cfg.Hkv) * cfg.d
+        self.qkv_width = (self.Hq + 2 * self.Hkv) * cfg.d
         self.w: Dict[str, torch.Tensor] = {}
         if weights_dir is not None and any(weights_dir.glob("*.safetensors")):
             self._load_hf(weights_dir)
@@ -151,7 +162,7 @@ class LlamaModel:
             self._random_init(seed)
         self.cos_sin = rope_table(self.max_position, cfg.d, cfg.rope_theta, cfg.rope_scaling, device)
         # KV pool: [layers, 2, num_blocks, Hkv, bs, d]; one (block, head) tile = bs x d contiguous ("HND")
-        self.kv = torch.zeros(cfg.layers, 2, num_blocks, cfg.Hkv, block_size, cfg.d, dtype=kv_dtype, device=device)
+        self.kv = torch.zeros(cfg.layers, 2, num_blocks, self.Hkv, block_size, cfg.d, dtype=kv_dtype, device=device)
         self.k_scale = self.v_scale = None
         if kv_dtype != torch.bfloat16:
             self.k_scale = torch.ones(1, dtype=torch.float32, device=device)
@@ -160,6 +171,29 @@ class LlamaModel:
         self._plans: Optional[list] = None      # per-layer b2_decode_plan handles (prepare_decode)
 
     # ------------------------------------------------------------------ weights
+    def _put(self, name: str, full: torch.Tensor) -> None:
+        """Store this rank's shard of the full tensor `name` (the whole tensor at tp = 1).  Shards are taken from the
+        full tensor, so every tp size holds exactly the weights of the tp = 1 model (same seed or same checkpoint)."""
+        n, r, c = self.tp_size, self.tp_rank, self.cfg
+        kind = name.rsplit(".", 1)[-1]
+        if n > 1:
+            d = c.d
+            if kind in ("wqkv", "bqkv"):
+                q, k, v = full.split([c.Hq * d, c.Hkv * d, c.Hkv * d], dim=0)
+                full = torch.cat([q[r * self.Hq * d:(r + 1) * self.Hq * d], k[r * self.Hkv * d:(r + 1) * self.Hkv * d],
+                                  v[r * self.Hkv * d:(r + 1) * self.Hkv * d]])
+            elif kind == "wo":
+                full = full[:, r * self.Hq * d:(r + 1) * self.Hq * d].contiguous()
+            elif kind == "wgu":
+                g, u = full.split([c.inter, c.inter], dim=0)
+                full = torch.cat([g[r * self.inter:(r + 1) * self.inter], u[r * self.inter:(r + 1) * self.inter]])
+            elif kind == "wdown":
+                full = full[:, r * self.inter:(r + 1) * self.inter].contiguous()
+            elif kind == "lm_head" and self.vocab_parallel:
+                vs = c.vocab // n
+                full = full[r * vs:(r + 1) * vs].clone()           # a copy: the full tensor can then be freed
+        self.w[name] = full
+
     def _random_init(self, seed: int) -> None:
         c, dev = self.cfg, self.dev
         g = torch.Generator(device=dev).manual_seed(seed)
@@ -167,19 +201,20 @@ class LlamaModel:
         def rnd(*shape, std=0.02):
             return (torch.randn(*shape, generator=g, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
 
-        w = self.w
-        w["embed"] = rnd(c.vocab, c.hidden)
+        put = self._put
+        put("embed", rnd(c.vocab, c.hidden))
+        full_qkv = (c.Hq + 2 * c.Hkv) * c.d
         for l in range(c.layers):
-            w[f"l{l}.ln1"] = torch.ones(c.hidden, dtype=torch.bfloat16, device=dev)
-            w[f"l{l}.wqkv"] = rnd(self.qkv_width, c.hidden)
+            put(f"l{l}.ln1", torch.ones(c.hidden, dtype=torch.bfloat16, device=dev))
+            put(f"l{l}.wqkv", rnd(full_qkv, c.hidden))
             if c.qkv_bias:
-                w[f"l{l}.bqkv"] = rnd(self.qkv_width)
-            w[f"l{l}.wo"] = rnd(c.hidden, c.Hq * c.d)
-            w[f"l{l}.ln2"] = torch.ones(c.hidden, dtype=torch.bfloat16, device=dev)
-            w[f"l{l}.wgu"] = rnd(2 * c.inter, c.hidden)
-            w[f"l{l}.wdown"] = rnd(c.hidden, c.inter)
-        w["norm"] = torch.ones(c.hidden, dtype=torch.bfloat16, device=dev)
-        w["lm_head"] = w["embed"] if c.tie_embeddings else rnd(c.vocab, c.hidden)
+                put(f"l{l}.bqkv", rnd(full_qkv))
+            put(f"l{l}.wo", rnd(c.hidden, c.Hq * c.d))
+            put(f"l{l}.ln2", torch.ones(c.hidden, dtype=torch.bfloat16, device=dev))
+            put(f"l{l}.wgu", rnd(2 * c.inter, c.hidden))
+            put(f"l{l}.wdown", rnd(c.hidden, c.inter))
+        put("norm", torch.ones(c.hidden, dtype=torch.bfloat16, device=dev))
+        put("lm_head", self.w["embed"] if c.tie_embeddings else rnd(c.vocab, c.hidden))
 
     def _load_hf(self, path: Path) -> None:
         from safetensors import safe_open
@@ -193,20 +228,20 @@ class LlamaModel:
         def get(name):
             return raw[name].to(torch.bfloat16).to(dev)
 
-        w = self.w
-        w["embed"] = get("model.embed_tokens.weight")
+        put = self._put
+        put("embed", get("model.embed_tokens.weight"))
         for l in range(c.layers):
             p = f"model.layers.{l}."
-            w[f"l{l}.ln1"] = get(p + "input_layernorm.weight")
-            w[f"l{l}.wqkv"] = torch.cat([get(p + f"self_attn.{x}_proj.weight") for x in "qkv"]).contiguous()
+            put(f"l{l}.ln1", get(p + "input_layernorm.weight"))
+            put(f"l{l}.wqkv", torch.cat([get(p + f"self_attn.{x}_proj.weight") for x in "qkv"]).contiguous())
             if c.qkv_bias:
-                w[f"l{l}.bqkv"] = torch.cat([get(p + f"self_attn.{x}_proj.bias") for x in "qkv"]).contiguous()
-            w[f"l{l}.wo"] = get(p + "self_attn.o_proj.weight")
-            w[f"l{l}.ln2"] = get(p + "post_attention_layernorm.weight")
-            w[f"l{l}.wgu"] = torch.cat([get(p + "mlp.gate_proj.weight"), get(p + "mlp.up_proj.weight")]).contiguous()
-            w[f"l{l}.wdown"] = get(p + "mlp.down_proj.weight")
-        w["norm"] = get("model.norm.weight")
-        w["lm_head"] = w["embed"] if c.tie_embeddings or "lm_head.weight" not in raw else get("lm_head.weight")
+                put(f"l{l}.bqkv", torch.cat([get(p + f"self_attn.{x}_proj.bias") for x in "qkv"]).contiguous())
+            put(f"l{l}.wo", get(p + "self_attn.o_proj.weight"))
+            put(f"l{l}.ln2", get(p + "post_attention_layernorm.weight"))
+            put(f"l{l}.wgu", torch.cat([get(p + "mlp.gate_proj.weight"), get(p + "mlp.up_proj.weight")]).contiguous())
+            put(f"l{l}.wdown", get(p + "mlp.down_proj.weight"))
+        put("norm", get("model.norm.weight"))
+        put("lm_head", self.w["embed"] if c.tie_embeddings or "lm_head.weight" not in raw else get("lm_head.weight"))
 
     def weight_bytes(self) -> int:
         seen, n = set(), 0
@@ -220,7 +255,7 @@ class LlamaModel:
     def decode_workspace(self, max_batch: int, max_nb: int) -> torch.Tensor:
         """The decode scratch, allocated ONCE for the largest batch (b2_paged_decode_workspace_bytes serves every batch
         size up to it).  Captured CUDA graphs hold its address, so it is never replaced: a larger request is a bug."""
-        need = max(ops.decode_workspace_bytes(max_batch, self.cfg.Hq, self.cfg.Hkv, self.cfg.d, self.bs, max_nb, 0), 256)
+        need = max(ops.decode_workspace_bytes(max_batch, self.Hq, self.Hkv, self.cfg.d, self.bs, max_nb, 0), 256)
         if self._ws is None:
             self._ws = torch.zeros(need, dtype=torch.uint8, device=self.dev)
         elif self._ws.numel() < need:
@@ -232,7 +267,7 @@ class LlamaModel:
         """One b2_decode_plan per layer over that layer's K/V pool, all sharing the one workspace (the layers run one
         after the other on one stream): the TMA descriptors are encoded here, not in every step."""
         ws = self.decode_workspace(max_batch, max_nb)
-        self._plans = [ops.DecodePlan(self.kv[l, 0], self.kv[l, 1], max_batch, self.cfg.Hq, max_nb,
+        self._plans = [ops.DecodePlan(self.kv[l, 0], self.kv[l, 1], max_batch, self.Hq, max_nb,
                                       k_scale=self.k_scale, v_scale=self.v_scale, workspace=ws)
                        for l in range(self.cfg.layers)]
         self._plan_shape = (max_batch, max_nb)
@@ -243,26 +278,29 @@ class LlamaModel:
         """tokens int64 [T] (rows [0, n_decode) = one new token per running sequence, the rest = prompt chunks),
         positions int32 [T], slots int64 [T].  Returns bf16 logits [len(sample_rows) or T, vocab]."""
         c, w = self.cfg, self.w
+        Hq, Hkv = self.Hq, self.Hkv                                      # this rank's heads (all of them at tp = 1)
         T = tokens.shape[0]
+        # tensor parallel: partial sums of up to tp.max_rows rows take the fused one-shot NVLink exchange (decode steps,
+        # small mixed steps); larger prompt chunks are bandwidth-bound and go through NCCL + the plain fused norm
+        one_shot = self.tp is not None and T <= self.tp.max_rows
         resid = w["embed"].index_select(0, tokens)                       # [T, hidden]  (residual stream, bf16)
         x = ops.rms_norm(resid, w["l0.ln1"], c.eps)
-        attn = torch.empty(T, c.Hq, c.d, dtype=torch.bfloat16, device=self.dev)
+        attn = torch.empty(T, Hq, c.d, dtype=torch.bfloat16, device=self.dev)
         fp8_plan = None
         if self.k_scale is not None and prefill is not None and prefill.total_tokens:
             kv_lens = prefill.kv_lens_host
             if kv_lens is None:      # one device read; the engine passes the scheduler's host copy instead
                 kv_lens = (prefill.ctx_start.long() + (prefill.cu_q[1:] - prefill.cu_q[:-1]).long()).cpu().tolist()
             src, sbt = ops.fp8_prefill_plan(prefill.block_tables, kv_lens, self.bs)
-            shape = (src.numel(), c.Hkv, self.bs, c.d)
+            shape = (src.numel(), Hkv, self.bs, c.d)
             fp8_plan = (src, sbt, torch.empty(shape, dtype=torch.bfloat16, device=self.dev),
                         torch.empty(shape, dtype=torch.bfloat16, device=self.dev))
+        part = None
         for l in range(c.layers):
-            if l > 0:
-                x = ops.rms_norm(x, w[f"l{l}.ln1"], c.eps, residual=resid, out=x)
             qkv = torch.nn.functional.linear(x, w[f"l{l}.wqkv"], w.get(f"l{l}.bqkv"))
             kc, vc = self.kv[l, 0], self.kv[l, 1]
-            ops.rope_and_cache(qkv, positions, self.cos_sin, kc, vc, slots, c.Hq, self.k_scale, self.v_scale)
-            q = qkv.view(T, c.Hq + 2 * c.Hkv, c.d)[:, : c.Hq]
+            ops.rope_and_cache(qkv, positions, self.cos_sin, kc, vc, slots, Hq, self.k_scale, self.v_scale)
+            q = qkv.view(T, Hq + 2 * Hkv, c.d)[:, :Hq]
             if n_decode:
                 if self._plans is not None and n_decode <= self._plan_shape[0] \
                         and dec_block_tables.shape[1] == self._plan_shape[1]:
@@ -282,13 +320,44 @@ class LlamaModel:
                     ops.prefill_attention(q[n_decode:], fp8_plan[2], fp8_plan[3], fp8_plan[1], prefill.cu_q,
                                           prefill.ctx_start, total_tokens=prefill.total_tokens, out=attn[n_decode:],
                                           k_scale=self.k_scale, v_scale=self.v_scale)
-            o = torch.nn.functional.linear(attn.view(T, c.Hq * c.d), w[f"l{l}.wo"])
-            x = ops.rms_norm(o, w[f"l{l}.ln2"], c.eps, residual=resid, out=o)
+            o = self._row_parallel(attn.view(T, Hq * c.d), w[f"l{l}.wo"], 0, one_shot)
+            x = self._reduce_norm(o, 0, one_shot, w[f"l{l}.ln2"], resid)
             gu = torch.nn.functional.linear(x, w[f"l{l}.wgu"])
             act = ops.silu_and_mul(gu)
-            x = torch.nn.functional.linear(act, w[f"l{l}.wdown"])
-        if sample_rows is not None:
-            x = x.index_select(0, sample_rows)
-            resid = resid.index_select(0, sample_rows)
-        x = ops.rms_norm(x, w["norm"], c.eps, residual=resid, out=x)
-        return torch.nn.functional.linear(x, w["lm_head"])
+            part = self._row_parallel(act, w[f"l{l}.wdown"], 1, one_shot)
+            if l + 1 < c.layers:
+                x = self._reduce_norm(part, 1, one_shot, w[f"l{l + 1}.ln1"], resid)
+        # final norm over the rows that are sampled.  One-shot path: reduce every row (T is small), then pick -- the
+        # partial-sum slots must strictly alternate; NCCL path: pick first, then reduce only those rows
+        if one_shot:
+            x = self._reduce_norm(part, 1, True, w["norm"], resid)
+            if sample_rows is not None:
+                x = x.index_select(0, sample_rows)
+        else:
+            if sample_rows is not None:
+                part = part.index_select(0, sample_rows)
+                resid = resid.index_select(0, sample_rows)
+            x = self._reduce_norm(part, 1, False, w["norm"], resid)
+        logits = torch.nn.functional.linear(x, w["lm_head"])
+        if self.vocab_parallel:
+            logits = self.tp.allgather_cols(logits)       # [rows, vocab] view of the peer-written buffer (valid until the next gather)
+        return logits
+
+    def _row_parallel(self, inp: torch.Tensor, weight: torch.Tensor, slot: int, one_shot: bool) -> torch.Tensor:
+        """Row-parallel projection (o_proj / down_proj): this rank's PARTIAL [T, hidden] sum.  On the one-shot path the
+        GEMM writes straight into the peer-mapped partial-sum buffer `slot`."""
+        if one_shot:
+            out = self.tp.inputs[slot][: inp.shape[0]]
+            torch.mm(inp, weight.t(), out=out)
+            return out
+        return torch.nn.functional.linear(inp, weight)
+
+    def _reduce_norm(self, part: torch.Tensor, slot: int, one_shot: bool, weight: torch.Tensor,
+                     resid: torch.Tensor) -> torch.Tensor:
+        """resid += sum over ranks of `part`; returns RMSNorm(resid) * weight."""
+        if self.tp is None:
+            return ops.rms_norm(part, weight, self.cfg.eps, residual=resid, out=part)
+        if one_shot:
+            return self.tp.allreduce_rms_norm(slot, part.shape[0], weight, resid, self.cfg.eps)
+        self.tp.all_reduce_nccl(part)
+        return ops.rms_norm(part, weight, self.cfg.eps, residual=resid, out=part)

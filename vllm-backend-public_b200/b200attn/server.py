@@ -44,6 +44,7 @@ class EngineRunner:
         self._stop = False
         self._thread = threading.Thread(target=self._main, name="b200attn-engine", daemon=True)
         self.t_start = time.time()
+        self.workers: list = []                  # child processes of ranks 1..tp-1
 
     def start(self) -> None:
         self._thread.start()
@@ -52,6 +53,17 @@ class EngineRunner:
         self._stop = True
         self._wake.set()
         self._thread.join(timeout=10)
+        if self.workers:
+            try:
+                if self.engine is not None and self.failed is None:
+                    self.engine.shutdown_workers()
+            except Exception:
+                pass
+            for p in self.workers:
+                try:
+                    p.wait(timeout=10)
+                except Exception:
+                    p.kill()
 
     def _main(self) -> None:
         try:
@@ -64,8 +76,22 @@ class EngineRunner:
             kw = self.args.engine_kwargs()
             wdir = Path(self.args.model_name) if Path(self.args.model_name).is_dir() else None
             self.tokenizer = load_tokenizer(self.args.model_name, cfg.vocab, self.tokenizer_path)
+            group = None
+            tpn = self.args.tensor_parallel_size
+            if tpn > 1:
+                # --tensor-parallel-size N: this process is rank 0 (GPU 0, the HTTP front end, the request queue);
+                # ranks 1..N-1 are child processes on GPUs 1..N-1 mirroring every step (b200attn.tp)
+                from . import tp
+                if torch.cuda.device_count() < tpn:
+                    raise RuntimeError(f"--tensor-parallel-size {tpn} needs {tpn} GPUs, {torch.cuda.device_count()} visible")
+                port = tp.free_port()
+                spec = {"model": self.args.model_name, "engine": dict(kw, eos_token_id=self.tokenizer.eos_token_id)}
+                self.workers = tp.launch_workers(tpn, spec, port)
+                torch.cuda.set_device(0)
+                tp.init_distributed(0, tpn, torch.device("cuda", 0), master_port=port)
+                group = tp.TPGroup(torch.device("cuda", 0))
             self.engine = LLMEngine(cfg, torch.device("cuda", 0), weights_dir=wdir,
-                                    eos_token_id=self.tokenizer.eos_token_id, **kw)
+                                    eos_token_id=self.tokenizer.eos_token_id, tp=group, **kw)
             n = self.engine.capture_all()
             print(f"[b200attn] {cfg.name}: {self.engine.model.weight_bytes() / 2**30:.1f} GiB weights, "
                   f"{self.engine.num_blocks} KV blocks x {self.engine.block_size} tokens, max_model_len "
@@ -80,6 +106,14 @@ class EngineRunner:
             return
         eng = self.engine
         while not self._stop:
+            dead = [p.pid for p in self.workers if p.poll() is not None]
+            if dead:                                              # a tensor-parallel rank died: the engine cannot step
+                self.failed = f"tensor-parallel worker process(es) {dead} exited"
+                for r in list(eng.requests.values()):
+                    r.finished, r.finish_reason = True, "error"
+                    if r.on_token:
+                        r.on_token(r, None)
+                return
             if eng.has_work():
                 try:
                     eng.step()
