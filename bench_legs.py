@@ -237,6 +237,28 @@ def tp_comm_leg(dev, group, T: int = 64, H: int = 4096, iters: int = 200) -> dic
             torch.cuda.synchronize()
             res[name] = round(e0.elapsed_time(e1) / iters * 1e3, 2)
             x.normal_()
+        # the same loops replayed as ONE CUDA graph: device time per exchange without the host launch cost
+        # (how the decode step runs them)
+        st = torch.cuda.Stream(dev)
+        for name, fn in (("fused_in_graph_us", fused), ("nccl_in_graph_us", nccl)):
+            try:
+                group.barrier()
+                with torch.cuda.stream(st):
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=st):
+                        fn()
+                    g.replay()
+                    st.synchronize()
+                    group.barrier()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(st)
+                    g.replay()
+                    e1.record(st)
+                    st.synchronize()
+                res[name] = round(e0.elapsed_time(e1) / iters * 1e3, 2)
+                del g
+            except Exception as e:                                            # noqa: BLE001
+                res[name] = f"{type(e).__name__}: {e}"[:200]
         group.barrier()
         group.close()
         res.update(T=T, H=H, tp=group.size, message_bytes=T * H * 2, iters=iters,
