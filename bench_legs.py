@@ -221,13 +221,18 @@ def tp_comm_leg(dev, group, T: int = 64, H: int = 4096, iters: int = 200) -> dic
             for i in range(iters):
                 group.allreduce_rms_norm(i & 1, T, w, resid, 1e-5, out=out)
 
+        def push():
+            for i in range(iters):
+                group.push_allreduce_rms_norm(x, w, resid, 1e-5, out=out)
+
         def nccl():
             for _ in range(iters):
                 group.all_reduce_nccl(x)
                 ops.rms_norm(x, w, 1e-5, residual=resid, out=out)
 
         res = {}
-        for name, fn in (("fused_nvlink_allreduce_rmsnorm_us", fused), ("nccl_allreduce_plus_rmsnorm_us", nccl)):
+        for name, fn in (("push_allreduce_rmsnorm_us", push), ("pull_allreduce_rmsnorm_us", fused),
+                         ("nccl_allreduce_plus_rmsnorm_us", nccl)):
             fn()
             group.barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -240,7 +245,7 @@ def tp_comm_leg(dev, group, T: int = 64, H: int = 4096, iters: int = 200) -> dic
         # the same loops replayed as ONE CUDA graph: device time per exchange without the host launch cost
         # (how the decode step runs them)
         st = torch.cuda.Stream(dev)
-        for name, fn in (("fused_in_graph_us", fused), ("nccl_in_graph_us", nccl)):
+        for name, fn in (("push_in_graph_us", push), ("pull_in_graph_us", fused), ("nccl_in_graph_us", nccl)):
             try:
                 group.barrier()
                 with torch.cuda.stream(st):

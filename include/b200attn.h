@@ -336,6 +336,10 @@ B2_API int64_t b2_sched_generated(const b2_scheduler* s, int64_t req_id);   /* t
  *     out = weight ? bf16(weight * h * rsqrt(mean(h^2) + eps)) : h.  The sum runs in rank order in fp32, so every
  *     rank computes the same bits.  Every rank must call it with the same (slot, T) in the same order, and
  *     alternate the slots (that is what makes buffer reuse safe, see comm.cu).
+ * b2_comm_push_allreduce_rms_norm   the same result by the PUSH protocol (the default in b200attn.tp): `partial`
+ *     (bf16 [T, H], row stride given) is ordinary device memory; every rank stores its rows into landing buffers on
+ *     every peer, where a slot still holding the sentinel (bf16 -0.0 in all lanes) has not arrived -- no barrier, one
+ *     NVLink crossing on the critical path.  A partial sum equal to -0.0 travels as +0.0.
  * b2_comm_allgather_cols   gathered[t][rank*cols + c] = local[t][c] on every rank (b2_comm_gathered: bf16
  *     [gather_rows, tp*cols]); the vocab-parallel lm_head.
  * Both only enqueue on `stream`; they are CUDA-graph capturable (the barrier epoch is device state).  A peer that
@@ -347,7 +351,7 @@ B2_API int b2_comm_alloc(size_t bytes, void** ptr, void* handle /* B2_COMM_HANDL
 B2_API int b2_comm_open(const void* handle, void** ptr);
 B2_API int b2_comm_close(void* ptr);
 B2_API int b2_comm_free(void* ptr);
-B2_API size_t b2_comm_region_bytes(int max_rows, int H, int gather_rows, int gather_cols);
+B2_API size_t b2_comm_region_bytes(int tp, int max_rows, int H, int gather_rows, int gather_cols);
 B2_API void* b2_comm_create(int rank, int tp, void* const* regions, size_t region_bytes, int max_rows, int H,
                             int gather_rows, int gather_cols);
 B2_API void b2_comm_destroy(void* comm);
@@ -355,6 +359,9 @@ B2_API void* b2_comm_input(void* comm, int slot);
 B2_API void* b2_comm_gathered(void* comm);
 B2_API int b2_comm_allreduce_rms_norm(void* comm, int slot, void* out, void* residual, const void* weight, int T,
                                       int64_t out_stride, int64_t res_stride, float eps, void* stream);
+B2_API int b2_comm_push_allreduce_rms_norm(void* comm, const void* partial, int64_t partial_stride, void* out,
+                                           void* residual, const void* weight, int T, int64_t out_stride,
+                                           int64_t res_stride, float eps, void* stream);
 B2_API int b2_comm_allgather_cols(void* comm, const void* local, int64_t local_stride, int T, int cols, void* stream);
 
 #ifdef __cplusplus

@@ -28,7 +28,7 @@ class Regions:
         from b200attn.tp import _device_view
         self.lib, self.n, self.H, self.max_rows = _lib.load(), n, H, max_rows
         lib = self.lib
-        nbytes = int(lib.b2_comm_region_bytes(max_rows, H, grows, gcols))
+        nbytes = int(lib.b2_comm_region_bytes(n, max_rows, H, grows, gcols))
         self.ptrs = []
         for _ in range(n):
             p, h = C.c_void_p(), C.create_string_buffer(64)
@@ -52,6 +52,14 @@ class Regions:
                                                        None if resid is None else resid.data_ptr(),
                                                        None if w is None else w.data_ptr(), T, self.H, self.H, eps,
                                                        stream.cuda_stream))
+
+    def push(self, r, part, out, resid, w, eps, stream):
+        from b200attn import _lib
+        T = part.shape[0]
+        _lib.check(self.lib.b2_comm_push_allreduce_rms_norm(self.comms[r], part.data_ptr(), part.stride(0), out.data_ptr(),
+                                                            None if resid is None else resid.data_ptr(),
+                                                            None if w is None else w.data_ptr(), T, self.H, self.H, eps,
+                                                            stream.cuda_stream))
 
     def allgather(self, r, local, stream):
         from b200attn import _lib
@@ -87,6 +95,10 @@ def test_comm_tp1_equals_rms_norm(cuda, H):
             # the norm: the two kernels sum the squares in a different thread order -> at most one bf16 ulp apart
             assert bool(((out.float() - ref.float()).abs() <= 2.0 ** -7 * ref.float().abs()).all())
             assert (out.view(torch.int16) != ref.view(torch.int16)).float().mean() < 0.01
+            r3, out3 = resid.clone(), torch.empty_like(x)
+            R.push(0, x, out3, r3, w, 1e-5, st)                                      # push variant: same arithmetic
+            assert torch.equal(out3.view(torch.int16), out.view(torch.int16))
+            assert torch.equal(r3.view(torch.int16), r2.view(torch.int16))
         # no weight: plain sum (+ residual); no residual: plain norm
         out = torch.empty_like(x)
         R.allreduce(0, 1, out, None, None, T, 1e-5, st)
@@ -107,17 +119,22 @@ def _two_rank_protocol():
     s = [torch.cuda.Stream(), torch.cuda.Stream()]
     w = torch.randn(H, device="cuda").to(torch.bfloat16)
     worst = 0.0
-    for it in range(40):
-        slot = it & 1
+    for it in range(60):
+        slot = (it // 3) & 1
         parts = [torch.randn(T, H, device="cuda").to(torch.bfloat16) for _ in range(2)]
         resid0 = torch.randn(T, H, device="cuda").to(torch.bfloat16)
         torch.cuda.synchronize()
         outs, resids = [], []
+        if it % 7 == 3:
+            parts[0][2, 5:9] = -0.0                      # the sentinel value itself must survive the push protocol
         for r in range(2):
             with torch.cuda.stream(s[r]):
-                R.inputs[r][slot][:T].copy_(parts[r])
                 out, rs = torch.empty(T, H, dtype=torch.bfloat16, device="cuda"), resid0.clone()
-                R.allreduce(r, slot, out, rs, w, T, 1e-5, s[r])
+                if it % 3 == 2:                          # every third exchange through the pull variant
+                    R.inputs[r][slot][:T].copy_(parts[r])
+                    R.allreduce(r, slot, out, rs, w, T, 1e-5, s[r])
+                else:
+                    R.push(r, parts[r], out, rs, w, 1e-5, s[r])
                 outs.append(out)
                 resids.append(rs)
         torch.cuda.synchronize()

@@ -77,12 +77,13 @@ SIGNATURES = {
     "b2_comm_open": (i32, [vp, vp]),
     "b2_comm_close": (i32, [vp]),
     "b2_comm_free": (i32, [vp]),
-    "b2_comm_region_bytes": (sz, [i32, i32, i32, i32]),
+    "b2_comm_region_bytes": (sz, [i32, i32, i32, i32, i32]),
     "b2_comm_create": (vp, [i32, i32, vp, sz, i32, i32, i32, i32]),
     "b2_comm_destroy": (None, [vp]),
     "b2_comm_input": (vp, [vp, i32]),
     "b2_comm_gathered": (vp, [vp]),
     "b2_comm_allreduce_rms_norm": (i32, [vp, i32, vp, vp, vp, i32, i64, i64, f32, vp]),
+    "b2_comm_push_allreduce_rms_norm": (i32, [vp, vp, i64, vp, vp, vp, i32, i64, i64, f32, vp]),
     "b2_comm_allgather_cols": (i32, [vp, vp, i64, i32, i32, vp]),
 }
 

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import json
 import math
+import os
 from dataclasses import dataclass, field
 from pathlib import Path
 from typing import Dict, List, Optional
@@ -153,6 +154,7 @@ class LlamaModel:
             raise ValueError(f"tensor_parallel_size {n} must divide Hkv={cfg.Hkv}, Hq={cfg.Hq} and inter={cfg.inter} / 8")
         self.Hq, self.Hkv, self.inter = cfg.Hq // n, cfg.Hkv // n, cfg.inter // n          # this rank's share
         self.vocab_parallel = n > 1 and cfg.vocab % (8 * n) == 0
+        self._exchange = os.environ.get("B2_TP_EXCHANGE", "push")         # push | pull | nccl (A/B knob)
         self.max_position = max_position or cfg.max_position
         self.qkv_width = (self.Hq + 2 * self.Hkv) * cfg.d
         self.w: Dict[str, torch.Tensor] = {}
@@ -280,9 +282,15 @@ class LlamaModel:
         c, w = self.cfg, self.w
         Hq, Hkv = self.Hq, self.Hkv                                      # this rank's heads (all of them at tp = 1)
         T = tokens.shape[0]
-        # tensor parallel: partial sums of up to tp.max_rows rows take the fused one-shot NVLink exchange (decode steps,
-        # small mixed steps); larger prompt chunks are bandwidth-bound and go through NCCL + the plain fused norm
-        one_shot = self.tp is not None and T <= self.tp.max_rows
+        # tensor parallel: partial sums of up to 256 rows (decode steps, small mixed steps) take the fused one-shot NVLink
+        # exchange -- "push" (no barrier) by default, "pull" (flag barrier + peer loads) up to tp.max_rows rows or when
+        # B2_TP_EXCHANGE=pull; larger prompt chunks are bandwidth-bound and go through NCCL + the plain fused norm
+        one_shot = None
+        if self.tp is not None and self._exchange != "nccl":
+            if T <= self.tp.PUSH_MAX_ROWS and self._exchange == "push":
+                one_shot = "push"
+            elif T <= self.tp.max_rows:
+                one_shot = "pull"
         resid = w["embed"].index_select(0, tokens)                       # [T, hidden]  (residual stream, bf16)
         x = ops.rms_norm(resid, w["l0.ln1"], c.eps)
         attn = torch.empty(T, Hq, c.d, dtype=torch.bfloat16, device=self.dev)
@@ -330,34 +338,36 @@ class LlamaModel:
         # final norm over the rows that are sampled.  One-shot path: reduce every row (T is small), then pick -- the
         # partial-sum slots must strictly alternate; NCCL path: pick first, then reduce only those rows
         if one_shot:
-            x = self._reduce_norm(part, 1, True, w["norm"], resid)
+            x = self._reduce_norm(part, 1, one_shot, w["norm"], resid)
             if sample_rows is not None:
                 x = x.index_select(0, sample_rows)
         else:
             if sample_rows is not None:
                 part = part.index_select(0, sample_rows)
                 resid = resid.index_select(0, sample_rows)
-            x = self._reduce_norm(part, 1, False, w["norm"], resid)
+            x = self._reduce_norm(part, 1, None, w["norm"], resid)
         logits = torch.nn.functional.linear(x, w["lm_head"])
         if self.vocab_parallel:
             logits = self.tp.allgather_cols(logits)       # [rows, vocab] view of the peer-written buffer (valid until the next gather)
         return logits
 
-    def _row_parallel(self, inp: torch.Tensor, weight: torch.Tensor, slot: int, one_shot: bool) -> torch.Tensor:
-        """Row-parallel projection (o_proj / down_proj): this rank's PARTIAL [T, hidden] sum.  On the one-shot path the
+    def _row_parallel(self, inp: torch.Tensor, weight: torch.Tensor, slot: int, one_shot) -> torch.Tensor:
+        """Row-parallel projection (o_proj / down_proj): this rank's PARTIAL [T, hidden] sum.  For the pull exchange the
         GEMM writes straight into the peer-mapped partial-sum buffer `slot`."""
-        if one_shot:
+        if one_shot == "pull":
             out = self.tp.inputs[slot][: inp.shape[0]]
             torch.mm(inp, weight.t(), out=out)
             return out
         return torch.nn.functional.linear(inp, weight)
 
-    def _reduce_norm(self, part: torch.Tensor, slot: int, one_shot: bool, weight: torch.Tensor,
+    def _reduce_norm(self, part: torch.Tensor, slot: int, one_shot, weight: torch.Tensor,
                      resid: torch.Tensor) -> torch.Tensor:
         """resid += sum over ranks of `part`; returns RMSNorm(resid) * weight."""
         if self.tp is None:
             return ops.rms_norm(part, weight, self.cfg.eps, residual=resid, out=part)
-        if one_shot:
+        if one_shot == "push":
+            return self.tp.push_allreduce_rms_norm(part, weight, resid, self.cfg.eps)
+        if one_shot == "pull":
             return self.tp.allreduce_rms_norm(slot, part.shape[0], weight, resid, self.cfg.eps)
         self.tp.all_reduce_nccl(part)
         return ops.rms_norm(part, weight, self.cfg.eps, residual=resid, out=part)

@@ -169,7 +169,7 @@ class TPGroup:
         torch.cuda.set_device(self.dev)
         if self._comm:                               # a second engine on the same group: release the old regions first
             self.close()
-        nbytes = int(lib.b2_comm_region_bytes(max_rows, hidden, gather_rows, gather_cols))
+        nbytes = int(lib.b2_comm_region_bytes(self.size, max_rows, hidden, gather_rows, gather_cols))
         if nbytes == 0:
             raise ValueError("comm region: bad sizes")
         ptr = C.c_void_p()
@@ -232,6 +232,34 @@ class TPGroup:
             self._comm, slot, out.data_ptr(), None if residual is None else residual.data_ptr(),
             None if weight is None else weight.data_ptr(), T, out.stride(0) if T > 1 else self.hidden, rs, float(eps),
             torch.cuda.current_stream(self.dev).cuda_stream))
+        return out
+
+    PUSH_MAX_ROWS = 256          # csrc/comm.cu: every CTA of a push exchange must be resident
+
+    def push_allreduce_rms_norm(self, part: torch.Tensor, weight: Optional[torch.Tensor],
+                                residual: Optional[torch.Tensor], eps: float,
+                                out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Same result as allreduce_rms_norm, by the push protocol (b2_comm_push_allreduce_rms_norm): `part` is this
+        rank's partial sum, bf16 [T, hidden] in ordinary device memory, T <= PUSH_MAX_ROWS."""
+        T = part.shape[0]
+        if part.dtype != torch.bfloat16 or part.shape != (T, self.hidden) or part.stride(1) != 1:
+            raise ValueError(f"part must be bf16 [T, {self.hidden}]")
+        if out is None:
+            out = torch.empty(T, self.hidden, dtype=torch.bfloat16, device=self.dev)
+        if out.dtype != torch.bfloat16 or out.shape != (T, self.hidden) or out.stride(1) != 1:
+            raise ValueError(f"out must be bf16 [{T}, {self.hidden}]")
+        rs = 0
+        if residual is not None:
+            if residual.dtype != torch.bfloat16 or residual.shape != (T, self.hidden) or residual.stride(1) != 1:
+                raise ValueError(f"residual must be bf16 [{T}, {self.hidden}]")
+            rs = residual.stride(0) if T > 1 else self.hidden
+        if weight is not None and (weight.dtype != torch.bfloat16 or weight.shape != (self.hidden,)
+                                   or not weight.is_contiguous()):
+            raise ValueError(f"weight must be a contiguous bf16 [{self.hidden}]")
+        _lib.check(self._lib.b2_comm_push_allreduce_rms_norm(
+            self._comm, part.data_ptr(), part.stride(0) if T > 1 else self.hidden, out.data_ptr(),
+            None if residual is None else residual.data_ptr(), None if weight is None else weight.data_ptr(), T,
+            out.stride(0) if T > 1 else self.hidden, rs, float(eps), torch.cuda.current_stream(self.dev).cuda_stream))
         return out
 
     def allgather_cols(self, local: torch.Tensor) -> torch.Tensor:

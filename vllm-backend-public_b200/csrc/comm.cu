@@ -34,11 +34,13 @@ namespace {
 
 constexpr int MAX_TP = B2_COMM_MAX_RANKS;
 constexpr size_t CTRL_BYTES = 4096;
+constexpr int PUSH_MAX_ROWS = 256;   // <= 2 CTAs x 148 SMs (see push_allreduce_rms_norm_kernel)
 
 struct Ctrl {                       // first CTRL_BYTES of every rank's region
     uint32_t epoch;                 // barriers this rank has completed (only this rank's kernels write it)
     uint32_t done;                  // CTAs of the running kernel that have finished
-    uint32_t pad[30];
+    uint32_t lam;                   // push exchanges this rank has completed (selects the landing buffer, mod 3)
+    uint32_t pad[29];
     uint32_t flag[MAX_TP][32];      // flag[src][0] = last epoch rank `src` has reached (one 128-byte line per source)
 };
 static_assert(sizeof(Ctrl) <= CTRL_BYTES, "control block");
@@ -49,7 +51,7 @@ struct Peers {
 
 struct Comm {
     int rank, tp, max_rows, H, gather_rows, gather_cols;
-    size_t region_bytes, off_in[2], off_gather;
+    size_t region_bytes, off_in[2], off_gather, off_lam, lam_src_bytes, lam_buf_bytes;
     Peers peers;
 };
 
@@ -263,6 +265,199 @@ allgather_cols_kernel(const Peers peers, int rank, size_t gather_off, const __nv
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// PUSH variant of the same exchange (the default): no barrier, no flag, one NVLink crossing on the critical path.
+// Every rank stores its partial row vectors straight into a landing buffer on every peer; a landing slot that still
+// holds the sentinel (bf16 -0.0 in every lane) has not arrived yet, so the consumer polls the very 16 bytes it needs
+// ("Lamport" style: the data is its own flag).  A partial sum that really is -0.0 is sent as +0.0 -- the same value.
+//   landing area of rank d: lam[3][TP src][max_rows][H] bf16; call k (device counter, equal on all ranks) uses
+//   buffer k % 3.  A thread re-arms exactly the slots it consumed (stores the sentinel back) right after reading
+//   them.  Reuse is safe: a peer can run at most one call ahead (it cannot finish call k+1 without this rank's
+//   call-k+1 data), so buffer k % 3 is next written in call k+3, long after this rank's call k has completed.
+// Validity is checked on all 8 lanes of a vector, so no store atomicity beyond 2 bytes is assumed.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool has_sentinel(const int4& v) {
+    const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+    bool s = false;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s |= ((w[i] & 0xffffu) == 0x8000u) | ((w[i] >> 16) == 0x8000u);
+    return s;
+}
+__device__ __forceinline__ int4 no_neg_zero(int4 v) {
+    uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if ((w[i] & 0xffffu) == 0x8000u) w[i] &= 0xffff0000u;
+        if ((w[i] >> 16) == 0x8000u) w[i] &= 0x0000ffffu;
+    }
+    return make_int4((int)w[0], (int)w[1], (int)w[2], (int)w[3]);
+}
+__device__ __forceinline__ int4 ld_volatile_16(const void* p) {
+    int4 r;
+    asm volatile("ld.volatile.global.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_volatile_16(void* p, const int4& v) {
+    asm volatile("st.volatile.global.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+
+__global__ void fill_u32_kernel(uint32_t* p, size_t n, uint32_t v) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+template <int TP, int VPT>
+__global__ void __launch_bounds__(512, 2)      // two CTAs per SM: all PUSH_MAX_ROWS CTAs of a launch are resident, so
+push_allreduce_rms_norm_kernel(                // no CTA can spin for data that a not-yet-scheduled peer CTA must push
+const Peers peers, int rank, size_t lam_off, size_t lam_src_bytes, size_t lam_buf_bytes,
+                               const __nv_bfloat16* __restrict__ partial, int64_t partial_stride,
+                               __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ residual,
+                               const __nv_bfloat16* __restrict__ weight, int H, int64_t out_stride, int64_t res_stride,
+                               float eps) {
+    char* mine = peer_base<TP>(peers, rank);
+    Ctrl* me = reinterpret_cast<Ctrl*>(mine);
+    __shared__ uint32_t s_lam;
+    __shared__ float red[32];
+    const int row = blockIdx.x;
+    const int nvec = H >> 3;
+
+    // this rank's partial row (written by the previous kernel on this stream), residual row and norm weight
+    int4 xv[VPT], rv[VPT], wv[VPT];
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = threadIdx.x + k * blockDim.x;
+        xv[k] = rv[k] = wv[k] = make_int4(0, 0, 0, 0);
+        if (v < nvec) {
+            xv[k] = *reinterpret_cast<const int4*>(partial + row * partial_stride + v * 8);
+            if (residual) rv[k] = *reinterpret_cast<const int4*>(residual + row * res_stride + v * 8);
+            if (weight) wv[k] = *reinterpret_cast<const int4*>(weight + v * 8);
+        }
+    }
+    if (threadIdx.x == 0) s_lam = ld_volatile(&me->lam);
+    __syncthreads();
+    const uint32_t call = s_lam;
+    const size_t buf_off = lam_off + (size_t)(call % 3u) * lam_buf_bytes;
+
+    // push: one 16-byte store per peer and vector, into the slot [buffer][src = rank][row][v] of every peer
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = threadIdx.x + k * blockDim.x;
+        if (v < nvec) {
+            xv[k] = no_neg_zero(xv[k]);
+            const size_t off = buf_off + (size_t)rank * lam_src_bytes + ((size_t)row * H + (size_t)v * 8) * sizeof(__nv_bfloat16);
+#pragma unroll
+            for (int p = 1; p < TP; ++p) {                         // start with the next rank: spreads the switch ports
+                const int dst = (rank + p) % TP;
+                st_volatile_16(peer_base<TP>(peers, dst) + off, xv[k]);
+            }
+        }
+    }
+
+    float h[VPT][8];
+    float ss = 0.f;
+    const int4 sentinel = make_int4((int)0x80008000u, (int)0x80008000u, (int)0x80008000u, (int)0x80008000u);
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+        const int v = threadIdx.x + k * blockDim.x;
+        if (v < nvec) {
+            const size_t off = buf_off + ((size_t)row * H + (size_t)v * 8) * sizeof(__nv_bfloat16);
+            int4 pv[TP];
+            uint32_t pending = 0;
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {
+                if (p == rank) { pv[p] = xv[k]; continue; }
+                pv[p] = ld_volatile_16(mine + off + (size_t)p * lam_src_bytes);
+                pending |= has_sentinel(pv[p]) ? (1u << p) : 0u;
+            }
+            if (pending) {
+                const uint64_t t0 = globaltimer_ns();
+                while (pending) {
+#pragma unroll
+                    for (int p = 0; p < TP; ++p) {
+                        if (pending & (1u << p)) {
+                            pv[p] = ld_volatile_16(mine + off + (size_t)p * lam_src_bytes);
+                            if (!has_sentinel(pv[p])) pending &= ~(1u << p);
+                        }
+                    }
+                    if (pending && globaltimer_ns() - t0 > 10000000000ull) __trap();
+                }
+            }
+#pragma unroll
+            for (int p = 0; p < TP; ++p)                            // re-arm the consumed slots for call k + 3
+                if (p != rank) st_volatile_16(mine + off + (size_t)p * lam_src_bytes, sentinel);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) h[k][i] = 0.f;
+#pragma unroll
+            for (int p = 0; p < TP; ++p) {                          // rank order: same bits on every rank
+                float f[8];
+                unpack8(pv[p], f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) h[k][i] += f[i];
+            }
+            if (residual) {
+                float r[8];
+                unpack8(rv[k], r);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) h[k][i] += r[i];
+            }
+            const int4 packed = pack8(h[k]);
+            if (residual) *reinterpret_cast<int4*>(residual + row * res_stride + v * 8) = packed;
+            if (!weight) *reinterpret_cast<int4*>(out + row * out_stride + v * 8) = packed;
+            unpack8(packed, h[k]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ss += h[k][i] * h[k][i];
+        }
+    }
+    if (weight) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+        __syncthreads();
+        float tot = 0.f;
+        const int nw = (blockDim.x + 31) >> 5;
+        for (int i = 0; i < nw; ++i) tot += red[i];
+        const float inv = rsqrtf(tot / (float)H + eps);
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+            const int v = threadIdx.x + k * blockDim.x;
+            if (v < nvec) {
+                float w[8], o[8];
+                unpack8(wv[k], w);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = w[i] * (h[k][i] * inv);
+                *reinterpret_cast<int4*>(out + row * out_stride + v * 8) = pack8(o);
+            }
+        }
+    }
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&me->done, 1u) == gridDim.x - 1) {
+            me->done = 0;
+            me->lam = call + 1;
+            __threadfence();
+        }
+    }
+}
+
+template <int TP>
+void launch_push(const Comm* c, const __nv_bfloat16* partial, int64_t partial_stride, __nv_bfloat16* out,
+                 __nv_bfloat16* residual, const __nv_bfloat16* weight, int T, int64_t out_stride, int64_t res_stride,
+                 float eps, cudaStream_t st) {
+    const int nvec = c->H / 8;
+#define B2_PUSH(VPT, THREADS)                                                                                         \
+    push_allreduce_rms_norm_kernel<TP, VPT><<<T, THREADS, 0, st>>>(c->peers, c->rank, c->off_lam, c->lam_src_bytes,    \
+                                                                   c->lam_buf_bytes, partial, partial_stride, out,     \
+                                                                   residual, weight, c->H, out_stride, res_stride, eps)
+    if (nvec <= 512) {
+        B2_PUSH(1, ((nvec + 31) / 32) * 32);
+    } else if (nvec <= 1024) {
+        B2_PUSH(2, 512);
+    } else {
+        B2_PUSH(4, 512);
+    }
+#undef B2_PUSH
+}
+
 template <int TP>
 void launch_allreduce(const Comm* c, int slot, __nv_bfloat16* out, __nv_bfloat16* residual, const __nv_bfloat16* weight,
                       int T, int64_t out_stride, int64_t res_stride, float eps, cudaStream_t st) {
@@ -331,10 +526,12 @@ extern "C" int b2_comm_free(void* ptr) {
     return B2_OK;
 }
 
-extern "C" size_t b2_comm_region_bytes(int max_rows, int H, int gather_rows, int gather_cols) {
-    if (max_rows <= 0 || H <= 0 || gather_rows < 0 || gather_cols < 0) return 0;
+extern "C" size_t b2_comm_region_bytes(int tp, int max_rows, int H, int gather_rows, int gather_cols) {
+    if (tp < 1 || tp > MAX_TP || max_rows <= 0 || H <= 0 || gather_rows < 0 || gather_cols < 0) return 0;
     const size_t in = align_up((size_t)max_rows * H * sizeof(__nv_bfloat16), 256);
-    return CTRL_BYTES + 2 * in + align_up((size_t)gather_rows * gather_cols * sizeof(__nv_bfloat16), 256);
+    // control | 2 partial-sum slots (pull variant) | gathered logits | 3 landing buffers x tp sources (push variant)
+    return CTRL_BYTES + 2 * in + align_up((size_t)gather_rows * gather_cols * sizeof(__nv_bfloat16), 256) +
+           3 * (size_t)tp * in;
 }
 
 extern "C" void* b2_comm_create(int rank, int tp, void* const* regions, size_t region_bytes, int max_rows, int H,
@@ -345,9 +542,9 @@ extern "C" void* b2_comm_create(int rank, int tp, void* const* regions, size_t r
                      "H %% 8 == 0, H <= 16384)", tp, rank, max_rows, H, gather_rows, gather_cols);
         return nullptr;
     }
-    if (region_bytes < b2_comm_region_bytes(max_rows, H, gather_rows, gather_cols)) {
+    if (region_bytes < b2_comm_region_bytes(tp, max_rows, H, gather_rows, gather_cols)) {
         b2_set_error("comm_create: regions hold %zu bytes, %zu required", region_bytes,
-                     b2_comm_region_bytes(max_rows, H, gather_rows, gather_cols));
+                     b2_comm_region_bytes(tp, max_rows, H, gather_rows, gather_cols));
         return nullptr;
     }
     for (int r = 0; r < tp; ++r)
@@ -366,7 +563,20 @@ extern "C" void* b2_comm_create(int rank, int tp, void* const* regions, size_t r
     c->off_in[0] = CTRL_BYTES;
     c->off_in[1] = CTRL_BYTES + in;
     c->off_gather = CTRL_BYTES + 2 * in;
+    c->off_lam = c->off_gather + align_up((size_t)gather_rows * gather_cols * sizeof(__nv_bfloat16), 256);
+    c->lam_src_bytes = in;
+    c->lam_buf_bytes = (size_t)tp * in;
     for (int r = 0; r < MAX_TP; ++r) c->peers.base[r] = r < tp ? static_cast<char*>(regions[r]) : nullptr;
+    // arm this rank's landing buffers: every slot holds the sentinel until a peer's data lands in it
+    fill_u32_kernel<<<592, 256>>>(reinterpret_cast<uint32_t*>(c->peers.base[rank] + c->off_lam),
+                                  3 * c->lam_buf_bytes / sizeof(uint32_t), 0x80008000u);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        b2_set_error("comm_create: arming the landing buffers failed: %s", cudaGetErrorString(e));
+        delete c;
+        return nullptr;
+    }
     return c;
 }
 
@@ -403,6 +613,33 @@ extern "C" int b2_comm_allreduce_rms_norm(void* comm, int slot, void* out, void*
         case 2: launch_allreduce<2>(c, slot, o, r, w, T, out_stride, res_stride, eps, st); break;
         case 4: launch_allreduce<4>(c, slot, o, r, w, T, out_stride, res_stride, eps, st); break;
         default: launch_allreduce<8>(c, slot, o, r, w, T, out_stride, res_stride, eps, st); break;
+    }
+    B2_CUDA_OK(cudaGetLastError());
+    return B2_OK;
+}
+
+extern "C" int b2_comm_push_allreduce_rms_norm(void* comm, const void* partial, int64_t partial_stride, void* out,
+                                               void* residual, const void* weight, int T, int64_t out_stride,
+                                               int64_t res_stride, float eps, void* stream) {
+    const Comm* c = static_cast<const Comm*>(comm);
+    B2_REQUIRE(c, B2_EINVAL, "comm_push_allreduce_rms_norm: null handle");
+    B2_REQUIRE(T >= 0 && T <= c->max_rows && T <= PUSH_MAX_ROWS, B2_EINVAL,
+               "comm_push_allreduce_rms_norm: T=%d outside [0, min(%d, %d)]", T, c->max_rows, PUSH_MAX_ROWS);
+    if (T == 0) return B2_OK;
+    B2_REQUIRE(out && partial, B2_EINVAL, "comm_push_allreduce_rms_norm: null pointer");
+    B2_REQUIRE(b2_aligned16(out) && b2_aligned16(partial) && b2_aligned16(residual) && b2_aligned16(weight) &&
+                   out_stride % 8 == 0 && res_stride % 8 == 0 && partial_stride % 8 == 0, B2_EINVAL,
+               "comm_push_allreduce_rms_norm: pointers / strides must keep 16-byte alignment");
+    auto* x = static_cast<const __nv_bfloat16*>(partial);
+    auto* o = static_cast<__nv_bfloat16*>(out);
+    auto* r = static_cast<__nv_bfloat16*>(residual);
+    auto* w = static_cast<const __nv_bfloat16*>(weight);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (c->tp) {
+        case 1: launch_push<1>(c, x, partial_stride, o, r, w, T, out_stride, res_stride, eps, st); break;
+        case 2: launch_push<2>(c, x, partial_stride, o, r, w, T, out_stride, res_stride, eps, st); break;
+        case 4: launch_push<4>(c, x, partial_stride, o, r, w, T, out_stride, res_stride, eps, st); break;
+        default: launch_push<8>(c, x, partial_stride, o, r, w, T, out_stride, res_stride, eps, st); break;
     }
     B2_CUDA_OK(cudaGetLastError());
     return B2_OK;
