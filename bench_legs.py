@@ -204,6 +204,21 @@ def tp_parity_leg(dev, group, model: str = "tiny8", seed: int = 1, gap: float = 
     return rec
 
 
+def _nvlink_kib(index: int):
+    """(tx, rx) data KiB over all NVLink links of GPU `index` (NVML field counters), or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        v = pynvml.nvmlDeviceGetFieldValues(h, [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
+                                                (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)])
+        if any(x.nvmlReturn != 0 for x in v):
+            return None
+        return int(v[0].value.ullVal), int(v[1].value.ullVal)
+    except Exception:                                                         # noqa: BLE001
+        return None
+
+
 def tp_comm_leg(dev, group, T: int = 64, H: int = 4096, iters: int = 200) -> dict:
     """The exchange after o_proj / down_proj at decode size: the fused one-shot NVLink kernel against NCCL all-reduce +
     the plain fused-add RMSNorm, back-to-back launches, CUDA events on rank 0 (every rank runs the same loop)."""
@@ -231,16 +246,23 @@ def tp_comm_leg(dev, group, T: int = 64, H: int = 4096, iters: int = 200) -> dic
                 ops.rms_norm(x, w, 1e-5, residual=resid, out=out)
 
         res = {}
+        gpu_index = int(os.environ.get("CUDA_VISIBLE_DEVICES", "0,1,2,3,4,5,6,7").split(",")[dev.index or 0])
         for name, fn in (("push_allreduce_rmsnorm_us", push), ("pull_allreduce_rmsnorm_us", fused),
                          ("nccl_allreduce_plus_rmsnorm_us", nccl)):
             fn()
             group.barrier()
+            k0 = _nvlink_kib(gpu_index)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             fn()
             e1.record()
             torch.cuda.synchronize()
             res[name] = round(e0.elapsed_time(e1) / iters * 1e3, 2)
+            group.barrier()
+            k1 = _nvlink_kib(gpu_index)
+            if k0 is not None and k1 is not None:                 # NVML link counters of this GPU around the loop
+                res[name.replace("_us", "_nvlink_bytes_per_call")] = {"tx": round((k1[0] - k0[0]) * 1024 / iters),
+                                                                      "rx": round((k1[1] - k0[1]) * 1024 / iters)}
             x.normal_()
         # the same loops replayed as ONE CUDA graph: device time per exchange without the host launch cost
         # (how the decode step runs them)
@@ -264,6 +286,12 @@ def tp_comm_leg(dev, group, T: int = 64, H: int = 4096, iters: int = 200) -> dic
                 del g
             except Exception as e:                                            # noqa: BLE001
                 res[name] = f"{type(e).__name__}: {e}"[:200]
+        if os.environ.get("B2_COMM_DEBUG") == "1":
+            import ctypes
+            torch.cuda.synchronize()
+            st4 = (ctypes.c_uint64 * 4)()
+            group._lib.b2_comm_debug_stamps(group._comm, st4)
+            res["push_stamps_ns"] = {"pushed": st4[1] - st4[0], "all_arrived": st4[2] - st4[0], "row_done": st4[3] - st4[0]}
         group.barrier()
         group.close()
         res.update(T=T, H=H, tp=group.size, message_bytes=T * H * 2, iters=iters,

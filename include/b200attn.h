@@ -357,6 +357,9 @@ B2_API void* b2_comm_create(int rank, int tp, void* const* regions, size_t regio
 B2_API void b2_comm_destroy(void* comm);
 B2_API void* b2_comm_input(void* comm, int slot);
 B2_API void* b2_comm_gathered(void* comm);
+/* diagnostic (B2_COMM_DEBUG=1 at b2_comm_create): globaltimer ns of CTA 0 in the last push exchange:
+ * kernel start, own rows pushed, first vector complete from every peer, row done.  Synchronises the device. */
+B2_API int b2_comm_debug_stamps(void* comm, uint64_t* out4);
 B2_API int b2_comm_allreduce_rms_norm(void* comm, int slot, void* out, void* residual, const void* weight, int T,
                                       int64_t out_stride, int64_t res_stride, float eps, void* stream);
 B2_API int b2_comm_push_allreduce_rms_norm(void* comm, const void* partial, int64_t partial_stride, void* out,

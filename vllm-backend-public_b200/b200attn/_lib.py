@@ -82,6 +82,7 @@ SIGNATURES = {
     "b2_comm_destroy": (None, [vp]),
     "b2_comm_input": (vp, [vp, i32]),
     "b2_comm_gathered": (vp, [vp]),
+    "b2_comm_debug_stamps": (i32, [vp, vp]),
     "b2_comm_allreduce_rms_norm": (i32, [vp, i32, vp, vp, vp, i32, i64, i64, f32, vp]),
     "b2_comm_push_allreduce_rms_norm": (i32, [vp, vp, i64, vp, vp, vp, i32, i64, i64, f32, vp]),
     "b2_comm_allgather_cols": (i32, [vp, vp, i64, i32, i32, vp]),

@@ -26,6 +26,8 @@
 // read of the slot used there; the slot is next written two barriers later.
 #include "b2_common.cuh"
 
+#include <stddef.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -40,7 +42,8 @@ struct Ctrl {                       // first CTRL_BYTES of every rank's region
     uint32_t epoch;                 // barriers this rank has completed (only this rank's kernels write it)
     uint32_t done;                  // CTAs of the running kernel that have finished
     uint32_t lam;                   // push exchanges this rank has completed (selects the landing buffer, mod 3)
-    uint32_t pad[29];
+    uint32_t pad[13];
+    uint64_t dbg[8];                // B2_COMM_DEBUG=1: globaltimer stamps of CTA 0 / thread 0 of the last push exchange
     uint32_t flag[MAX_TP][32];      // flag[src][0] = last epoch rank `src` has reached (one 128-byte line per source)
 };
 static_assert(sizeof(Ctrl) <= CTRL_BYTES, "control block");
@@ -50,7 +53,7 @@ struct Peers {
 };
 
 struct Comm {
-    int rank, tp, max_rows, H, gather_rows, gather_cols;
+    int rank, tp, max_rows, H, gather_rows, gather_cols, debug, weak_st;
     size_t region_bytes, off_in[2], off_gather, off_lam, lam_src_bytes, lam_buf_bytes;
     Peers peers;
 };
@@ -313,8 +316,11 @@ const Peers peers, int rank, size_t lam_off, size_t lam_src_bytes, size_t lam_bu
                                const __nv_bfloat16* __restrict__ partial, int64_t partial_stride,
                                __nv_bfloat16* __restrict__ out, __nv_bfloat16* __restrict__ residual,
                                const __nv_bfloat16* __restrict__ weight, int H, int64_t out_stride, int64_t res_stride,
-                               float eps) {
+                               float eps, int flags) {
     char* mine = peer_base<TP>(peers, rank);
+    const bool dbg = (flags & 1) && blockIdx.x == 0 && threadIdx.x == 0;
+    uint64_t ts[4];
+    if (dbg) ts[0] = globaltimer_ns();
     Ctrl* me = reinterpret_cast<Ctrl*>(mine);
     __shared__ uint32_t s_lam;
     __shared__ float red[32];
@@ -348,10 +354,12 @@ const Peers peers, int rank, size_t lam_off, size_t lam_src_bytes, size_t lam_bu
 #pragma unroll
             for (int p = 1; p < TP; ++p) {                         // start with the next rank: spreads the switch ports
                 const int dst = (rank + p) % TP;
-                st_volatile_16(peer_base<TP>(peers, dst) + off, xv[k]);
+                if (flags & 2) *reinterpret_cast<int4*>(peer_base<TP>(peers, dst) + off) = xv[k];
+                else st_volatile_16(peer_base<TP>(peers, dst) + off, xv[k]);
             }
         }
     }
+    if (dbg) ts[1] = globaltimer_ns();
 
     float h[VPT][8];
     float ss = 0.f;
@@ -382,6 +390,7 @@ const Peers peers, int rank, size_t lam_off, size_t lam_src_bytes, size_t lam_bu
                     if (pending && globaltimer_ns() - t0 > 10000000000ull) __trap();
                 }
             }
+            if (dbg && k == 0) ts[2] = globaltimer_ns();
 #pragma unroll
             for (int p = 0; p < TP; ++p)                            // re-arm the consumed slots for call k + 3
                 if (p != rank) st_volatile_16(mine + off + (size_t)p * lam_src_bytes, sentinel);
@@ -429,6 +438,10 @@ const Peers peers, int rank, size_t lam_off, size_t lam_src_bytes, size_t lam_bu
             }
         }
     }
+    if (dbg) {
+        ts[3] = globaltimer_ns();
+        for (int i = 0; i < 4; ++i) me->dbg[i] = ts[i];
+    }
     if (threadIdx.x == 0) {
         __threadfence();
         if (atomicAdd(&me->done, 1u) == gridDim.x - 1) {
@@ -447,7 +460,8 @@ void launch_push(const Comm* c, const __nv_bfloat16* partial, int64_t partial_st
 #define B2_PUSH(VPT, THREADS)                                                                                         \
     push_allreduce_rms_norm_kernel<TP, VPT><<<T, THREADS, 0, st>>>(c->peers, c->rank, c->off_lam, c->lam_src_bytes,    \
                                                                    c->lam_buf_bytes, partial, partial_stride, out,     \
-                                                                   residual, weight, c->H, out_stride, res_stride, eps)
+                                                                   residual, weight, c->H, out_stride, res_stride, eps, \
+                                                                   c->debug | (c->weak_st << 1))
     if (nvec <= 512) {
         B2_PUSH(1, ((nvec + 31) / 32) * 32);
     } else if (nvec <= 1024) {
@@ -559,6 +573,10 @@ extern "C" void* b2_comm_create(int rank, int tp, void* const* regions, size_t r
     }
     c->rank = rank; c->tp = tp; c->max_rows = max_rows; c->H = H;
     c->gather_rows = gather_rows; c->gather_cols = gather_cols; c->region_bytes = region_bytes;
+    const char* env = getenv("B2_COMM_DEBUG");
+    c->debug = env && env[0] == '1';
+    env = getenv("B2_COMM_WEAK_ST");
+    c->weak_st = env && env[0] == '1';
     const size_t in = align_up((size_t)max_rows * H * sizeof(__nv_bfloat16), 256);
     c->off_in[0] = CTRL_BYTES;
     c->off_in[1] = CTRL_BYTES + in;
@@ -586,6 +604,13 @@ extern "C" void* b2_comm_input(void* comm, int slot) {
     const Comm* c = static_cast<const Comm*>(comm);
     if (!c || slot < 0 || slot > 1) return nullptr;
     return c->peers.base[c->rank] + c->off_in[slot];
+}
+
+extern "C" int b2_comm_debug_stamps(void* comm, uint64_t* out4) {
+    const Comm* c = static_cast<const Comm*>(comm);
+    B2_REQUIRE(c && out4, B2_EINVAL, "comm_debug_stamps: null pointer");
+    B2_CUDA_OK(cudaMemcpy(out4, c->peers.base[c->rank] + offsetof(Ctrl, dbg), 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return B2_OK;
 }
 
 extern "C" void* b2_comm_gathered(void* comm) {
