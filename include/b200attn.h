@@ -232,6 +232,15 @@ B2_API int b2_rope_and_cache(void* qkv, const int32_t* positions, const float* c
                       int kv_dtype, const float* k_scale, const float* v_scale, void* stream);
 B2_API int b2_sample(int64_t* tokens, const void* logits, int B, int V, int64_t stride, const float* temperature,
               const int64_t* seeds, void* stream);
+/* b2_sample with the OpenAI / vLLM sampling filters (top_k int32 [B], top_p fp32 [B]; either may be NULL): for rows
+ * with temperature > 0 the draw is restricted to the candidate set {logit >= t}: t = the top_k-th largest logit
+ * (ties kept; top_k <= 0 or >= V: no limit), then raised to the smallest set of top logits whose softmax(logits / T)
+ * mass reaches top_p of the top-k mass (ties kept; top_p >= 1: no limit) -- vLLM's order, top-k first.  The draw is the
+ * same Gumbel-max with the same hash, so top_k = 0, top_p = 1 is b2_sample bit for bit.  Sort-free: bisection over the
+ * 16-bit key space of bf16 (16 passes over the L2-resident row per filter). */
+B2_API int b2_sample_filtered(int64_t* tokens, const void* logits, int B, int V, int64_t stride,
+                              const float* temperature, const int64_t* seeds, const int32_t* top_k, const float* top_p,
+                              void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Block manager (host only): the page allocator that produces block_tables / seq_lens /

@@ -162,8 +162,42 @@ def sample_scores_ref(logits: torch.Tensor, temperature: Optional[torch.Tensor],
     return s
 
 
-def sample_ref(logits, temperature=None, seeds=None) -> torch.Tensor:
+def sample_candidates_ref(logits: torch.Tensor, temperature, top_k=None, top_p=None, slack: float = 0.0):
+    """bool [B, V]: the tokens a draw may return under top-k then top-p (vLLM's order; engine contract in
+    include/b200attn.h::b2_sample_filtered).  Row b: t_k = the top_k-th largest logit (ties kept); masses
+    w_i = exp((l_i - max) / T) over {l >= t_k}; the smallest set of top logit VALUES (ties kept) whose mass reaches
+    top_p * (1 - slack) of that total.  `slack` > 0 narrows and < 0 widens the nucleus, so that a test can bound a
+    kernel that sums the masses in another order from both sides."""
+    B, V = logits.shape
+    lf = logits.to(torch.float64)
+    keep = torch.ones(B, V, dtype=torch.bool)
+    for b in range(B):
+        T = float(temperature[b]) if temperature is not None else 0.0
+        if T <= 0:
+            continue
+        row = lf[b]
+        k = int(top_k[b]) if top_k is not None else 0
+        p = float(top_p[b]) if top_p is not None else 1.0
+        m = torch.ones(V, dtype=torch.bool)
+        if 0 < k < V:
+            kth = torch.sort(row, descending=True).values[k - 1]
+            m = row >= kth
+        if p < 1.0:
+            w = torch.where(m, torch.exp((row - row[m].max()) / T), torch.zeros_like(row))
+            vals = torch.unique(row[m])                              # ascending
+            mass_ge = torch.stack([w[row >= v].sum() for v in vals])  # non-increasing in v
+            target = p * (1.0 - slack) * w.sum()
+            ok = mass_ge >= target
+            t = vals[ok].max()                                       # largest value whose top set still reaches the target
+            m = m & (row >= t)
+        keep[b] = m
+    return keep
+
+
+def sample_ref(logits, temperature=None, seeds=None, top_k=None, top_p=None) -> torch.Tensor:
     s = sample_scores_ref(logits, temperature, seeds)
+    if top_k is not None or top_p is not None:
+        s = torch.where(sample_candidates_ref(logits, temperature, top_k, top_p), s, torch.full_like(s, -float("inf")))
     # torch.argmax does not promise the first index on ties; do it explicitly
     mx = s.max(dim=-1, keepdim=True).values
     first = torch.where(s == mx, torch.arange(s.shape[1]).expand_as(s), torch.full_like(s, s.shape[1], dtype=torch.long))

@@ -20,6 +20,7 @@ for p in (ROOT / "vllm-backend-public_b200", ROOT / "oracle", ROOT / "tests"):
 import torch  # noqa: E402
 
 import b200attn  # noqa: E402
+import b200attn.model  # noqa: E402
 from b200attn import ops  # noqa: E402
 import paged_attention_ref as R  # noqa: E402
 import layer_ref as L  # noqa: E402
@@ -30,6 +31,31 @@ only = set(sys.argv[1:])
 
 def want(name):
     return not only or name in only
+
+
+class Guard:
+    """Stand-in for memcheck / initcheck where compute-sanitizer is not available: every buffer a kernel may write sits
+    between two 4 KiB red zones that must still hold their pattern afterwards (out-of-bounds writes), and scratch
+    buffers start as all-ones bytes = NaN (a read of scratch the kernel did not write first shows up in the result)."""
+    PAD = 4096
+
+    def __init__(self):
+        self.bufs = []
+
+    def alloc(self, shape, dtype, fill=None):
+        n = int(torch.tensor(shape).prod()) * torch.empty(0, dtype=dtype).element_size()
+        buf = torch.full((n + 2 * self.PAD,), 0xA5, dtype=torch.uint8, device=dev)
+        inner = buf[self.PAD:self.PAD + n]
+        inner.fill_(0xFF if fill == "nan" else 0)
+        self.bufs.append((buf, n))
+        return inner.view(dtype).view(shape)
+
+    def check(self, what):
+        torch.cuda.synchronize()
+        for buf, n in self.bufs:
+            assert bool((buf[:self.PAD] == 0xA5).all()) and bool((buf[self.PAD + n:] == 0xA5).all()), \
+                f"{what}: a red zone was overwritten (out-of-bounds write)"
+        self.bufs = []
 
 
 def close(out, ref, what, atol=2e-3, rtol=1e-2):
@@ -45,13 +71,15 @@ def decode_cases():
             inp["seq_lens"] = lens
             shape = (inp["num_blocks"], 2, bs, 128)
             ks = vs = None
+            G = Guard()
             if fp8:
-                kc = torch.zeros(shape, dtype=torch.uint8, device=dev)
+                kc = G.alloc(shape, torch.uint8)
+                vc = G.alloc(shape, torch.uint8)
                 ks = torch.tensor([0.05], device=dev)
                 vs = torch.tensor([0.04], device=dev)
             else:
-                kc = torch.zeros(shape, dtype=torch.bfloat16, device=dev)
-            vc = torch.zeros_like(kc)
+                kc = G.alloc(shape, torch.bfloat16)
+                vc = G.alloc(shape, torch.bfloat16)
             slots = inp["slot_mapping"].clone()
             slots[::7] = -1                                     # skipped tokens
             ops.reshape_and_cache(inp["k"].to(dev), inp["v"].to(dev), kc, vc, slots.to(dev), ks, vs)
@@ -62,11 +90,22 @@ def decode_cases():
             assert torch.equal(kc.cpu().view(torch.uint8), kc_ref.view(torch.uint8)), "KV write not bit-exact"
             ref = R.paged_decode_ref(inp["q"], kc_ref, vc_ref, inp["block_tables"], lens, kv_dtype=1 if fp8 else 0,
                                      k_scale=0.05 if fp8 else 1.0, v_scale=0.04 if fp8 else 1.0, return_f32=True)
+            G.check(f"KV write fp8={fp8} bs={bs}")
             for splits in (1, 3, 0):
-                out = ops.paged_decode(inp["q"].to(dev), kc, vc, inp["block_tables"].to(dev), lens.to(dev),
-                                       k_scale=ks, v_scale=vs, num_splits=splits)
-                torch.cuda.synchronize()
-                close(out, ref, f"decode fp8={fp8} bs={bs} splits={splits}")
+                runs = []
+                for rep in range(3):                       # same launch three times: a race would show as differing bits
+                    out = G.alloc((5, 8, 128), torch.bfloat16, fill="nan")
+                    need = max(ops.decode_workspace_bytes(5, 8, 2, 128, bs, inp["block_tables"].shape[1], splits), 256)
+                    ws = G.alloc((need,), torch.uint8, fill="nan")          # scratch starts as NaN
+                    ops.paged_decode(inp["q"].to(dev), kc, vc, inp["block_tables"].to(dev), lens.to(dev),
+                                     k_scale=ks, v_scale=vs, num_splits=splits, out=out, workspace=ws)
+                    torch.cuda.synchronize()
+                    assert bool(torch.isfinite(out.float()).all()), "NaN in the result: uninitialised scratch was read"
+                    close(out, ref, f"decode fp8={fp8} bs={bs} splits={splits}")
+                    runs.append(out.clone())
+                    G.check(f"decode fp8={fp8} bs={bs} splits={splits}")
+                assert all(torch.equal(runs[0].view(torch.int16), r.view(torch.int16)) for r in runs[1:]), \
+                    f"decode fp8={fp8} bs={bs} splits={splits}: results differ between identical launches"
     print("decode cases ok")
 
 

@@ -278,3 +278,55 @@ def test_sample_distribution(cuda):
     freq = torch.bincount(got, minlength=V).float() / N
     p = torch.softmax(logits.float(), 0)
     assert (freq - p).abs().max() < 0.015
+
+
+def test_sample_top_k_top_p(cuda):
+    """b2_sample_filtered against the oracle's candidate sets (oracle/layer_ref.py::sample_candidates_ref).  The kernel
+    sums the softmax masses in another order than the oracle, so the nucleus is bounded from both sides: every draw lies
+    in the oracle's set widened by 1e-3 of the mass, and is the best-scoring token of a set no smaller than the one
+    narrowed by 1e-3; top-k alone (integer counts) is exact."""
+    g = torch.Generator().manual_seed(5)
+    B, V = 24, 32000
+    logits = (torch.randn(B, V, generator=g) * 2.5).to(torch.bfloat16)
+    temp = torch.full((B,), 0.9)
+    temp[::6] = 0.0
+    seeds = torch.arange(B, dtype=torch.int64) * 104729 + 3
+    top_k = torch.tensor([0, 1, 5, 50, 1000, V, 7, 0] * 3, dtype=torch.int32)
+    top_p = torch.tensor([1.0, 1.0, 0.5, 0.9, 0.3, 0.99, 1.0, 0.7] * 3, dtype=torch.float32)
+    got = ops.sample(logits.to(cuda), temp.to(cuda), seeds.to(cuda), top_k=top_k.to(cuda), top_p=top_p.to(cuda)).cpu()
+    scores = L.sample_scores_ref(logits, temp, seeds)
+    loose = L.sample_candidates_ref(logits, temp, top_k, top_p, slack=-1e-3)      # nucleus target raised: a superset
+    tight = L.sample_candidates_ref(logits, temp, top_k, top_p, slack=1e-3)
+    assert loose.gather(1, got.unsqueeze(1)).all(), "a draw fell outside the candidate set"
+    best_tight = torch.where(tight, scores, torch.full_like(scores, -float("inf"))).max(dim=1).values
+    picked = scores.gather(1, got.unsqueeze(1)).squeeze(1)
+    assert (picked >= best_tight - 1e-3).all(), "a better-scoring candidate was passed over"
+    # top-k only: exact
+    only_k = ops.sample(logits.to(cuda), temp.to(cuda), seeds.to(cuda), top_k=top_k.to(cuda)).cpu()
+    ref_k = L.sample_ref(logits, temp, seeds, top_k=top_k)
+    sk = scores.gather(1, only_k.unsqueeze(1)).squeeze(1)
+    rk = scores.gather(1, ref_k.unsqueeze(1)).squeeze(1)
+    assert (sk >= rk - 1e-3).all() and L.sample_candidates_ref(logits, temp, top_k, None).gather(1, only_k.unsqueeze(1)).all()
+    # no filter = b2_sample bit for bit; top_k = 1 = greedy
+    plain = ops.sample(logits.to(cuda), temp.to(cuda), seeds.to(cuda)).cpu()
+    nofilt = ops.sample(logits.to(cuda), temp.to(cuda), seeds.to(cuda), top_k=torch.zeros(B, dtype=torch.int32, device=cuda),
+                        top_p=torch.ones(B, device=cuda)).cpu()
+    assert torch.equal(plain, nofilt)
+    k1 = ops.sample(logits.to(cuda), torch.ones(B, device=cuda), seeds.to(cuda),
+                    top_k=torch.ones(B, dtype=torch.int32, device=cuda)).cpu()
+    assert torch.equal(k1, L.sample_ref(logits))
+
+
+def test_sample_top_p_distribution(cuda):
+    """Draws under top_p follow the renormalised nucleus: p = 0.8 over softmax([2, 1.5, 1, .5, 0, -1]) keeps 4 tokens."""
+    logits = torch.tensor([2.0, 1.0, 0.0, -1.0, 0.5, 1.5, -30.0, -30.0]).to(torch.bfloat16)
+    N, V = 20000, 8
+    rows = logits.unsqueeze(0).repeat(N, 1).contiguous()
+    seeds = torch.arange(N, dtype=torch.int64) * 2654435761 + 17
+    got = ops.sample(rows.to(cuda), torch.ones(N, device=cuda), seeds.to(cuda),
+                     top_p=torch.full((N,), 0.8, device=cuda)).cpu()
+    keep = L.sample_candidates_ref(logits.unsqueeze(0), torch.ones(1), None, torch.tensor([0.8]))[0]
+    p = torch.softmax(logits.float(), 0) * keep
+    p = p / p.sum()
+    freq = torch.bincount(got, minlength=V).float() / N
+    assert int(keep.sum()) == 4 and (freq[~keep] == 0).all() and (freq - p).abs().max() < 0.015

@@ -160,3 +160,28 @@ def test_llama_forward_oracle_matches_transformers():
     # ours rounds activations to bf16 between ops (as the engine does); HF here runs pure fp32
     assert (ours - hf).abs().max() < 3e-2 * hf.abs().max()
     assert (ours.argmax(-1) == hf.argmax(-1)).float().mean() > 0.9
+
+
+def test_sample_candidates_oracle():
+    """top-k then top-p (b2_sample_filtered's contract) on a hand-checkable row."""
+    logits = torch.tensor([[3.0, 1.0, 2.0, 2.0, 0.0, -1.0]]).to(torch.bfloat16)
+    T = torch.ones(1)
+    k = lambda n: torch.tensor([n], dtype=torch.int32)                       # noqa: E731
+    p = lambda x: torch.tensor([x], dtype=torch.float32)                     # noqa: E731
+    assert L.sample_candidates_ref(logits, T, k(1), None)[0].tolist() == [True, False, False, False, False, False]
+    assert L.sample_candidates_ref(logits, T, k(2), None)[0].tolist() == [True, False, True, True, False, False]   # tie kept
+    assert L.sample_candidates_ref(logits, T, k(0), None)[0].all() and L.sample_candidates_ref(logits, T, k(6), None)[0].all()
+    w = torch.exp(logits[0].double() - 3.0)
+    frac0 = float(w[0] / w.sum())                                            # 0.44: mass of the top token alone
+    assert L.sample_candidates_ref(logits, T, None, p(frac0 - 0.01))[0].tolist() == [True] + [False] * 5
+    assert L.sample_candidates_ref(logits, T, None, p(frac0 + 0.01))[0].tolist() == [True, False, True, True, False, False]
+    assert L.sample_candidates_ref(logits, T, None, p(1.0))[0].all()
+    # top-p is taken over the top-k mass: k = 3 (-> {3, 2, 2}) then p just above the top token's share of THAT mass
+    share = float(w[0] / (w[0] + w[2] + w[3]))
+    assert L.sample_candidates_ref(logits, T, k(3), p(share - 0.01))[0].tolist() == [True] + [False] * 5
+    assert L.sample_candidates_ref(logits, T, k(3), p(share + 0.01))[0].tolist() == [True, False, True, True, False, False]
+    # greedy rows ignore the filters; a filtered draw is the best-scoring candidate
+    assert L.sample_candidates_ref(logits, torch.zeros(1), k(1), p(0.1))[0].all()
+    rows = logits.repeat(200, 1)
+    got = L.sample_ref(rows, torch.ones(200), torch.arange(200, dtype=torch.int64), top_k=torch.full((200,), 2, dtype=torch.int32))
+    assert set(got.tolist()) == {0, 2, 3}

@@ -166,7 +166,8 @@ def test_chat_completions(client):
     ({"prompt": [1, "a"]}, 400, "prompt"),
     ({"prompt": "x", "max_tokens": 0}, 400, "max_tokens"),
     ({"prompt": "x", "temperature": -1}, 400, "temperature"),
-    ({"prompt": "x", "top_p": 0.5}, 400, "top_p"),
+    ({"prompt": "x", "top_p": 0.0}, 400, "top_p"),
+    ({"prompt": "x", "top_k": "many"}, 400, "top_k"),
     ({"prompt": "x", "n": 0}, 400, "n"),
     ({"prompt": "x", "stop": 5}, 400, "stop"),
     ({"prompt": "x" * 64}, 400, "prompt"),
@@ -306,3 +307,24 @@ def test_chat_uses_the_models_own_template_when_the_tokenizer_ships_one(tmp_path
                                   {"role": "user", "content": "hi there"}])
     assert t.encode_rendered(text) == [0, 2, 4, 3, 5, 1, 2, 4, 5, 3]
     assert not hasattr(ByteTokenizer(300), "apply_chat_template")
+
+
+def test_evaljob_renders_like_the_reference_and_describes_a_runnable_job():
+    """b200attn.evaljob.process_template against the outputs of the reference's own function
+    (tests/golden/reference_contract.json, generated from benchmark-eval/main.py:55-58), and the committed
+    evaluate.yaml renders to a valid Job whose container is the load generator pointed at the engine."""
+    import json
+    from pathlib import Path
+    from b200attn import evaljob
+    fx = json.loads((Path(__file__).parent / "golden" / "reference_contract.json").read_text())["process_template"]
+    for model, url, rendered in fx["cases"]:
+        assert evaljob.process_template(fx["template"], model, url) == rendered
+    text, job = evaljob.render_for_model("B200_Llama-3.1-8B", "http://127.0.0.1:8005")
+    assert "{" not in text.split("spec:", 1)[1].replace('["python", "-m", "b200attn.loadgen"]', "")   # no placeholder left
+    assert job["metadata"]["name"] == "eval-b200-llama-3-1-8b"
+    argv, env = evaljob.job_command(job)
+    assert argv[:3] == ["python", "-m", "b200attn.loadgen"] and argv[argv.index("--model") + 1] == "B200-Llama-3-1-8B"
+    assert env["VLLM_MODEL_ENDPOINT"] == "http://127.0.0.1:8005/v1/completions"
+    import pytest
+    with pytest.raises(ValueError):
+        evaljob.render_for_model("m", "u", template="kind: [unclosed")

@@ -32,6 +32,8 @@ from .scheduler import Scheduler, StepPlan
 class SamplingParams:
     max_tokens: int = 16
     temperature: float = 1.0
+    top_k: int = 0                    # <= 0: no limit
+    top_p: float = 1.0                # >= 1: no limit
     seed: Optional[int] = None
     ignore_eos: bool = False
     stop_token_ids: Tuple[int, ...] = ()
@@ -146,17 +148,20 @@ class LLMEngine:
         self._h_i64 = torch.zeros(3 * B, dtype=torch.int64).pin_memory()          # tokens | slots | seeds
         self._h_i32 = torch.zeros(2 * B, dtype=torch.int32).pin_memory()          # positions | seq_lens
         self._h_bt = torch.zeros(B, self.max_nb, dtype=torch.int32).pin_memory()
-        self._h_temp = torch.zeros(B, dtype=torch.float32).pin_memory()
+        self._h_temp = torch.zeros(2 * B, dtype=torch.float32).pin_memory()       # temperature | top_p
+        self._h_topk = torch.zeros(B, dtype=torch.int32).pin_memory()
         self._h_out = torch.zeros(max(B, 1), dtype=torch.int64).pin_memory()
         self._d_i64 = torch.zeros(3 * B, dtype=torch.int64, device=self.dev)
         self._d_i32 = torch.zeros(2 * B, dtype=torch.int32, device=self.dev)
         self._d_bt = torch.zeros(B, self.max_nb, dtype=torch.int32, device=self.dev)
-        self._d_temp = torch.zeros(B, dtype=torch.float32, device=self.dev)
+        self._d_temp = torch.zeros(2 * B, dtype=torch.float32, device=self.dev)
+        self._d_topk = torch.zeros(B, dtype=torch.int32, device=self.dev)
         self._d_out = torch.zeros(B, dtype=torch.int64, device=self.dev)
         self._np_i64 = self._h_i64.numpy()
         self._np_i32 = self._h_i32.numpy()
         self._np_bt = self._h_bt.numpy()
         self._np_temp = self._h_temp.numpy()
+        self._np_topk = self._h_topk.numpy()
         self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
         self._buckets = _buckets(B)
         self._stream = torch.cuda.Stream(self.dev)
@@ -260,7 +265,8 @@ class LLMEngine:
         self._hm_tok, self._hm_slot, self._hm_pos = pin(Tm, torch.int64), pin(Tm, torch.int64), pin(Tm, torch.int32)
         self._hm_aux = pin(2 * B, torch.int64)                 # seeds [B] | sample rows [B]
         self._hm_meta = pin(3 * B + 1, torch.int32)            # decode seq_lens [B] | cu_q [B + 1] | ctx_start [B]
-        self._hm_temp = pin(B, torch.float32)
+        self._hm_temp = pin(2 * B, torch.float32)             # temperature [B] | top_p [B]
+        self._hm_topk = pin(B, torch.int32)
         self._hm_pbt = torch.zeros(B, self.max_nb, dtype=torch.int32).pin_memory()
 
     def step(self) -> List[Tuple[Request, int]]:
@@ -325,7 +331,8 @@ class LLMEngine:
         def run():
             logits = self.model.forward(self._d_i64[:bucket], self._d_i32[:bucket], self._d_i64[B:B + bucket], bucket,
                                         self._d_bt[:bucket], self._d_i32[B:B + bucket], None, None, num_splits)
-            ops.sample(logits, self._d_temp[:bucket], self._d_i64[2 * B:2 * B + bucket], out=self._d_out[:bucket])
+            ops.sample(logits, self._d_temp[:bucket], self._d_i64[2 * B:2 * B + bucket], out=self._d_out[:bucket],
+                       top_k=self._d_topk[:bucket], top_p=self._d_temp[B:B + bucket])
 
         if not self.use_graphs:
             self._graphs[key] = run
@@ -363,6 +370,10 @@ class LLMEngine:
         self._np_bt[:nd, :used] = plan.block_tables[:, :used]
         self._np_temp[:bucket] = 0
         self._np_temp[:nd] = [r.params.temperature for r in reqs]
+        self._np_temp[B:B + bucket] = 1.0
+        self._np_temp[B:B + nd] = [r.params.top_p for r in reqs]
+        self._np_topk[:bucket] = 0
+        self._np_topk[:nd] = [r.params.top_k for r in reqs]
         num_splits = ops.plan_num_splits(self._h_i32[B:B + nd], *self._plan_heads, self.cfg.d, self.block_size,
                                          ops.KV_FP8_E4M3 if self.kv_dtype == torch.uint8 else ops.KV_BF16)
         replay = self._decode_graph(bucket, num_splits)
@@ -371,6 +382,7 @@ class LLMEngine:
             self._d_i32.copy_(self._h_i32, non_blocking=True)
             self._d_bt[:nd, :used].copy_(self._h_bt[:nd, :used], non_blocking=True)
             self._d_temp.copy_(self._h_temp, non_blocking=True)
+            self._d_topk.copy_(self._h_topk, non_blocking=True)
             if self.time_device:
                 self._ev[0].record(self._stream)
             replay()
@@ -423,6 +435,8 @@ class LLMEngine:
         if ns == 0:
             aux[B] = 0                       # no row to sample this step: lm_head runs on one dummy row
         self._hm_temp.numpy()[:ns] = [r.params.temperature for r in sample_reqs]
+        self._hm_temp.numpy()[B:B + ns] = [r.params.top_p for r in sample_reqs]
+        self._hm_topk.numpy()[:ns] = [r.params.top_k for r in sample_reqs]
         bsz = self.block_size
         used_p = (int((plan.prefill_start + plan.prefill_len).max()) + bsz - 1) // bsz
         self._hm_pbt.numpy()[:npf, :used_p] = plan.prefill_block_tables[:, :used_p]
@@ -440,6 +454,7 @@ class LLMEngine:
             d_aux = self._hm_aux.to(dev, non_blocking=True)
             d_meta = self._hm_meta.to(dev, non_blocking=True)
             d_temp = self._hm_temp.to(dev, non_blocking=True)
+            d_topk = self._hm_topk.to(dev, non_blocking=True)
             d_pbt = self._hm_pbt[:npf].to(dev, non_blocking=True)
             dec_bt = dec_sl = None
             if nd:
@@ -450,7 +465,7 @@ class LLMEngine:
                               kv_lens_host=(plan.prefill_start + plan.prefill_len).tolist())
             logits = self.model.forward(d_tok, d_pos, d_slot, nd, dec_bt, dec_sl, pf, d_aux[B:B + max(ns, 1)], num_splits)
             if ns:
-                out = ops.sample(logits, d_temp[:ns], d_aux[:ns])
+                out = ops.sample(logits, d_temp[:ns], d_aux[:ns], top_k=d_topk[:ns], top_p=d_temp[B:B + ns])
                 self._h_out[:ns].copy_(out, non_blocking=True)
         self._stream.synchronize()
         self.stats.gpu_launches += self.cfg.layers * (self._launches_per_layer + 1) + 3

@@ -476,11 +476,14 @@ def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_sin: torch.Te
 
 
 def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, seeds: Optional[torch.Tensor] = None,
-           out: Optional[torch.Tensor] = None) -> torch.Tensor:
+           out: Optional[torch.Tensor] = None, top_k: Optional[torch.Tensor] = None,
+           top_p: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Token per row of bf16 logits [B, V]: greedy where temperature <= 0 (or None), else one Gumbel-max draw from
-    softmax(logits / T) keyed by seeds[b] (b2_sample).  Returns int64 [B]."""
+    softmax(logits / T) keyed by seeds[b], restricted to the top_k[b] largest logits (int32 [B]; <= 0: no limit) and then
+    to the smallest top set holding top_p[b] of that mass (fp32 [B]; >= 1: no limit) -- b2_sample_filtered.
+    Returns int64 [B]."""
     lib = _lib.load()
-    dev = _need_cuda(logits=logits, temperature=temperature, seeds=seeds, out=out)
+    dev = _need_cuda(logits=logits, temperature=temperature, seeds=seeds, out=out, top_k=top_k, top_p=top_p)
     B, V, st = _rows(logits, "logits")
     if temperature is not None and (temperature.dtype != torch.float32 or temperature.shape != (B,)
                                     or not temperature.is_contiguous()):
@@ -491,5 +494,10 @@ def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, see
         out = torch.empty(B, dtype=torch.int64, device=dev)
     elif out.dtype != torch.int64 or out.shape != (B,) or not out.is_contiguous():
         raise ValueError("out must be a contiguous int64 [B]")
-    _lib.check(lib.b2_sample(_ptr(out), _ptr(logits), B, V, st, _ptr(temperature), _ptr(seeds), _stream(dev)))
+    if top_k is not None and (top_k.dtype != torch.int32 or top_k.shape != (B,) or not top_k.is_contiguous()):
+        raise ValueError("top_k must be a contiguous int32 [B]")
+    if top_p is not None and (top_p.dtype != torch.float32 or top_p.shape != (B,) or not top_p.is_contiguous()):
+        raise ValueError("top_p must be a contiguous fp32 [B]")
+    _lib.check(lib.b2_sample_filtered(_ptr(out), _ptr(logits), B, V, st, _ptr(temperature), _ptr(seeds), _ptr(top_k),
+                                      _ptr(top_p), _stream(dev)))
     return out

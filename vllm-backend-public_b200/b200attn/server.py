@@ -188,11 +188,10 @@ def sampling_from_body(body: Dict[str, Any], default_max_tokens: int = 16):
     max_tokens = num("max_tokens", body.get("max_completion_tokens", default_max_tokens), int, 1)
     temperature = num("temperature", 1.0, float, 0.0, 100.0)
     top_p = num("top_p", 1.0, float, 0.0, 1.0)
+    top_k = num("top_k", 0, int, -1)                      # vLLM extension of the OpenAI body: -1 / 0 = no limit
     n = num("n", 1, int, 1, 64)
-    if top_p < 1.0 and temperature > 0:
-        # nucleus truncation is not implemented by b2_sample: say so instead of silently sampling something else
-        raise ApiError(400, "top_p < 1 is not supported by this engine (use temperature, or temperature=0 for greedy)",
-                       param="top_p")
+    if top_p <= 0.0:
+        raise ApiError(400, "top_p must be in (0, 1]", param="top_p")
     seed = body.get("seed")
     if seed is not None and (isinstance(seed, bool) or not isinstance(seed, int)):
         raise ApiError(400, "seed must be an integer", param="seed")
@@ -206,7 +205,7 @@ def sampling_from_body(body: Dict[str, Any], default_max_tokens: int = 16):
     stop_ids = body.get("stop_token_ids") or []
     if not (isinstance(stop_ids, list) and all(isinstance(t, int) for t in stop_ids)):
         raise ApiError(400, "stop_token_ids must be a list of integers", param="stop_token_ids")
-    sp = SamplingParams(max_tokens=max_tokens, temperature=temperature, seed=seed,
+    sp = SamplingParams(max_tokens=max_tokens, temperature=temperature, top_k=max(top_k, 0), top_p=top_p, seed=seed,
                         ignore_eos=bool(body.get("ignore_eos", False)), stop_token_ids=tuple(stop_ids))
     return sp, n, stop
 

@@ -274,22 +274,25 @@ __device__ __forceinline__ uint32_t hash_u32(uint64_t seed, uint32_t idx) {
     return (uint32_t)(z >> 40);                                          // 24 bits
 }
 
-__global__ void __launch_bounds__(1024)
-sample_kernel(int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ logits, int V, int64_t stride,
-              const float* __restrict__ temperature, const int64_t* __restrict__ seeds) {
-    const int b = blockIdx.x;
-    const float T = temperature ? temperature[b] : 0.f;
-    const uint64_t seed = seeds ? (uint64_t)seeds[b] : 0ull;
-    const __nv_bfloat16* row = logits + b * stride;
+// order-preserving 16-bit key of a bf16 bit pattern: key(a) < key(b)  <=>  a < b  (-0 < +0; NaN sorts outside)
+__device__ __forceinline__ uint32_t bf16_key(uint32_t u) { return (u & 0x8000u) ? (~u & 0xffffu) : (u | 0x8000u); }
+
+// argmax over the row of (logit / T + Gumbel noise) [T > 0] or of the logit [T <= 0], restricted to keys >= min_key
+// (0 = every token); lowest index among equal maxima.  Every thread returns; thread 0 holds the result.
+__device__ __forceinline__ int sample_row(const __nv_bfloat16* __restrict__ row, int V, float T, uint64_t seed,
+                                          uint32_t min_key) {
     float best = -INFINITY;
     int best_i = 0x7fffffff;
     const float invT = T > 0.f ? 1.f / T : 1.f;
     for (int v = threadIdx.x; v < (V >> 3); v += blockDim.x) {
+        const int4 raw = b2::ld_nc_16(row + v * 8);
         float f[8];
-        unpack8(b2::ld_nc_16(row + v * 8), f);
+        unpack8(raw, f);
+        const uint32_t w[4] = {(uint32_t)raw.x, (uint32_t)raw.y, (uint32_t)raw.z, (uint32_t)raw.w};
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int idx = v * 8 + j;
+            if (min_key && bf16_key((j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xffffu)) < min_key) continue;
             float s = f[j];
             if (T > 0.f) {
                 const float u = ((float)hash_u32(seed, (uint32_t)idx) + 0.5f) * (1.f / 16777216.f);
@@ -299,6 +302,7 @@ sample_kernel(int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ lo
         }
     }
     for (int idx = (V & ~7) + threadIdx.x; idx < V; idx += blockDim.x) {     // tail (V not a multiple of 8)
+        if (min_key && bf16_key((uint32_t)__bfloat16_as_ushort(row[idx])) < min_key) continue;
         float s = __bfloat162float(row[idx]);
         if (T > 0.f) {
             const float u = ((float)hash_u32(seed, (uint32_t)idx) + 0.5f) * (1.f / 16777216.f);
@@ -314,6 +318,7 @@ sample_kernel(int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ lo
     }
     __shared__ float sb[32];
     __shared__ int si[32];
+    __syncthreads();                                   // sb / si may still be read by an earlier call
     if ((threadIdx.x & 31) == 0) { sb[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = best_i; }
     __syncthreads();
     if (threadIdx.x < 32) {
@@ -326,8 +331,108 @@ sample_kernel(int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ lo
             const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
             if (ob > best || (ob == best && oi < best_i)) { best = ob; best_i = oi; }
         }
-        if (threadIdx.x == 0) tokens[b] = best_i == 0x7fffffff ? 0 : best_i;
     }
+    return best_i == 0x7fffffff ? 0 : best_i;
+}
+
+// block-wide sums of (count, mass) over the tokens with key in [lo_key, 65535] and key >= t_key;
+// mass_i = exp2((logit_i - m) * c).  Fixed reduction order: the same bits on every launch.
+__device__ __forceinline__ void measure_ge(const __nv_bfloat16* __restrict__ row, int V, uint32_t t_key, float m, float c,
+                                           bool want_mass, int& count, float& mass) {
+    int cnt = 0;
+    float ms = 0.f;
+    for (int v = threadIdx.x; v < (V >> 3); v += blockDim.x) {
+        const int4 raw = b2::ld_nc_16(row + v * 8);
+        const uint32_t w[4] = {(uint32_t)raw.x, (uint32_t)raw.y, (uint32_t)raw.z, (uint32_t)raw.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t u = (j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xffffu);
+            if (bf16_key(u) >= t_key && (u & 0x7f80u) != 0x7f80u) {            // not inf / NaN
+                ++cnt;
+                if (want_mass) ms += b2::fast_exp2((__uint_as_float(u << 16) - m) * c);
+            }
+        }
+    }
+    for (int idx = (V & ~7) + threadIdx.x; idx < V; idx += blockDim.x) {
+        const uint32_t u = __bfloat16_as_ushort(row[idx]);
+        if (bf16_key(u) >= t_key && (u & 0x7f80u) != 0x7f80u) {
+            ++cnt;
+            if (want_mass) ms += b2::fast_exp2((__uint_as_float(u << 16) - m) * c);
+        }
+    }
+    __shared__ int rc[32];
+    __shared__ float rm[32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        ms += __shfl_xor_sync(0xffffffffu, ms, o);
+    }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) { rc[threadIdx.x >> 5] = cnt; rm[threadIdx.x >> 5] = ms; }
+    __syncthreads();
+    cnt = 0;
+    ms = 0.f;
+    const int nw = blockDim.x >> 5;
+    for (int i = 0; i < nw; ++i) { cnt += rc[i]; ms += rm[i]; }
+    count = cnt;
+    mass = ms;
+}
+
+__global__ void __launch_bounds__(1024)
+sample_kernel(int64_t* __restrict__ tokens, const __nv_bfloat16* __restrict__ logits, int V, int64_t stride,
+              const float* __restrict__ temperature, const int64_t* __restrict__ seeds,
+              const int32_t* __restrict__ top_k, const float* __restrict__ top_p) {
+    const int b = blockIdx.x;
+    const float T = temperature ? temperature[b] : 0.f;
+    const uint64_t seed = seeds ? (uint64_t)seeds[b] : 0ull;
+    const __nv_bfloat16* row = logits + b * stride;
+    const int k = top_k ? top_k[b] : 0;
+    const float p = top_p ? top_p[b] : 1.f;
+    uint32_t min_key = 0;
+    if (T > 0.f && ((k > 0 && k < V) || p < 1.f)) {
+        // the candidate set is {key >= t}: t = the k-th largest logit (ties kept), then raised to the smallest set of
+        // top logits whose softmax mass reaches p of the top-k mass (ties kept).  Both by bisection over the 16-bit key
+        // space: 16 passes over the row (L2 resident) each.
+        uint32_t lo = 0, hi = 65536;
+        int cnt;
+        float mass;
+        if (k > 0 && k < V) {
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                measure_ge(row, V, mid, 0.f, 0.f, false, cnt, mass);
+                if (cnt >= k) lo = mid; else hi = mid;
+            }
+        }
+        min_key = lo;
+        if (p < 1.f) {
+            // row maximum (finite values) for a stable exponent
+            float mx = -INFINITY;
+            for (int idx = threadIdx.x; idx < V; idx += blockDim.x) {
+                const float x = __bfloat162float(row[idx]);
+                if (x > mx && x < INFINITY) mx = x;
+            }
+            __shared__ float smx[32];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            if ((threadIdx.x & 31) == 0) smx[threadIdx.x >> 5] = mx;
+            __syncthreads();
+            mx = smx[0];
+            for (int i = 1; i < (int)(blockDim.x >> 5); ++i) mx = fmaxf(mx, smx[i]);
+            const float c = 1.4426950408889634f / T;
+            measure_ge(row, V, min_key, mx, c, true, cnt, mass);
+            const float target = p * mass;
+            lo = min_key;
+            hi = 65536;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                measure_ge(row, V, mid, mx, c, true, cnt, mass);
+                if (mass >= target && cnt > 0) lo = mid; else hi = mid;
+            }
+            min_key = lo;
+        }
+    }
+    const int tok = sample_row(row, V, T, seed, min_key);
+    if (threadIdx.x == 0) tokens[b] = tok;
 }
 
 }  // namespace
@@ -422,12 +527,19 @@ extern "C" int b2_rope_and_cache(void* qkv, const int32_t* positions, const floa
 
 extern "C" int b2_sample(int64_t* tokens, const void* logits, int B, int V, int64_t stride, const float* temperature,
                          const int64_t* seeds, void* stream) {
+    return b2_sample_filtered(tokens, logits, B, V, stride, temperature, seeds, nullptr, nullptr, stream);
+}
+
+extern "C" int b2_sample_filtered(int64_t* tokens, const void* logits, int B, int V, int64_t stride,
+                                  const float* temperature, const int64_t* seeds, const int32_t* top_k,
+                                  const float* top_p, void* stream) {
     B2_REQUIRE(B >= 0 && V > 0, B2_EINVAL, "sample: bad sizes B=%d V=%d", B, V);
     if (B == 0) return B2_OK;
     B2_REQUIRE(tokens && logits, B2_EINVAL, "sample: null pointer");
     B2_REQUIRE(b2_aligned16(logits) && stride % 8 == 0, B2_EINVAL, "sample: logits rows must be 16-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    sample_kernel<<<B, 1024, 0, st>>>(tokens, static_cast<const __nv_bfloat16*>(logits), V, stride, temperature, seeds);
+    sample_kernel<<<B, 1024, 0, st>>>(tokens, static_cast<const __nv_bfloat16*>(logits), V, stride, temperature, seeds,
+                                      top_k, top_p);
     B2_CUDA_OK(cudaGetLastError());
     return B2_OK;
 }
