@@ -318,7 +318,7 @@ def test_sample_top_k_top_p(cuda):
 
 
 def test_sample_top_p_distribution(cuda):
-    """Draws under top_p follow the renormalised nucleus: p = 0.8 over softmax([2, 1.5, 1, .5, 0, -1]) keeps 4 tokens."""
+    """Draws under top_p follow the renormalised nucleus: p = 0.8 over softmax([2, 1.5, 1, .5, 0, -1]) keeps 3 tokens (0.83)."""
     logits = torch.tensor([2.0, 1.0, 0.0, -1.0, 0.5, 1.5, -30.0, -30.0]).to(torch.bfloat16)
     N, V = 20000, 8
     rows = logits.unsqueeze(0).repeat(N, 1).contiguous()
@@ -329,4 +329,4 @@ def test_sample_top_p_distribution(cuda):
     p = torch.softmax(logits.float(), 0) * keep
     p = p / p.sum()
     freq = torch.bincount(got, minlength=V).float() / N
-    assert int(keep.sum()) == 4 and (freq[~keep] == 0).all() and (freq - p).abs().max() < 0.015
+    assert int(keep.sum()) == 3 and (freq[~keep] == 0).all() and (freq - p).abs().max() < 0.015
