@@ -68,6 +68,8 @@ class EngineStats:
     busy_s: float = 0.0
     device_ms: float = 0.0          # CUDA-event time of the decode-step replays (only with engine.time_device)
     device_steps: int = 0
+    sync_wait_s: float = 0.0        # part of busy_s spent waiting for the GPU (stream synchronize): busy - wait = host work
+    mixed_busy_s: float = 0.0
 
 
 def _buckets(max_batch: int) -> List[int]:
@@ -227,7 +229,9 @@ class LLMEngine:
         s = self.stats
         self.metrics = {"running": self.sched.num_running, "waiting": self.sched.num_waiting,
                         "free_blocks": self.sched.num_free_blocks, "prompt_tokens": s.prompt_tokens,
-                        "generated_tokens": s.generated_tokens, "steps": s.steps, "preemptions": s.preemptions}
+                        "generated_tokens": s.generated_tokens, "steps": s.steps, "preemptions": s.preemptions,
+                        "mixed_steps": s.mixed_steps, "busy_s": round(s.busy_s, 4), "sync_wait_s": round(s.sync_wait_s, 4),
+                        "mixed_busy_s": round(s.mixed_busy_s, 4)}
 
     # ------------------------------------------------------------------------------------ one step
     def _admit(self) -> None:
@@ -296,8 +300,10 @@ class LLMEngine:
             sampled_rows, tokens = self._run_decode(plan)
             self.stats.decode_steps += 1
         else:
+            tm = time.perf_counter()
             sampled_rows, tokens = self._run_mixed(plan)
             self.stats.mixed_steps += 1
+            self.stats.mixed_busy_s += time.perf_counter() - tm
         now = time.perf_counter()
         out: List[Tuple[Request, int]] = []
         for r, tok in zip(sampled_rows, tokens):
@@ -389,7 +395,9 @@ class LLMEngine:
             if self.time_device:
                 self._ev[1].record(self._stream)
             self._h_out[:bucket].copy_(self._d_out[:bucket], non_blocking=True)
+        tw = time.perf_counter()
         self._stream.synchronize()
+        self.stats.sync_wait_s += time.perf_counter() - tw
         if self.time_device:
             self.stats.device_ms += self._ev[0].elapsed_time(self._ev[1])
             self.stats.device_steps += 1
@@ -467,7 +475,9 @@ class LLMEngine:
             if ns:
                 out = ops.sample(logits, d_temp[:ns], d_aux[:ns], top_k=d_topk[:ns], top_p=d_temp[B:B + ns])
                 self._h_out[:ns].copy_(out, non_blocking=True)
+        tw = time.perf_counter()
         self._stream.synchronize()
+        self.stats.sync_wait_s += time.perf_counter() - tw
         self.stats.gpu_launches += self.cfg.layers * (self._launches_per_layer + 1) + 3
         return sample_reqs, (self._h_out[:ns].tolist() if ns else [])
 

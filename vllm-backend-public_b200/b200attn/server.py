@@ -57,6 +57,7 @@ class EngineRunner:
             try:
                 if self.engine is not None and self.failed is None:
                     self.engine.shutdown_workers()
+                    self.engine.close()              # the workers close too: the barrier inside must be matched
             except Exception:
                 pass
             for p in self.workers:
@@ -315,7 +316,11 @@ def create_app(runner: EngineRunner):
                       f"b200attn_num_requests_waiting {m['waiting']}",
                       f"b200attn_kv_blocks_free {m['free_blocks']}", f"b200attn_kv_blocks_total {eng.num_blocks}",
                       f"b200attn_prompt_tokens_total {m['prompt_tokens']}", f"b200attn_generation_tokens_total {m['generated_tokens']}",
-                      f"b200attn_engine_steps_total {m['steps']}", f"b200attn_preemptions_total {m['preemptions']}"]
+                      f"b200attn_engine_steps_total {m['steps']}", f"b200attn_preemptions_total {m['preemptions']}",
+                      f"b200attn_engine_mixed_steps_total {m.get('mixed_steps', 0)}",
+                      f"b200attn_engine_busy_seconds_total {m.get('busy_s', 0)}",
+                      f"b200attn_engine_gpu_wait_seconds_total {m.get('sync_wait_s', 0)}",
+                      f"b200attn_engine_mixed_step_seconds_total {m.get('mixed_busy_s', 0)}"]
         return PlainTextResponse("\n".join(lines) + "\n")
 
     def check_model(body):
