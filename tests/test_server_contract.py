@@ -73,6 +73,7 @@ class StubRunner(EngineRunner):
         while not self._stop:
             if self.engine.has_work():
                 self.engine.step()
+                self._flush_events()            # the real engine calls this through its after_step hook
             else:
                 self._wake.wait(0.01)
                 self._wake.clear()

@@ -180,6 +180,7 @@ class LLMEngine:
         self._incoming: List[Request] = []
         self._aborts: List[int] = []
         self.stats = EngineStats()
+        self.after_step: Optional[Callable[[], None]] = None    # engine thread: called once at the end of every step()
         self.metrics: Dict[str, int] = {}
         self._publish_metrics()
         torch.cuda.synchronize(self.dev)
@@ -275,6 +276,13 @@ class LLMEngine:
 
     def step(self) -> List[Tuple[Request, int]]:
         """Admit queued requests, run one scheduler plan on the GPU, return [(request, new token)]."""
+        try:
+            return self._step()
+        finally:
+            if self.after_step is not None:
+                self.after_step()
+
+    def _step(self) -> List[Tuple[Request, int]]:
         t0 = time.perf_counter()
         self._admit()
         plan = self.sched.step()

@@ -17,6 +17,7 @@ Errors use OpenAI's envelope: {"error": {"message", "type", "param", "code"}} wi
 from __future__ import annotations
 
 import asyncio
+import os
 import json
 import sys
 import threading
@@ -42,12 +43,19 @@ class EngineRunner:
         self.failed: Optional[str] = None
         self._wake = threading.Event()
         self._stop = False
-        self._thread = threading.Thread(target=self._main, name="b200attn-engine", daemon=True)
+        self._thread = threading.Thread(target=self._thread_main, name="b200attn-engine", daemon=True)
+        self._engine_tid = None
         self.t_start = time.time()
         self.workers: list = []                  # child processes of ranks 1..tp-1
+        self._events: list = []                  # (queue, token) pairs of the running step (engine thread only)
+        self._loop = None
 
     def start(self) -> None:
         self._thread.start()
+
+    def _thread_main(self) -> None:
+        self._engine_tid = threading.get_ident()
+        self._main()
 
     def stop(self) -> None:
         self._stop = True
@@ -94,6 +102,7 @@ class EngineRunner:
             self.engine = LLMEngine(cfg, torch.device("cuda", 0), weights_dir=wdir,
                                     eos_token_id=self.tokenizer.eos_token_id, tp=group, **kw)
             n = self.engine.capture_all()
+            self.engine.after_step = self._flush_events
             print(f"[b200attn] {cfg.name}: {self.engine.model.weight_bytes() / 2**30:.1f} GiB weights, "
                   f"{self.engine.num_blocks} KV blocks x {self.engine.block_size} tokens, max_model_len "
                   f"{self.engine.max_model_len}, {n} decode graphs, ready after {time.time() - self.t_start:.1f}s",
@@ -114,6 +123,7 @@ class EngineRunner:
                     r.finished, r.finish_reason = True, "error"
                     if r.on_token:
                         r.on_token(r, None)
+                self._flush_events()
                 return
             if eng.has_work():
                 try:
@@ -128,6 +138,7 @@ class EngineRunner:
                         r.finished, r.finish_reason = True, "error"
                         if r.on_token:
                             r.on_token(r, None)
+                    self._flush_events()
                     return
             else:
                 self._wake.wait(timeout=0.05)
@@ -137,11 +148,30 @@ class EngineRunner:
         q: asyncio.Queue = asyncio.Queue()
 
         def on_token(req, tok):
-            loop.call_soon_threadsafe(q.put_nowait, tok)
+            if threading.get_ident() == self._engine_tid:        # engine thread, inside step(): only collect
+                self._events.append((q, tok))
+            else:                                                # any other caller: deliver now
+                loop.call_soon_threadsafe(q.put_nowait, tok)
 
+        self._loop = loop
         req = self.engine.add_request(prompt_ids, params, on_token)
         self._wake.set()
         return req, q
+
+    def _flush_events(self) -> None:
+        """Engine thread, once per step: hand every token of the step to the event loop with ONE wake-up (a
+        call_soon_threadsafe per token costs a self-pipe write and a loop iteration each)."""
+        if self._events and self._loop is not None:
+            evs, self._events = self._events, []
+            try:
+                self._loop.call_soon_threadsafe(self._deliver, evs)
+            except RuntimeError:                     # loop already closed (shutdown)
+                pass
+
+    @staticmethod
+    def _deliver(evs) -> None:
+        for q, tok in evs:
+            q.put_nowait(tok)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -497,6 +527,10 @@ def main(argv: Optional[List[str]] = None) -> int:
         if on:
             print("[b200attn] " + note, file=sys.stderr)
     import uvicorn
+    # the engine thread and the HTTP event loop share this interpreter: a 5 ms GIL switch interval would cost the engine
+    # up to 5 ms every time it gives the lock away at a launch; and no CPU math here is worth an OpenMP pool
+    sys.setswitchinterval(1e-4)
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
     runner = EngineRunner(args, tokenizer)
     runner.start()
     app = create_app(runner)

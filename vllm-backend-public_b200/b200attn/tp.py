@@ -340,7 +340,7 @@ def launch_workers(world: int, spec: dict, master_port: int, log_dir: Optional[s
     for r in range(1, world):
         env = dict(os.environ)
         env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(world), "MASTER_ADDR": "127.0.0.1",
-                    "MASTER_PORT": str(master_port), "B200ATTN_TP_SPEC": json.dumps(spec),
+                    "MASTER_PORT": str(master_port), "B200ATTN_TP_SPEC": json.dumps(spec), "OMP_NUM_THREADS": "1",
                     "PYTHONPATH": pkg_parent + os.pathsep + env.get("PYTHONPATH", "")})
         out = None
         if log_dir:
