@@ -230,6 +230,13 @@ B2_API int b2_rope_and_cache(void* qkv, const int32_t* positions, const float* c
                       void* k_cache, void* v_cache, const int64_t* slot_mapping, int T, int Hq, int Hkv,
                       int d, int bs, int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
                       int kv_dtype, const float* k_scale, const float* v_scale, void* stream);
+/* b2_rope_and_cache with write_k = 0: the rotated K rows go to the cache only, not back into qkv (an engine that
+ * reads K only from the cache saves 2 of 26 KiB per token); q is always rotated in place.  write_k = 1 is
+ * b2_rope_and_cache. */
+B2_API int b2_rope_and_cache_ex(void* qkv, const int32_t* positions, const float* cos_sin, int max_pos,
+                      void* k_cache, void* v_cache, const int64_t* slot_mapping, int T, int Hq, int Hkv,
+                      int d, int bs, int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
+                      int kv_dtype, const float* k_scale, const float* v_scale, int write_k, void* stream);
 B2_API int b2_sample(int64_t* tokens, const void* logits, int B, int V, int64_t stride, const float* temperature,
               const int64_t* seeds, void* stream);
 /* b2_sample with the OpenAI / vLLM sampling filters (top_k int32 [B], top_p fp32 [B]; either may be NULL): for rows

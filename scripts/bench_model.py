@@ -5,6 +5,7 @@
 CUDA events on the launching stream, >= 3 warm-ups, inputs larger than L2 or L2 flushed (said per line)."""
 import argparse
 import json
+import os
 import sys
 import time
 from pathlib import Path
@@ -18,7 +19,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--skip-model", action="store_true")
 ap.add_argument("--model", default="llama-3-8b")
 ap.add_argument("--steps", type=int, default=100)
-ap.add_argument("--only", choices=["all", "prefill", "ops", "decode"], default="all")
+ap.add_argument("--only", choices=["all", "prefill", "ops", "decode", "gemm"], default="all")
 ap.add_argument("--batch", type=int, default=64)
 ap.add_argument("--ctx", type=int, default=4096)
 ap.add_argument("--kv", choices=["auto", "fp8"], default="auto", help="KV cache dtype of the whole-model decode run")
@@ -104,11 +105,35 @@ for T in (64, 8192) if a.only in ("all", "ops") else ():
     med, best = timeit(lambda: ops.rope_and_cache(qkv, pos, table, kc, vc, slots, Hq), flush_l2=small, reps=reps)
     byt = T * ((Hq + Hkv) * d * 2 * 2 + Hkv * d * 2 + 2 * Hkv * d * 2 + d * 4)
     emit(op="rope_and_cache", T=T, us=med * 1e3, GBps=byt / med / 1e6, frac_hbm=byt / med / 1e6 / HBM,
-         l2="flushed" if small else "working set > L2" if byt > 126e6 else "fits L2 (reported as is)")
+         l2="flushed" if small else "working set > L2" if byt > 126e6 else "fits L2 (reported as is)",
+         kernel="streaming (persistent, pipelined)" if T >= 2 * 4 * 148 and os.environ.get("B2_ROPE_IMPL", "")[:1] != "t" else "one token per CTA")
+    med, best = timeit(lambda: ops.rope_and_cache(qkv, pos, table, kc, vc, slots, Hq, write_k=False), flush_l2=small, reps=reps)
+    byt2 = byt - T * Hkv * d * 2
+    emit(op="rope_and_cache(write_k=0)", T=T, us=med * 1e3, GBps=byt2 / med / 1e6, frac_hbm=byt2 / med / 1e6 / HBM,
+         note="rotated K goes to the cache only (what the engine runs)")
 logits = torch.randn(64, 128256, device=dev).to(torch.bfloat16)
 med, best = timeit(lambda: ops.sample(logits), flush_l2=True)
 emit(op="sample(greedy)", B=64, V=128256, us=med * 1e3, GBps=64 * 128256 * 2 / med / 1e6, frac_hbm=64 * 128256 * 2 / med / 1e6 / HBM,
      l2="flushed")
+
+# ---------------------------------------------------------------- the decode-step GEMMs (cuBLAS), per rank at tp 1 / 8
+if a.only in ("all", "gemm"):
+    M, Hd, I, QKV = 64, 4096, 14336, 6144
+    for tp in (1, 2, 8):
+        for name, K, N in (("wqkv", Hd, QKV // tp), ("wo", Hd // tp, Hd), ("wgu", Hd, 2 * I // tp), ("wdown", I // tp, Hd)):
+            xg = torch.randn(M, K, device=dev).to(torch.bfloat16)
+            # 16 different weight matrices back to back (as 16 layers): the weights stream from HBM, not from L2
+            ws = [torch.randn(N, K, device=dev).to(torch.bfloat16) for _ in range(16)]
+            og = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+
+            def run():
+                for wgt in ws:
+                    torch.mm(xg, wgt.t(), out=og)
+            med, best = timeit(run, iters=20)
+            byt = N * K * 2 + M * K * 2 + M * N * 2
+            emit(op="decode_gemm", name=name, tp=tp, M=M, K=K, N=N, us=med * 1e3 / 16, GBps=byt * 16 / med / 1e6,
+                 frac_hbm=byt * 16 / med / 1e6 / HBM, note="cuBLAS via torch.mm, 16 distinct weights back to back")
+            del ws
 
 if a.skip_model:
     sys.exit(0)

@@ -233,6 +233,36 @@ def test_rope_and_cache_bit_exact(cuda, Hq, Hkv, bs, fp8):
     assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref)), "cache write must be bit-exact"
 
 
+@pytest.mark.parametrize("fp8", [False, True])
+@pytest.mark.parametrize("Hq,Hkv,write_k", [(32, 8, True), (32, 8, False), (64, 8, True), (4, 1, False)])
+def test_rope_and_cache_streaming_kernel_bit_exact(cuda, Hq, Hkv, write_k, fp8):
+    """T large enough for the persistent, software-pipelined kernel (>= 2 x 4 CTAs x SMs tokens); (64, 8) takes the
+    3-items-per-thread instantiation.  write_k=False: the k part of qkv stays as it was, the cache is the same."""
+    d, bs, T = 128, 16, 2600
+    nblk = (T + bs - 1) // bs + 8
+    g = torch.Generator().manual_seed(Hq)
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * d, generator=g).to(torch.bfloat16)
+    pos = torch.randint(0, 5000, (T,), generator=g, dtype=torch.int32)
+    slots = torch.randperm(nblk * bs, generator=g)[:T].to(torch.int64)
+    slots[::11] = -1
+    table = L.rope_table(5000, d, theta=500000.0, scaling=None)
+    dt = torch.uint8 if fp8 else torch.bfloat16
+    kc_ref = torch.zeros(nblk, Hkv, bs, d, dtype=dt)
+    vc_ref = torch.zeros_like(kc_ref)
+    ks, vs = 0.013, 0.021
+    ref = L.rope_and_cache_ref(qkv, pos, table, kc_ref, vc_ref, slots, Hq, R.KV_FP8_E4M3 if fp8 else R.KV_BF16, ks, vs)
+    kc = torch.zeros(nblk, Hkv, bs, d, dtype=dt, device=cuda)
+    vc = torch.zeros_like(kc)
+    dq = qkv.to(cuda)
+    sc = dict(k_scale=torch.tensor([ks], device=cuda), v_scale=torch.tensor([vs], device=cuda)) if fp8 else {}
+    ops.rope_and_cache(dq, pos.to(cuda), table.to(cuda), kc, vc, slots.to(cuda), Hq, write_k=write_k, **sc)
+    want = ref.clone()
+    if not write_k:
+        want.view(T, Hq + 2 * Hkv, d)[:, Hq:Hq + Hkv] = qkv.view(T, Hq + 2 * Hkv, d)[:, Hq:Hq + Hkv]
+    assert torch.equal(bits(dq), bits(want)), "rotated q (and k when asked) must be bit-exact"
+    assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref)), "cache write must be bit-exact"
+
+
 def test_sample_greedy_exact(cuda):
     g = torch.Generator().manual_seed(0)
     logits = torch.randn(9, 128256, generator=g).to(torch.bfloat16)

@@ -307,7 +307,8 @@ class LlamaModel:
         for l in range(c.layers):
             qkv = torch.nn.functional.linear(x, w[f"l{l}.wqkv"], w.get(f"l{l}.bqkv"))
             kc, vc = self.kv[l, 0], self.kv[l, 1]
-            ops.rope_and_cache(qkv, positions, self.cos_sin, kc, vc, slots, Hq, self.k_scale, self.v_scale)
+            ops.rope_and_cache(qkv, positions, self.cos_sin, kc, vc, slots, Hq, self.k_scale, self.v_scale,
+                               write_k=False)          # K is read from the cache only
             q = qkv.view(T, Hq + 2 * Hkv, c.d)[:, :Hq]
             if n_decode:
                 if self._plans is not None and n_decode <= self._plan_shape[0] \

@@ -449,9 +449,11 @@ def silu_and_mul(gate_up: torch.Tensor, out: Optional[torch.Tensor] = None) -> t
 
 def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_sin: torch.Tensor, k_cache: torch.Tensor,
                    v_cache: torch.Tensor, slot_mapping: torch.Tensor, Hq: int,
-                   k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None) -> None:
+                   k_scale: Optional[torch.Tensor] = None, v_scale: Optional[torch.Tensor] = None,
+                   write_k: bool = True) -> None:
     """Neox rotary on the q and k parts of qkv [T, (Hq + 2 Hkv) * d] in place, then K', V into the paged cache
-    through slot_mapping (b2_rope_and_cache).  cos_sin: fp32 [max_pos, d] = cos | sin halves per position."""
+    through slot_mapping (b2_rope_and_cache_ex).  cos_sin: fp32 [max_pos, d] = cos | sin halves per position.
+    write_k=False leaves the k part of qkv unrotated (the rotated rows go to the cache only)."""
     lib = _lib.load()
     dev = _need_cuda(qkv=qkv, positions=positions, cos_sin=cos_sin, k_cache=k_cache, v_cache=v_cache,
                      slot_mapping=slot_mapping, k_scale=k_scale, v_scale=v_scale)
@@ -470,9 +472,9 @@ def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_sin: torch.Te
         for s in (k_scale, v_scale):
             if s is None or s.dtype != torch.float32 or s.numel() != 1:
                 raise ValueError("fp8 KV cache needs 1-element fp32 device tensors k_scale / v_scale")
-    _lib.check(lib.b2_rope_and_cache(_ptr(qkv), _ptr(positions), _ptr(cos_sin), cos_sin.shape[0], _ptr(k_cache),
-                                     _ptr(v_cache), _ptr(slot_mapping), T, Hq, Hkv, d, bs, ts, bstride, hstride, kvd,
-                                     _ptr(k_scale), _ptr(v_scale), _stream(dev)))
+    _lib.check(lib.b2_rope_and_cache_ex(_ptr(qkv), _ptr(positions), _ptr(cos_sin), cos_sin.shape[0], _ptr(k_cache),
+                                        _ptr(v_cache), _ptr(slot_mapping), T, Hq, Hkv, d, bs, ts, bstride, hstride, kvd,
+                                        _ptr(k_scale), _ptr(v_scale), 1 if write_k else 0, _stream(dev)))
 
 
 def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, seeds: Optional[torch.Tensor] = None,

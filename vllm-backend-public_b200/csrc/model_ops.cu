@@ -12,6 +12,8 @@
 // All are byte movers: 16-byte vector loads/stores, fp32 math, one rounding to bf16 on the way out.
 #include "b2_common.cuh"
 
+#include <stdlib.h>
+
 namespace {
 
 __device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
@@ -262,6 +264,148 @@ rope_and_cache_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------
+// Streaming form of the same op (the default for T >= 2 x grid): a persistent grid, each CTA walks tokens
+// t, t + grid, ... with a two-deep software pipeline -- the q|k|v row of the NEXT token, its slot, the position of the
+// token after it and (warp 0) the next token's cos/sin row are all in flight while the current token is rotated and
+// stored.  One token per CTA (the kernel above) keeps a CTA's 12 KiB of loads in flight only for the first third of
+// its life: 4.6 TB/s at 8k tokens.  write_k = 0 skips the in-place store of the rotated K rows (an engine that reads
+// K only from the cache does not need them: 2 of 26 KiB per token).
+// ---------------------------------------------------------------------------------------------
+template <bool FP8, int ITEMS>
+__global__ void __launch_bounds__(256, ITEMS == 2 ? 4 : 3)
+rope_and_cache_stream_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ positions,
+                             const float* __restrict__ cos_sin, int max_pos, void* __restrict__ k_cache,
+                             void* __restrict__ v_cache, const int64_t* __restrict__ slot_mapping, int T, int Hq, int Hkv,
+                             int d, int bs, int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
+                             const float* __restrict__ k_scale, const float* __restrict__ v_scale, int write_k) {
+    __shared__ __align__(16) float cs_s[2][256];           // cos | sin row of the current / next token (d <= 256)
+    const int half = d >> 1;
+    const int pairs_per_head = half >> 3;
+    const int vec_per_head = d >> 3;
+    const int n_rot = (Hq + Hkv) * pairs_per_head;
+    const int n_items = n_rot + Hkv * vec_per_head;
+    // what this thread's items are does not depend on the token: decode them once
+    int src[ITEMS], hd[ITEMS], cc[ITEMS];                   // element offset in the row, head (k/v: cache head), vector column
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+        const int i = threadIdx.x + k * blockDim.x;
+        if (i < n_rot) {
+            const int h = i / pairs_per_head, c = i - h * pairs_per_head;
+            src[k] = h * d + c * 8; hd[k] = h; cc[k] = c;
+        } else if (i < n_items) {
+            const int j = i - n_rot;
+            src[k] = (Hq + Hkv) * d + j * 8; hd[k] = j / vec_per_head; cc[k] = j - hd[k] * vec_per_head;
+        } else {
+            src[k] = -1; hd[k] = 0; cc[k] = 0;
+        }
+    }
+    float ks = 1.f, vs = 1.f;
+    if (FP8) { ks = *k_scale; vs = *v_scale; }
+
+    int t = blockIdx.x;
+    if (t >= T) return;
+    const int step = gridDim.x;
+    int4 xa[ITEMS], xb[ITEMS];
+    auto load_row = [&](int tok, int4 (&a)[ITEMS], int4 (&b)[ITEMS]) {
+        const __nv_bfloat16* row = qkv + tok * token_stride;
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) {
+            const int i = threadIdx.x + k * blockDim.x;
+            a[k] = b[k] = make_int4(0, 0, 0, 0);
+            if (src[k] >= 0) {
+                a[k] = *reinterpret_cast<const int4*>(row + src[k]);
+                if (i < n_rot) b[k] = *reinterpret_cast<const int4*>(row + src[k] + half);
+            }
+        }
+    };
+    const int nload = d >> 2;                               // float4 loads that cover one cos|sin row
+    auto load_cs = [&](int pos) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if ((int)threadIdx.x < nload) {
+            const int p = min(max(pos, 0), max_pos - 1);
+            v = *reinterpret_cast<const float4*>(cos_sin + (int64_t)p * d + threadIdx.x * 4);
+        }
+        return v;
+    };
+    // prologue: token t entirely, position of t + step
+    load_row(t, xa, xb);
+    int64_t slot = slot_mapping[t];
+    {
+        const float4 v = load_cs(positions[t]);
+        if ((int)threadIdx.x < nload) *reinterpret_cast<float4*>(&cs_s[0][threadIdx.x * 4]) = v;
+    }
+    int npos = t + step < T ? positions[t + step] : 0;
+    int buf = 0;
+    for (; t < T; t += step) {
+        const int tn = t + step;
+        int4 na[ITEMS], nb[ITEMS];
+        int64_t nslot = -1;
+        int p2 = 0;
+        float4 ncs = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tn < T) {                                       // everything the next iteration needs goes out now
+            load_row(tn, na, nb);
+            nslot = slot_mapping[tn];
+            ncs = load_cs(npos);
+            if (tn + step < T) p2 = positions[tn + step];
+        }
+        __syncthreads();                                    // cs_s[buf] is complete
+        const float* cs = cs_s[buf];
+        int64_t blk = 0;
+        int off = 0;
+        if (slot >= 0) {
+            if (slot < (int64_t)0x7fffffff) {
+                const uint32_t s32 = (uint32_t)slot;
+                blk = s32 / (uint32_t)bs;
+                off = (int)(s32 - (uint32_t)blk * (uint32_t)bs);
+            } else {
+                blk = slot / bs;
+                off = (int)(slot - blk * bs);
+            }
+        }
+        __nv_bfloat16* row = qkv + t * token_stride;
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) {
+            const int i = threadIdx.x + k * blockDim.x;
+            if (i < n_rot) {
+                const int h = hd[k], c = cc[k];
+                float x1[8], x2[8], co[8], si[8], o1[8], o2[8];
+                unpack8(xa[k], x1);
+                unpack8(xb[k], x2);
+                *reinterpret_cast<float4*>(co) = *reinterpret_cast<const float4*>(cs + c * 8);
+                *reinterpret_cast<float4*>(co + 4) = *reinterpret_cast<const float4*>(cs + c * 8 + 4);
+                *reinterpret_cast<float4*>(si) = *reinterpret_cast<const float4*>(cs + half + c * 8);
+                *reinterpret_cast<float4*>(si + 4) = *reinterpret_cast<const float4*>(cs + half + c * 8 + 4);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    o1[j] = __fsub_rn(__fmul_rn(x1[j], co[j]), __fmul_rn(x2[j], si[j]));
+                    o2[j] = __fadd_rn(__fmul_rn(x2[j], co[j]), __fmul_rn(x1[j], si[j]));
+                }
+                if (h < Hq || write_k) {
+                    *reinterpret_cast<int4*>(row + src[k]) = pack8(o1);
+                    *reinterpret_cast<int4*>(row + src[k] + half) = pack8(o2);
+                }
+                if (h >= Hq && slot >= 0) {
+                    const int64_t e = blk * cache_block_stride + (int64_t)(h - Hq) * cache_head_stride + (int64_t)off * d + c * 8;
+                    store_cache8<FP8>(k_cache, e, o1, ks);
+                    store_cache8<FP8>(k_cache, e + half, o2, ks);
+                }
+            } else if (i < n_items && slot >= 0) {
+                float f[8];
+                unpack8(xa[k], f);
+                const int64_t e = blk * cache_block_stride + (int64_t)hd[k] * cache_head_stride + (int64_t)off * d + cc[k] * 8;
+                store_cache8<FP8>(v_cache, e, f, vs);
+            }
+        }
+        if (tn < T && (int)threadIdx.x < nload) *reinterpret_cast<float4*>(&cs_s[buf ^ 1][threadIdx.x * 4]) = ncs;
+#pragma unroll
+        for (int k = 0; k < ITEMS; ++k) { xa[k] = na[k]; xb[k] = nb[k]; }
+        slot = nslot;
+        npos = p2;
+        buf ^= 1;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // token choice: one CTA per row of bf16 logits [B, V].
 //   temperature[b] <= 0: argmax (lowest index among equal maxima)
 //   else: argmax of logit / T + g, g = -log(-log(u)), u from a counter hash of (seed[b], index)   (Gumbel-max)
@@ -497,6 +641,15 @@ extern "C" int b2_rope_and_cache(void* qkv, const int32_t* positions, const floa
                                  int d, int bs, int64_t token_stride, int64_t cache_block_stride,
                                  int64_t cache_head_stride, int kv_dtype, const float* k_scale, const float* v_scale,
                                  void* stream) {
+    return b2_rope_and_cache_ex(qkv, positions, cos_sin, max_pos, k_cache, v_cache, slot_mapping, T, Hq, Hkv, d, bs,
+                                token_stride, cache_block_stride, cache_head_stride, kv_dtype, k_scale, v_scale, 1, stream);
+}
+
+extern "C" int b2_rope_and_cache_ex(void* qkv, const int32_t* positions, const float* cos_sin, int max_pos,
+                                 void* k_cache, void* v_cache, const int64_t* slot_mapping, int T, int Hq, int Hkv,
+                                 int d, int bs, int64_t token_stride, int64_t cache_block_stride,
+                                 int64_t cache_head_stride, int kv_dtype, const float* k_scale, const float* v_scale,
+                                 int write_k, void* stream) {
     B2_REQUIRE(T >= 0 && Hq > 0 && Hkv > 0 && d > 0 && bs > 0 && max_pos > 0, B2_EINVAL,
                "rope_and_cache: bad sizes T=%d Hq=%d Hkv=%d d=%d bs=%d", T, Hq, Hkv, d, bs);
     if (T == 0) return B2_OK;
@@ -513,6 +666,30 @@ extern "C" int b2_rope_and_cache(void* qkv, const int32_t* positions, const floa
     if (kv_dtype == B2_KV_FP8_E4M3) B2_REQUIRE(k_scale && v_scale, B2_EINVAL, "rope_and_cache: fp8 needs scales");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     auto* p = static_cast<__nv_bfloat16*>(qkv);
+    // streaming kernel: persistent grid of 4 CTAs per SM, when there are tokens enough to pipeline and the row fits
+    // ITEMS x 256 work items; B2_ROPE_IMPL=token forces the one-token-per-CTA kernel (A/B)
+    static const int sm_count = [] {
+        int dev = 0, n = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        return n;
+    }();
+    static const bool force_token = [] { const char* e = getenv("B2_ROPE_IMPL"); return e && e[0] == 't'; }();
+    const int n_items = (Hq + Hkv) * (d / 16) + Hkv * (d / 8);
+    const int grid = sm_count * (n_items <= 512 ? 4 : 3);
+    if (!force_token && d <= 256 && T >= 2 * grid && n_items <= 3 * 256) {
+#define B2_ROPE_STREAM(FP8, ITEMS)                                                                                    \
+        rope_and_cache_stream_kernel<FP8, ITEMS><<<grid, 256, 0, st>>>(                                                \
+            p, positions, cos_sin, max_pos, k_cache, v_cache, slot_mapping, T, Hq, Hkv, d, bs, token_stride,           \
+            cache_block_stride, cache_head_stride, k_scale, v_scale, write_k)
+        if (kv_dtype == B2_KV_BF16) {
+            if (n_items <= 512) B2_ROPE_STREAM(false, 2); else B2_ROPE_STREAM(false, 3);
+        } else {
+            if (n_items <= 512) B2_ROPE_STREAM(true, 2); else B2_ROPE_STREAM(true, 3);
+        }
+#undef B2_ROPE_STREAM
+        B2_CUDA_OK(cudaGetLastError());
+        return B2_OK;
+    }
     if (kv_dtype == B2_KV_BF16)
         rope_and_cache_kernel<false><<<T, 256, 0, st>>>(p, positions, cos_sin, max_pos, k_cache, v_cache, slot_mapping, Hq, Hkv, d,
                                                         bs, token_stride, cache_block_stride, cache_head_stride,
