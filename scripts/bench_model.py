@@ -100,13 +100,18 @@ for T in (64, 8192) if a.only in ("all", "ops") else ():
     kc = torch.zeros(nblk, Hkv, bs, d, device=dev, dtype=torch.bfloat16)
     vc = torch.zeros_like(kc)
     pos = torch.arange(T, device=dev, dtype=torch.int32)
-    slots = torch.randperm(nblk * bs, device=dev)[:T].to(torch.int64)
+    if small:     # a decode step: every token in another block
+        slots = torch.randperm(nblk * bs, device=dev)[:T].to(torch.int64)
+    else:         # a prompt chunk: tokens fill 16-token blocks in order, the blocks are scattered over the pool
+        blocks = torch.randperm(nblk, device=dev)
+        ar = torch.arange(T, device=dev)
+        slots = (blocks[ar // bs] * bs + ar % bs).to(torch.int64)
     table = torch.randn(max(T, 64), d, device=dev)
     med, best = timeit(lambda: ops.rope_and_cache(qkv, pos, table, kc, vc, slots, Hq), flush_l2=small, reps=reps)
     byt = T * ((Hq + Hkv) * d * 2 * 2 + Hkv * d * 2 + 2 * Hkv * d * 2 + d * 4)
     emit(op="rope_and_cache", T=T, us=med * 1e3, GBps=byt / med / 1e6, frac_hbm=byt / med / 1e6 / HBM,
          l2="flushed" if small else "working set > L2" if byt > 126e6 else "fits L2 (reported as is)",
-         kernel="streaming (persistent, pipelined)" if T >= 2 * 4 * 148 and os.environ.get("B2_ROPE_IMPL", "")[:1] != "t" else "one token per CTA")
+         kernel="streaming (persistent grid, shared-memory ring fed by bulk copies)" if T >= 2 * 4 * 148 and os.environ.get("B2_ROPE_IMPL", "")[:1] != "t" else "one token per CTA")
     med, best = timeit(lambda: ops.rope_and_cache(qkv, pos, table, kc, vc, slots, Hq, write_k=False), flush_l2=small, reps=reps)
     byt2 = byt - T * Hkv * d * 2
     emit(op="rope_and_cache(write_k=0)", T=T, us=med * 1e3, GBps=byt2 / med / 1e6, frac_hbm=byt2 / med / 1e6 / HBM,

@@ -17,9 +17,14 @@ cs = rope_table(T, d, 500000.0, None, dev)
 nb = T // bs
 kc = torch.zeros(nb, Hkv, bs, d, dtype=torch.bfloat16, device=dev)
 vc = torch.zeros_like(kc)
-slots = torch.randperm(T, device=dev).to(torch.int64)
+import os
+if os.environ.get("SLOTS", "prefill") == "random":
+    slots = torch.randperm(T, device=dev).to(torch.int64)                      # every token in another block (worst case)
+else:   # a prompt chunk: tokens fill 16-token blocks in order, the blocks are scattered over the pool
+    blocks = torch.randperm(nb, device=dev)
+    slots = (blocks[torch.arange(T, device=dev) // bs] * bs + torch.arange(T, device=dev) % bs).to(torch.int64)
 for _ in range(3):
     ops.rms_norm(x, w, 1e-5, residual=res)
-    ops.rope_and_cache(qkv, pos, cs, kc, vc, slots, Hq)
+    ops.rope_and_cache(qkv, pos, cs, kc, vc, slots, Hq, write_k=os.environ.get("WRITE_K", "1") == "1")
 torch.cuda.synchronize()
 print("ok")

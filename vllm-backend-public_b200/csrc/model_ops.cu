@@ -264,92 +264,84 @@ rope_and_cache_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------
-// Streaming form of the same op (the default for T >= 2 x grid): a persistent grid, each CTA walks tokens
-// t, t + grid, ... with a two-deep software pipeline -- the q|k|v row of the NEXT token, its slot, the position of the
-// token after it and (warp 0) the next token's cos/sin row are all in flight while the current token is rotated and
-// stored.  One token per CTA (the kernel above) keeps a CTA's 12 KiB of loads in flight only for the first third of
-// its life: 4.6 TB/s at 8k tokens.  write_k = 0 skips the in-place store of the rotated K rows (an engine that reads
-// K only from the cache does not need them: 2 of 26 KiB per token).
+// Streaming form of the same op (the default when there are tokens enough to pipeline): a persistent grid; each CTA
+// walks tokens t, t + grid, ... through a ring of RING stages in shared memory.  A producer warp fetches the whole
+// q|k|v row of a token (12 KiB at Llama-3-8B widths) and its cos|sin row with two bulk copies (cp.async.bulk, completion
+// counted on an mbarrier) up to RING tokens ahead; the 8 consumer warps rotate out of shared memory and store.
+// Why: with one token per CTA (the kernel above) a CTA has its 12 KiB of loads in flight for only the first third of
+// its life, and ncu shows the loads taking ~3 us under the mixed read/write traffic -- 48 KiB in flight per SM is
+// 2.5 TB/s of reads.  The ring keeps up to 4 CTAs x RING x 12 KiB in flight per SM without a register per byte.
+// write_k = 0 skips the in-place store of the rotated K rows (an engine that reads K only from the cache does not need
+// them: 2 of 26 KiB per token).
 // ---------------------------------------------------------------------------------------------
-template <bool FP8, int ITEMS>
-__global__ void __launch_bounds__(256, ITEMS == 2 ? 4 : 3)
-rope_and_cache_stream_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ positions,
-                             const float* __restrict__ cos_sin, int max_pos, void* __restrict__ k_cache,
-                             void* __restrict__ v_cache, const int64_t* __restrict__ slot_mapping, int T, int Hq, int Hkv,
-                             int d, int bs, int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
-                             const float* __restrict__ k_scale, const float* __restrict__ v_scale, int write_k) {
-    __shared__ __align__(16) float cs_s[2][256];           // cos | sin row of the current / next token (d <= 256)
+constexpr int ROPE_RING = 4;
+constexpr int ROPE_CONSUMERS = 256;
+
+template <bool FP8>
+__global__ void __launch_bounds__(ROPE_CONSUMERS + 32)
+rope_and_cache_ring_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ positions,
+                           const float* __restrict__ cos_sin, int max_pos, void* __restrict__ k_cache,
+                           void* __restrict__ v_cache, const int64_t* __restrict__ slot_mapping, int T, int Hq, int Hkv,
+                           int d, int bs, int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
+                           const float* __restrict__ k_scale, const float* __restrict__ v_scale, int write_k,
+                           int stage_bytes) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bars[2 * ROPE_RING];          // full[RING] | empty[RING]
     const int half = d >> 1;
     const int pairs_per_head = half >> 3;
     const int vec_per_head = d >> 3;
     const int n_rot = (Hq + Hkv) * pairs_per_head;
     const int n_items = n_rot + Hkv * vec_per_head;
-    // what this thread's items are does not depend on the token: decode them once
-    int src[ITEMS], hd[ITEMS], cc[ITEMS];                   // element offset in the row, head (k/v: cache head), vector column
-#pragma unroll
-    for (int k = 0; k < ITEMS; ++k) {
-        const int i = threadIdx.x + k * blockDim.x;
-        if (i < n_rot) {
-            const int h = i / pairs_per_head, c = i - h * pairs_per_head;
-            src[k] = h * d + c * 8; hd[k] = h; cc[k] = c;
-        } else if (i < n_items) {
-            const int j = i - n_rot;
-            src[k] = (Hq + Hkv) * d + j * 8; hd[k] = j / vec_per_head; cc[k] = j - hd[k] * vec_per_head;
-        } else {
-            src[k] = -1; hd[k] = 0; cc[k] = 0;
+    const uint32_t row_bytes = (uint32_t)(Hq + 2 * Hkv) * d * sizeof(__nv_bfloat16);
+    const uint32_t cs_bytes = (uint32_t)d * sizeof(float);
+    // stage layout: row | cos|sin row | slot (int64)
+    const uint32_t full0 = b2::smem_u32(&bars[0]), empty0 = b2::smem_u32(&bars[ROPE_RING]);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < ROPE_RING; ++s) {
+            b2::mbar_init(full0 + 8 * s, 1);
+            b2::mbar_init(empty0 + 8 * s, ROPE_CONSUMERS / 32);
         }
+        b2::fence_mbar_init();
     }
+    __syncthreads();
+    const int first = blockIdx.x, step = gridDim.x;
+    if (first >= T) return;
+
+    if (threadIdx.x >= ROPE_CONSUMERS) {
+        // ---------------- producer warp: one lane issues the copies ----------------
+        if (threadIdx.x != ROPE_CONSUMERS) return;
+        int t = first;
+        int pos = positions[t];
+        int64_t slot = slot_mapping[t];
+        for (int j = 0; t < T; ++j, t += step) {
+            const int s = j % ROPE_RING;
+            const int tn = t + step;
+            int npos = 0;
+            int64_t nslot = -1;
+            if (tn < T) { npos = positions[tn]; nslot = slot_mapping[tn]; }      // next token's scalars under this wait
+            if (j >= ROPE_RING) b2::mbar_wait(empty0 + 8 * s, ((j / ROPE_RING) - 1) & 1);
+            unsigned char* st = smem + (size_t)s * stage_bytes;
+            *reinterpret_cast<int64_t*>(st + row_bytes + cs_bytes) = slot;
+            const int p = min(max(pos, 0), max_pos - 1);
+            b2::mbar_arrive_expect_tx(full0 + 8 * s, row_bytes + cs_bytes);      // release: the slot store is visible
+            b2::bulk_load(b2::smem_u32(st), qkv + t * token_stride, row_bytes, full0 + 8 * s);
+            b2::bulk_load(b2::smem_u32(st + row_bytes), cos_sin + (int64_t)p * d, cs_bytes, full0 + 8 * s);
+            pos = npos;
+            slot = nslot;
+        }
+        return;
+    }
+    // ---------------- consumers ----------------
     float ks = 1.f, vs = 1.f;
     if (FP8) { ks = *k_scale; vs = *v_scale; }
-
-    int t = blockIdx.x;
-    if (t >= T) return;
-    const int step = gridDim.x;
-    int4 xa[ITEMS], xb[ITEMS];
-    auto load_row = [&](int tok, int4 (&a)[ITEMS], int4 (&b)[ITEMS]) {
-        const __nv_bfloat16* row = qkv + tok * token_stride;
-#pragma unroll
-        for (int k = 0; k < ITEMS; ++k) {
-            const int i = threadIdx.x + k * blockDim.x;
-            a[k] = b[k] = make_int4(0, 0, 0, 0);
-            if (src[k] >= 0) {
-                a[k] = *reinterpret_cast<const int4*>(row + src[k]);
-                if (i < n_rot) b[k] = *reinterpret_cast<const int4*>(row + src[k] + half);
-            }
-        }
-    };
-    const int nload = d >> 2;                               // float4 loads that cover one cos|sin row
-    auto load_cs = [&](int pos) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if ((int)threadIdx.x < nload) {
-            const int p = min(max(pos, 0), max_pos - 1);
-            v = *reinterpret_cast<const float4*>(cos_sin + (int64_t)p * d + threadIdx.x * 4);
-        }
-        return v;
-    };
-    // prologue: token t entirely, position of t + step
-    load_row(t, xa, xb);
-    int64_t slot = slot_mapping[t];
-    {
-        const float4 v = load_cs(positions[t]);
-        if ((int)threadIdx.x < nload) *reinterpret_cast<float4*>(&cs_s[0][threadIdx.x * 4]) = v;
-    }
-    int npos = t + step < T ? positions[t + step] : 0;
-    int buf = 0;
-    for (; t < T; t += step) {
-        const int tn = t + step;
-        int4 na[ITEMS], nb[ITEMS];
-        int64_t nslot = -1;
-        int p2 = 0;
-        float4 ncs = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (tn < T) {                                       // everything the next iteration needs goes out now
-            load_row(tn, na, nb);
-            nslot = slot_mapping[tn];
-            ncs = load_cs(npos);
-            if (tn + step < T) p2 = positions[tn + step];
-        }
-        __syncthreads();                                    // cs_s[buf] is complete
-        const float* cs = cs_s[buf];
+    int t = first;
+    for (int j = 0; t < T; ++j, t += step) {
+        const int s = j % ROPE_RING;
+        b2::mbar_wait(full0 + 8 * s, (j / ROPE_RING) & 1);
+        const unsigned char* st = smem + (size_t)s * stage_bytes;
+        const __nv_bfloat16* srow = reinterpret_cast<const __nv_bfloat16*>(st);
+        const float* cs = reinterpret_cast<const float*>(st + row_bytes);
+        const int64_t slot = *reinterpret_cast<const int64_t*>(st + row_bytes + cs_bytes);
         int64_t blk = 0;
         int off = 0;
         if (slot >= 0) {
@@ -363,45 +355,42 @@ rope_and_cache_stream_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __r
             }
         }
         __nv_bfloat16* row = qkv + t * token_stride;
-#pragma unroll
-        for (int k = 0; k < ITEMS; ++k) {
-            const int i = threadIdx.x + k * blockDim.x;
+        for (int i = threadIdx.x; i < n_items; i += ROPE_CONSUMERS) {
             if (i < n_rot) {
-                const int h = hd[k], c = cc[k];
+                const int h = i / pairs_per_head, c = i - h * pairs_per_head;
+                const int so = h * d + c * 8;
                 float x1[8], x2[8], co[8], si[8], o1[8], o2[8];
-                unpack8(xa[k], x1);
-                unpack8(xb[k], x2);
+                unpack8(*reinterpret_cast<const int4*>(srow + so), x1);
+                unpack8(*reinterpret_cast<const int4*>(srow + so + half), x2);
                 *reinterpret_cast<float4*>(co) = *reinterpret_cast<const float4*>(cs + c * 8);
                 *reinterpret_cast<float4*>(co + 4) = *reinterpret_cast<const float4*>(cs + c * 8 + 4);
                 *reinterpret_cast<float4*>(si) = *reinterpret_cast<const float4*>(cs + half + c * 8);
                 *reinterpret_cast<float4*>(si + 4) = *reinterpret_cast<const float4*>(cs + half + c * 8 + 4);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    o1[j] = __fsub_rn(__fmul_rn(x1[j], co[j]), __fmul_rn(x2[j], si[j]));
-                    o2[j] = __fadd_rn(__fmul_rn(x2[j], co[j]), __fmul_rn(x1[j], si[j]));
+                for (int q = 0; q < 8; ++q) {
+                    o1[q] = __fsub_rn(__fmul_rn(x1[q], co[q]), __fmul_rn(x2[q], si[q]));
+                    o2[q] = __fadd_rn(__fmul_rn(x2[q], co[q]), __fmul_rn(x1[q], si[q]));
                 }
                 if (h < Hq || write_k) {
-                    *reinterpret_cast<int4*>(row + src[k]) = pack8(o1);
-                    *reinterpret_cast<int4*>(row + src[k] + half) = pack8(o2);
+                    *reinterpret_cast<int4*>(row + so) = pack8(o1);
+                    *reinterpret_cast<int4*>(row + so + half) = pack8(o2);
                 }
                 if (h >= Hq && slot >= 0) {
                     const int64_t e = blk * cache_block_stride + (int64_t)(h - Hq) * cache_head_stride + (int64_t)off * d + c * 8;
                     store_cache8<FP8>(k_cache, e, o1, ks);
                     store_cache8<FP8>(k_cache, e + half, o2, ks);
                 }
-            } else if (i < n_items && slot >= 0) {
+            } else if (slot >= 0) {
+                const int jv = i - n_rot;
+                const int h = jv / vec_per_head, c = jv - h * vec_per_head;
                 float f[8];
-                unpack8(xa[k], f);
-                const int64_t e = blk * cache_block_stride + (int64_t)hd[k] * cache_head_stride + (int64_t)off * d + cc[k] * 8;
+                unpack8(*reinterpret_cast<const int4*>(srow + (Hq + Hkv) * d + jv * 8), f);
+                const int64_t e = blk * cache_block_stride + (int64_t)h * cache_head_stride + (int64_t)off * d + c * 8;
                 store_cache8<FP8>(v_cache, e, f, vs);
             }
         }
-        if (tn < T && (int)threadIdx.x < nload) *reinterpret_cast<float4*>(&cs_s[buf ^ 1][threadIdx.x * 4]) = ncs;
-#pragma unroll
-        for (int k = 0; k < ITEMS; ++k) { xa[k] = na[k]; xb[k] = nb[k]; }
-        slot = nslot;
-        npos = p2;
-        buf ^= 1;
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) b2::mbar_arrive(empty0 + 8 * s);           // this warp is done with the stage
     }
 }
 
@@ -666,27 +655,32 @@ extern "C" int b2_rope_and_cache_ex(void* qkv, const int32_t* positions, const f
     if (kv_dtype == B2_KV_FP8_E4M3) B2_REQUIRE(k_scale && v_scale, B2_EINVAL, "rope_and_cache: fp8 needs scales");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     auto* p = static_cast<__nv_bfloat16*>(qkv);
-    // streaming kernel: persistent grid of 4 CTAs per SM, when there are tokens enough to pipeline and the row fits
-    // ITEMS x 256 work items; B2_ROPE_IMPL=token forces the one-token-per-CTA kernel (A/B)
+    // streaming kernel: a persistent grid, each CTA a ring of ROPE_RING token rows in shared memory fed by bulk copies;
+    // taken when there are tokens enough to pipeline.  B2_ROPE_IMPL=token forces the one-token-per-CTA kernel (A/B)
     static const int sm_count = [] {
         int dev = 0, n = 148;
         if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
         return n;
     }();
     static const bool force_token = [] { const char* e = getenv("B2_ROPE_IMPL"); return e && e[0] == 't'; }();
-    const int n_items = (Hq + Hkv) * (d / 16) + Hkv * (d / 8);
-    const int grid = sm_count * (n_items <= 512 ? 4 : 3);
-    if (!force_token && d <= 256 && T >= 2 * grid && n_items <= 3 * 256) {
-#define B2_ROPE_STREAM(FP8, ITEMS)                                                                                    \
-        rope_and_cache_stream_kernel<FP8, ITEMS><<<grid, 256, 0, st>>>(                                                \
-            p, positions, cos_sin, max_pos, k_cache, v_cache, slot_mapping, T, Hq, Hkv, d, bs, token_stride,           \
-            cache_block_stride, cache_head_stride, k_scale, v_scale, write_k)
-        if (kv_dtype == B2_KV_BF16) {
-            if (n_items <= 512) B2_ROPE_STREAM(false, 2); else B2_ROPE_STREAM(false, 3);
-        } else {
-            if (n_items <= 512) B2_ROPE_STREAM(true, 2); else B2_ROPE_STREAM(true, 3);
+    const size_t row_bytes = (size_t)(Hq + 2 * Hkv) * d * 2;
+    const int stage_bytes = (int)((row_bytes + (size_t)d * 4 + 16 + 127) / 128 * 128);
+    const size_t smem_bytes = (size_t)stage_bytes * ROPE_RING;
+    int per_sm = (int)((220u * 1024u) / (smem_bytes + 1024));
+    if (per_sm > 4) per_sm = 4;
+    const int grid = sm_count * (per_sm > 0 ? per_sm : 1);
+    if (!force_token && per_sm >= 1 && smem_bytes <= 200u * 1024u && row_bytes % 16 == 0 && d % 16 == 0 &&
+        T >= 2 * grid) {
+        auto kern = kv_dtype == B2_KV_BF16 ? rope_and_cache_ring_kernel<false> : rope_and_cache_ring_kernel<true>;
+        static size_t attr_set[2] = {0, 0};
+        size_t& cur = attr_set[kv_dtype == B2_KV_BF16 ? 0 : 1];
+        if (smem_bytes > cur) {
+            B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+            cur = smem_bytes;
         }
-#undef B2_ROPE_STREAM
+        kern<<<grid, ROPE_CONSUMERS + 32, smem_bytes, st>>>(p, positions, cos_sin, max_pos, k_cache, v_cache, slot_mapping,
+                                                            T, Hq, Hkv, d, bs, token_stride, cache_block_stride,
+                                                            cache_head_stride, k_scale, v_scale, write_k, stage_bytes);
         B2_CUDA_OK(cudaGetLastError());
         return B2_OK;
     }
