@@ -308,26 +308,41 @@ rope_and_cache_ring_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __res
     if (first >= T) return;
 
     if (threadIdx.x >= ROPE_CONSUMERS) {
-        // ---------------- producer warp: one lane issues the copies ----------------
-        if (threadIdx.x != ROPE_CONSUMERS) return;
-        int t = first;
-        int pos = positions[t];
-        int64_t slot = slot_mapping[t];
-        for (int j = 0; t < T; ++j, t += step) {
-            const int s = j % ROPE_RING;
-            const int tn = t + step;
-            int npos = 0;
-            int64_t nslot = -1;
-            if (tn < T) { npos = positions[tn]; nslot = slot_mapping[tn]; }      // next token's scalars under this wait
-            if (j >= ROPE_RING) b2::mbar_wait(empty0 + 8 * s, ((j / ROPE_RING) - 1) & 1);
-            unsigned char* st = smem + (size_t)s * stage_bytes;
-            *reinterpret_cast<int64_t*>(st + row_bytes + cs_bytes) = slot;
-            const int p = min(max(pos, 0), max_pos - 1);
-            b2::mbar_arrive_expect_tx(full0 + 8 * s, row_bytes + cs_bytes);      // release: the slot store is visible
-            b2::bulk_load(b2::smem_u32(st), qkv + t * token_stride, row_bytes, full0 + 8 * s);
-            b2::bulk_load(b2::smem_u32(st + row_bytes), cos_sin + (int64_t)p * d, cs_bytes, full0 + 8 * s);
-            pos = npos;
-            slot = nslot;
+        // ---------------- producer warp ----------------
+        // The 32 lanes fetch position and slot of the next 32 tokens of this CTA at once (one exposed load latency per
+        // 32 tokens, and the batch after is already in flight); lane 0 issues the bulk copies.
+        const int lane = threadIdx.x & 31;
+        auto fetch = [&](int j0, int& pos_l, int64_t& slot_l) {
+            const int64_t tl = (int64_t)first + (int64_t)(j0 + lane) * step;
+            pos_l = 0;
+            slot_l = -1;
+            if (tl < T) { pos_l = positions[tl]; slot_l = slot_mapping[tl]; }
+        };
+        int pos_l, npos_l;
+        int64_t slot_l, nslot_l;
+        fetch(0, pos_l, slot_l);
+        for (int j0 = 0; (int64_t)first + (int64_t)j0 * step < T; j0 += 32) {
+            fetch(j0 + 32, npos_l, nslot_l);
+            for (int jj = 0; jj < 32; ++jj) {
+                const int j = j0 + jj;
+                const int64_t t = (int64_t)first + (int64_t)j * step;
+                if (t >= T) break;
+                const int pos = __shfl_sync(0xffffffffu, pos_l, jj);
+                const int64_t slot = __shfl_sync(0xffffffffu, slot_l, jj);
+                if (lane == 0) {
+                    const int s = j % ROPE_RING;
+                    if (j >= ROPE_RING) b2::mbar_wait(empty0 + 8 * s, ((j / ROPE_RING) - 1) & 1);
+                    unsigned char* st = smem + (size_t)s * stage_bytes;
+                    *reinterpret_cast<int64_t*>(st + row_bytes + cs_bytes) = slot;
+                    const int p = min(max(pos, 0), max_pos - 1);
+                    b2::mbar_arrive_expect_tx(full0 + 8 * s, row_bytes + cs_bytes);  // release: the slot store is visible
+                    b2::bulk_load(b2::smem_u32(st), qkv + t * token_stride, row_bytes, full0 + 8 * s);
+                    b2::bulk_load(b2::smem_u32(st + row_bytes), cos_sin + (int64_t)p * d, cs_bytes, full0 + 8 * s);
+                }
+                __syncwarp();
+            }
+            pos_l = npos_l;
+            slot_l = nslot_l;
         }
         return;
     }
