@@ -279,7 +279,7 @@ constexpr int ROPE_CONSUMERS = 256;
 constexpr int ROPE_MAX_ITEMS = 3;        // work items per consumer thread: rows of up to 80 heads of 128
 
 template <bool FP8>
-__global__ void __launch_bounds__(ROPE_CONSUMERS + 32)
+__global__ void __launch_bounds__(ROPE_CONSUMERS + 32, 4)     // <= 56 registers: four CTAs (36 warps, 16 stages) per SM
 rope_and_cache_ring_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ positions,
                            const float* __restrict__ cos_sin, int max_pos, void* __restrict__ k_cache,
                            void* __restrict__ v_cache, const int64_t* __restrict__ slot_mapping, int T, int Hq, int Hkv,
