@@ -278,7 +278,7 @@ constexpr int ROPE_RING = 4;
 constexpr int ROPE_CONSUMERS = 256;
 constexpr int ROPE_MAX_ITEMS = 3;        // work items per consumer thread: rows of up to 80 heads of 128
 
-template <bool FP8>
+template <bool FP8, int MAXI>          // MAXI work items per consumer thread: 2 covers rows of up to 512 items (Llama-3-8B: 448)
 __global__ void __launch_bounds__(ROPE_CONSUMERS + 32, 4)     // <= 56 registers: four CTAs (36 warps, 16 stages) per SM
 rope_and_cache_ring_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ positions,
                            const float* __restrict__ cos_sin, int max_pos, void* __restrict__ k_cache,
@@ -348,14 +348,14 @@ rope_and_cache_ring_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __res
         return;
     }
     // ---------------- consumers ----------------
-    // What a thread's (up to ROPE_MAX_ITEMS) work items are does not depend on the token: decode them once -- the kernel is
+    // What a thread's (up to MAXI) work items are does not depend on the token: decode them once -- the kernel is
     // issue-bound (ncu: 2.7 warp instructions per cycle per SM), and the per-token integer divides were a fifth of it.
     float ks = 1.f, vs = 1.f;
     if (FP8) { ks = *k_scale; vs = *v_scale; }
-    int so[ROPE_MAX_ITEMS], kind[ROPE_MAX_ITEMS], col[ROPE_MAX_ITEMS];      // row offset (elements); 0 none 1 q 2 k 3 v; c * 8
-    int64_t coff[ROPE_MAX_ITEMS];                                           // offset inside a cache block
+    int so[MAXI], kind[MAXI], col[MAXI];      // row offset (elements); 0 none 1 q 2 k 3 v; c * 8
+    int64_t coff[MAXI];                                           // offset inside a cache block
 #pragma unroll
-    for (int k = 0; k < ROPE_MAX_ITEMS; ++k) {
+    for (int k = 0; k < MAXI; ++k) {
         const int i = threadIdx.x + k * ROPE_CONSUMERS;
         so[k] = 0; kind[k] = 0; col[k] = (threadIdx.x % pairs_per_head) * 8; coff[k] = 0;
         if (i < n_rot) {
@@ -391,7 +391,7 @@ rope_and_cache_ring_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __res
         *reinterpret_cast<float4*>(si) = *reinterpret_cast<const float4*>(cs + half + col[0]);
         *reinterpret_cast<float4*>(si + 4) = *reinterpret_cast<const float4*>(cs + half + col[0] + 4);
 #pragma unroll
-        for (int k = 0; k < ROPE_MAX_ITEMS; ++k) {
+        for (int k = 0; k < MAXI; ++k) {
             if (kind[k] == 1 || kind[k] == 2) {
                 float x1[8], x2[8], o1[8], o2[8];
                 unpack8(*reinterpret_cast<const int4*>(srow + so[k]), x1);
@@ -699,9 +699,12 @@ extern "C" int b2_rope_and_cache_ex(void* qkv, const int32_t* positions, const f
     if (!force_token && per_sm >= 1 && smem_bytes <= 200u * 1024u && row_bytes % 16 == 0 && d % 16 == 0 &&
         (bs & (bs - 1)) == 0 && n_items <= ROPE_MAX_ITEMS * ROPE_CONSUMERS && ROPE_CONSUMERS % (d / 16) == 0 &&
         T >= 2 * grid) {
-        auto kern = kv_dtype == B2_KV_BF16 ? rope_and_cache_ring_kernel<false> : rope_and_cache_ring_kernel<true>;
-        static size_t attr_set[2] = {0, 0};
-        size_t& cur = attr_set[kv_dtype == B2_KV_BF16 ? 0 : 1];
+        const bool two = n_items <= 2 * ROPE_CONSUMERS;
+        auto kern = kv_dtype == B2_KV_BF16
+                        ? (two ? rope_and_cache_ring_kernel<false, 2> : rope_and_cache_ring_kernel<false, ROPE_MAX_ITEMS>)
+                        : (two ? rope_and_cache_ring_kernel<true, 2> : rope_and_cache_ring_kernel<true, ROPE_MAX_ITEMS>);
+        static size_t attr_set[4] = {0, 0, 0, 0};
+        size_t& cur = attr_set[(kv_dtype == B2_KV_BF16 ? 0 : 1) + (two ? 0 : 2)];
         if (smem_bytes > cur) {
             B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
             cur = smem_bytes;
