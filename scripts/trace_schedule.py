@@ -25,6 +25,12 @@ dev = torch.device("cuda:0")
 lib = b200attn.load()
 lib.b2_debug_read_trace.argtypes = [C.c_void_p, C.c_int]
 prob = bench.build_problem(dev, wl["B"], wl["Hq"], wl["Hkv"], wl["ctx"], wl["fp8"], seed=0)
+if len(sys.argv) > 2 and sys.argv[2] == "ragged":        # the serving shape: lengths log-uniform in [128, ctx] (as bench.py --ragged)
+    import math
+    g = torch.Generator().manual_seed(1234)
+    lens = torch.exp(torch.empty(wl["B"]).uniform_(math.log(128.0), math.log(float(wl["ctx"])), generator=g)).to(torch.int32)
+    prob["seq_lens"] = lens.clamp_(128, wl["ctx"])
+    print("ragged lengths: sum", int(prob["seq_lens"].sum()), "max", int(prob["seq_lens"].max()))
 bt, sl = prob["block_tables"].to(dev), prob["seq_lens"].to(dev)
 ks, vs = prob["scales"] or (None, None)
 

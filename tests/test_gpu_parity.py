@@ -387,7 +387,8 @@ def test_full_size_config4_tp1_llama3_70b_b256_ctx8k(cuda):
 # ------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("env", [{}, {"B2_STATIC_PCT": "0", "B2_CHUNK_TOKENS": "64"},
                                  {"B2_STATIC_PCT": "50", "B2_CHUNK_TOKENS": "128"}, {"B2_STATIC_PCT": "100"},
-                                 {"B2_STATIC_PCT": "85", "B2_CHUNK_TOKENS": "512"}])
+                                 {"B2_STATIC_PCT": "85", "B2_CHUNK_TOKENS": "512"},
+                                 {"B2_FUSED_MERGE": "0"}, {"B2_FUSED_MERGE": "0", "B2_STATIC_PCT": "0", "B2_CHUNK_TOKENS": "64"}])
 def test_decode_schedule_variants_ragged(cuda, env, monkeypatch):
     for k, v in env.items():
         monkeypatch.setenv(k, v)
@@ -401,6 +402,20 @@ def test_decode_schedule_variants_ragged(cuda, env, monkeypatch):
                                 num_splits=0)
     assert_close(out, ref, what=f"schedule {env}")
     assert float(out[3].float().abs().max()) == 0.0
+    # the same call again on the same workspace-free path, and through a plan handle twice: the counters the fused merge
+    # keeps in the workspace header (claims, finished CTAs, partial runs per item) must come back to zero every time
+    plan = b200attn.ops.DecodePlan(kc, vc, 37, 16, inp["block_tables"].shape[1])
+    o2 = torch.empty_like(out)
+    for _ in range(3):
+        o2.fill_(float("nan"))
+        plan.run(inp["q"].to(cuda), inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda), o2, 0)
+        assert torch.equal(o2.view(torch.int16), out.view(torch.int16)), "plan-handle run differs from the stateless call"
+    small = slice(0, 9)                       # a smaller batch on the same handle (header laid out for 37 sequences)
+    o3 = torch.full((9, 16, 128), float("nan"), dtype=torch.bfloat16, device=cuda)
+    plan.run(inp["q"][small].to(cuda), inp["block_tables"][small].to(cuda), inp["seq_lens"][small].to(cuda), o3, 0)
+    assert_close(o3, ref[small], what=f"schedule {env}, 9 of 37 sequences on the same handle")
+    plan.run(inp["q"].to(cuda), inp["block_tables"].to(cuda), inp["seq_lens"].to(cuda), o2, 0)
+    assert torch.equal(o2.view(torch.int16), out.view(torch.int16))
 
 
 def test_decode_many_sequences_grouped_prefix(cuda):
