@@ -55,10 +55,9 @@ def test_argument_validation_without_gpu():
     assert lib.b2_paged_decode_workspace_bytes(64, 32, 8, 128, 16, 256, 1) == 0
     assert lib.b2_paged_decode_auto_splits(64, 32, 8, 128, 16, 256, 0) == 0      # 0 = persistent schedule
     assert lib.b2_paged_decode_workspace_bytes(64, 32, 8, 128, 16, 256, 4) == 64 * 32 * 4 * 129 * 4
-    # dynamic persistent schedule: a header (256 bytes of counters + one 4-byte partial-run counter per (sequence, item),
-    # rounded to 256) + partial slots of 8 heads x (d + 1) floats; the slot count grows with the batch
+    # dynamic persistent schedule: a 256-byte header (claim counter) + partial slots of 8 heads x (d + 1) floats; the slot count grows with the batch
     def hdr(B, ipb):
-        return 256 + (B * ipb * 4 + 255) // 256 * 256
+        return 256
     w = lib.b2_paged_decode_workspace_bytes(64, 32, 8, 128, 16, 256, 0)
     w4 = lib.b2_paged_decode_workspace_bytes(4, 32, 8, 128, 16, 256, 0)
     assert w > w4 > 256 and (w - hdr(64, 8)) % (8 * 129 * 4) == 0 and (w4 - hdr(4, 8)) % (8 * 129 * 4) == 0

@@ -66,9 +66,7 @@ struct DecodeParams {
     int B, Hq, Hkv, G, HG, max_nb, num_splits, split_tokens;
     int chunk_tokens, static_pct;   // dynamic schedule: claim granularity, share of chunks dealt statically
     int two_box;                    // bf16: the cache map holds one 128-byte half per box (driver refused the one-box map)
-    uint32_t* counter;              // dynamic schedule: claim counter (workspace header word 0; word 1 = CTAs finished)
-    uint32_t* item_ctr;             // dynamic schedule, fused merge: partial runs written so far, per (sequence, item)
-    int fused_merge;                // 1: the CTA that writes an item's last partial combines them (no merge kernel)
+    uint32_t* counter;              // dynamic schedule: claim counter (workspace header)
     int64_t q_stride, out_stride;
     float scale_log2;  // softmax scale * log2(e)
 };
@@ -89,7 +87,7 @@ struct Cfg {
     static constexpr int SCRATCH_BYTES = 2 * SLOT_FLOATS * 4;
     static constexpr int SMEM_BYTES = RING_BYTES + BAR_BYTES + SCRATCH_BYTES;
     // dynamic schedule: per-stage descriptors + the chunk prefix over (groups of) sequences
-    static constexpr int META_BYTES = NSTAGE * 32 + 16;   // per stage: descriptor + (fused merge) the item's run arithmetic; + 1 flag
+    static constexpr int META_BYTES = NSTAGE * 16;
     static constexpr int PMAX = NT == 1 ? 512 : 128;
     static constexpr int PRE_BYTES = (PMAX + 1 + 3) / 4 * 16;
     // dynamic schedule, NT == 1: the run's q rows travel with its first stage (bulk copy, same full-barrier),
@@ -828,6 +826,11 @@ __device__ __forceinline__ uint32_t dyn_runs_of_item_fast(uint32_t ci0, uint32_t
 }
 
 // The four consumer warps (tid128 = 0..127) combine the partial runs of one item into bf16 output rows.
+// (Round 2 experiment, removed again: combining the partials INSIDE the decode kernel -- per-item arrival counters in
+// the workspace header, the CTA that writes an item's last partial merges it -- was parity-green but slower than the
+// PDL merge kernel on every ragged shape (63.1 vs 60.1 us config-2 shape, 99.9 vs 89.6 fp8): two fences + an atomic at
+// every partial run's end sit on the consumers' critical path, the merging CTA stalls its own pipeline, and the extra
+// code cost the 128-register fp8 instantiation its spill-free allocation.)
 // thread -> (head tid128/16 [+8], 8 consecutive d); partials were written by other CTAs: read through L2 (ld.cg).
 template <int HEADS>
 __device__ __forceinline__ void merge_item(__nv_bfloat16* __restrict__ out_rows, const float* ws_o, const float* ws_lse,
@@ -999,17 +1002,8 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
                     if (st == 0 && run_first) flags |= META_FIRST;
                     if (st == n_stage - 1 && !cont) {
                         flags |= META_LAST;
-                        if (run_k0 == 0 && cp.k == cp.nck - 1) {
-                            flags |= META_DIRECT;
-                        } else {
-                            flags |= (int)(dyn_slot(run_c0, S, stat_total, NC) << 4);
-                            if (p.fused_merge) {      // what the merging CTA needs to know about the item
-                                const uint32_t ci0 = cid - (uint32_t)cp.k;
-                                s_meta[NSTAGE + s] = make_int4((int)ci0, cp.nck,
-                                                               (int)dyn_runs_of_item_fast(ci0, (uint32_t)cp.nck, S, stat_total),
-                                                               cp.b * IPB + cp.j);
-                            }
-                        }
+                        if (run_k0 == 0 && cp.k == cp.nck - 1) flags |= META_DIRECT;
+                        else flags |= (int)(dyn_slot(run_c0, S, stat_total, NC) << 4);
                     }
                     s_meta[s] = make_int4(cp.b, cp.j, min(TOK, ntok - st * TOK), flags);
                     uint32_t tx = nb_stage * 2 * C::BOX_BYTES;
@@ -1039,16 +1033,6 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
             cur_static = next_static;
         }
         if (!ordered) asm volatile("griddepcontrol.wait;" ::: "memory");
-        // fused merge: no kernel follows that could re-arm the claim counter, so the CTA whose producer finishes last
-        // does it (every CTA has made its final claim by then)
-        if (p.fused_merge && lane == 0) {
-            __threadfence();
-            if (atomicAdd(p.counter + 1, 1u) == NC - 1) {
-                p.counter[0] = 0u;
-                p.counter[1] = 0u;
-                __threadfence();
-            }
-        }
         // end-of-work sentinel: a stage with no bytes
         const uint32_t s = it % NSTAGE;
         b2::mbar_wait(bar_empty + s * 8, ((it / NSTAGE) & 1) ^ 1);
@@ -1078,10 +1062,6 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
             const uint32_t s = it % NSTAGE;
             b2::mbar_wait(bar_full + s * 8, (it / NSTAGE) & 1);
             const int4 m = s_meta[s];
-            // the item's run arithmetic travels with the last stage of a partial run: read it before the stage (and
-            // its descriptors) are handed back to the producer
-            int4 m2 = make_int4(0, 0, 0, 0);
-            if (p.fused_merge && (m.w & (META_LAST | META_DIRECT | META_END)) == META_LAST) m2 = s_meta[NSTAGE + s];
             if (m.w & META_END) {
                 if (warp == 0) {
                     B2_TRACE_AT(x, 3);
@@ -1118,39 +1098,18 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
                         const int64_t slot = (int64_t)((uint32_t)m.w >> 4);
                         write_result<FP8, NT>(acc, nheads, vs, sl2, nullptr, p.ws_o + slot * (C::HEADS * D),
                                               p.ws_lse + slot * C::HEADS, scratch, lane);
-                        if (p.fused_merge) {
-                            // count this partial; whoever writes an item's last one combines them right here
-                            __threadfence();
-                            __syncwarp();
-                            if (lane == 0) {
-                                const uint32_t prev = atomicAdd(p.item_ctr + m2.w, 1u);
-                                const bool last = prev + 1 == (uint32_t)m2.z;
-                                if (last) p.item_ctr[m2.w] = 0u;         // armed for the next call
-                                __threadfence();
-                                s_meta[2 * NSTAGE].x = last ? 1 : 0;
-                                s_meta[2 * NSTAGE].y = m2.x;
-                                s_meta[2 * NSTAGE].z = m2.y;
-                            }
-                        }
                     }
                 }
-                const bool maybe_merge = p.fused_merge && !(m.w & META_DIRECT);
                 consumer_bar();   // warp 0 has read its staged rows: the scratch is free for the next run's merge
-                if (maybe_merge) {
-                    const int4 f = s_meta[2 * NSTAGE];
-                    if (f.x)
-                        merge_item<C::HEADS>(p.out + cb * p.out_stride + (int64_t)head0 * D, p.ws_o, p.ws_lse, (uint32_t)f.y,
-                                             (uint32_t)f.z, S, stat_total, NC, nheads, tid);
-                }
             }
         }
     }
 }
 
 // first kernel of a dynamic-schedule call: zero the claim counter
-__global__ void zero_counter_kernel(uint32_t* counter, int n_words) {
+__global__ void zero_counter_kernel(uint32_t* counter) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the decode grid may start its static share
-    for (int i = threadIdx.x; i < n_words; i += blockDim.x) counter[i] = 0u;   // claim / finished counters + item counters
+    if (threadIdx.x == 0) *counter = 0u;
 }
 
 // One block per item (sequence b = blockIdx.y, item j = blockIdx.x): combine its partial runs unless one
@@ -1257,10 +1216,6 @@ int env_int(const char* name, int dflt) {
 struct Knobs {
     int chunk_tokens;   // B2_CHUNK_TOKENS: claim granularity of the dynamic schedule (0 = automatic)
     int static_pct;     // B2_STATIC_PCT: share of the chunks dealt statically
-    int fused_merge;    // B2_FUSED_MERGE=1: combine partials inside the decode kernel instead of the PDL merge kernel.
-                        // Parity-green, measured SLOWER (ragged config-2 shape 63.1 vs 60.1 us, fp8 99.9 vs 89.6): the two
-                        // fences + atomic at every partial run's end sit on the consumers' critical path and the merging
-                        // CTA stalls its own pipeline, while the PDL kernel merges on idle resources.  Kept as the A/B.
     int fp8_ctas;       // B2_FP8_CTAS: 3 (default) or 2 resident CTAs per SM for the fp8 kernels
     int two_box;        // B2_TWO_BOX=1: force the two-boxes-per-tile bf16 map (the fallback path)
 };
@@ -1269,7 +1224,6 @@ Knobs read_knobs() {
     k.chunk_tokens = env_int("B2_CHUNK_TOKENS", 0);
     int pct = env_int("B2_STATIC_PCT", 85);
     k.static_pct = pct < 0 ? 0 : (pct > 100 ? 100 : pct);
-    k.fused_merge = env_int("B2_FUSED_MERGE", 0) != 0;
     k.fp8_ctas = env_int("B2_FP8_CTAS", 3) == 3 ? 3 : 2;
     k.two_box = env_int("B2_TWO_BOX", 0) != 0;
     return k;
@@ -1349,9 +1303,7 @@ struct Plan {
 };
 
 // dynamic schedule: workspace header (claim counter)
-constexpr size_t WS_HEADER_BYTES = 256;   // claim counter, CTAs-finished counter
-// the dynamic schedule's header: the two counters + one partial-run counter per (sequence, item) for the fused merge
-size_t ws_header_bytes(int64_t items) { return WS_HEADER_BYTES + (size_t)((items * 4 + 255) / 256 * 256); }
+constexpr size_t WS_HEADER_BYTES = 256;
 
 int dyn_ct_max(int bs) { return bs * 32 < 512 ? bs * 32 : 512; }   // <= 32 blocks per chunk
 
@@ -1394,7 +1346,7 @@ void make_plan(Plan* pl, int B, int Hkv, int G, int bs, int max_nb, int num_spli
 
 size_t plan_workspace(const Plan& pl, int B, int Hq) {
     if (pl.num_splits == 0) {
-        return ws_header_bytes((int64_t)B * pl.ipb) + (size_t)pl.slots * (8 * pl.nt) * (D + 1) * sizeof(float);
+        return WS_HEADER_BYTES + (size_t)pl.slots * (8 * pl.nt) * (D + 1) * sizeof(float);
     }
     if (pl.num_splits == 1) return 0;
     return (size_t)B * Hq * pl.num_splits * (D + 1) * sizeof(float);
@@ -1408,7 +1360,6 @@ size_t workspace_bound(int B, int Hq, int Hkv, int bs, int max_nb, int num_split
     make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits, 3, kn);
     size_t best = plan_workspace(pl, B, Hq);
     if (num_splits > 0) return best;                       // grid split: monotone in B
-    const size_t hdr = ws_header_bytes((int64_t)B * pl.ipb);   // a plan handle reserves the header of its largest batch
     const int NC = persistent_grid(3);
     const int64_t per_seq = (int64_t)pl.ipb * max_nb * bs;  // streamed tokens one sequence adds
     for (int ct = TOK; ct * 2 <= dyn_ct_max(bs); ct *= 2) {
@@ -1417,7 +1368,7 @@ size_t workspace_bound(int B, int Hq, int Hkv, int bs, int max_nb, int num_split
         const int64_t b = first_bigger - 1;
         if (b >= 1 && b < B) {
             make_plan(&pl, (int)b, Hkv, Hq / Hkv, bs, max_nb, 0, 3, kn);
-            best = std::max(best, plan_workspace(pl, (int)b, Hq) - ws_header_bytes(b * pl.ipb) + hdr);
+            best = std::max(best, plan_workspace(pl, (int)b, Hq));
         }
     }
     return best;
@@ -1442,7 +1393,7 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         const int grid = persistent_grid(C::CTAS_DYN);
         B2_REQUIRE(grid == pl.nc, B2_EINVAL, "paged_decode: plan made for %d CTAs, kernel runs %d", pl.nc, grid);
         if (zero_first) {
-            zero_counter_kernel<<<1, 256, 0, st>>>(p.counter, (int)(ws_header_bytes((int64_t)p.B * p.Hkv * p.HG) / 4));
+            zero_counter_kernel<<<1, 32, 0, st>>>(p.counter);
             B2_CUDA_OK(cudaGetLastError());
         }
         cudaLaunchAttribute at[1];
@@ -1458,7 +1409,6 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         cfg.attrs = at;
         cfg.numAttrs = zero_first ? 1 : 0;
         B2_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmK, tmV, p));
-        if (p.fused_merge) return B2_OK;          // partials are combined by the CTA that writes an item's last one
         cudaLaunchConfig_t cfg2 = {};
         cfg2.gridDim = dim3(p.Hkv * p.HG, p.B);
         cfg2.blockDim = dim3(128);
@@ -1510,7 +1460,6 @@ struct DecodeGeom {
     const float* v_scale;
     void* workspace;
     size_t workspace_bytes;
-    int max_B;          // plan handle: the batch size its workspace header was laid out (and zeroed) for; 0 = stateless call
 };
 
 int check_geom(int Hq, int Hkv, int d, int bs, int max_nb, int64_t num_blocks, const void* k_cache, const void* v_cache,
@@ -1563,28 +1512,23 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
     p.scale_log2 = g.scale * LOG2E;
     p.ws_o = nullptr; p.ws_lse = nullptr;
     p.counter = nullptr;
-    p.item_ctr = nullptr;
-    p.fused_merge = kn.fused_merge;
     p.chunk_tokens = pl.chunk_tokens;
     p.static_pct = pl.static_pct;
     p.two_box = maps.two_box;
     // a plan handle keeps its zeroed claim counter in the workspace header: the partials of every schedule start
     // behind it (the stateless call re-zeroes the counter itself and uses the header only for the dynamic schedule)
     const bool header = pl.num_splits == 0 || !zero_first;
-    // header layout is that of the handle's largest batch (zeroed once at creation), or of this call's batch (stateless)
-    const size_t hdr_bytes = ws_header_bytes((int64_t)(g.max_B > 0 ? g.max_B : B) * pl.ipb);
-    const size_t body = plan_workspace(pl, B, g.Hq) - (pl.num_splits == 0 ? ws_header_bytes((int64_t)B * pl.ipb) : 0);
+    const size_t body = plan_workspace(pl, B, g.Hq) - (pl.num_splits == 0 ? WS_HEADER_BYTES : 0);
     if (body) {
-        const size_t need = body + (header ? hdr_bytes : 0);
+        const size_t need = body + (header ? WS_HEADER_BYTES : 0);
         B2_REQUIRE(g.workspace && g.workspace_bytes >= need && b2_aligned16(g.workspace), B2_ENOMEM,
                    "paged_decode: workspace %zu bytes < required %zu", g.workspace_bytes, need);
         char* base = static_cast<char*>(g.workspace);
         if (pl.num_splits == 0) {
             B2_REQUIRE(pl.slots < (1LL << 27), B2_EUNSUPPORTED, "paged_decode: %lld partial slots", (long long)pl.slots);
             p.counter = reinterpret_cast<uint32_t*>(base);
-            p.item_ctr = reinterpret_cast<uint32_t*>(base + WS_HEADER_BYTES);
         }
-        if (header) base += hdr_bytes;
+        if (header) base += WS_HEADER_BYTES;
         p.ws_o = reinterpret_cast<float*>(base);
         p.ws_lse = p.ws_o + body / sizeof(float) / (D + 1) * D;
     }
@@ -1702,7 +1646,7 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
     rc = make_decode_maps(&maps, k_cache, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride,
                           kn.two_box != 0);
     if (rc != B2_OK) return rc;
-    const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes, 0};
+    const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
     return run_decode(g, maps, kn, /*zero_first=*/true, out, q, block_tables, seq_lens, B, q_stride, out_stride, num_splits,
                       static_cast<cudaStream_t>(stream));
 }
@@ -1744,7 +1688,7 @@ extern "C" b2_decode_plan* b2_decode_plan_create(const void* k_cache, const void
         b2_set_error("decode_plan_create: out of host memory");
         return nullptr;
     }
-    pl->g = DecodeGeom{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes, max_B};
+    pl->g = DecodeGeom{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
     pl->kn = kn;
     pl->max_B = max_B;
     if (make_decode_maps(&pl->maps, k_cache, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride,
@@ -1753,9 +1697,7 @@ extern "C" b2_decode_plan* b2_decode_plan_create(const void* k_cache, const void
         return nullptr;
     }
     // the claim counter starts at zero; every dynamic-schedule call leaves it at zero again (merge_chunks_kernel)
-    Plan hp;
-    make_plan(&hp, max_B, Hkv, Hq / Hkv, bs, max_nb, 0, 3, kn);
-    if (cudaMemsetAsync(workspace, 0, ws_header_bytes((int64_t)max_B * hp.ipb), static_cast<cudaStream_t>(stream)) != cudaSuccess) {
+    if (cudaMemsetAsync(workspace, 0, WS_HEADER_BYTES, static_cast<cudaStream_t>(stream)) != cudaSuccess) {
         b2_set_error("decode_plan_create: cudaMemsetAsync of the workspace header failed");
         delete pl;
         return nullptr;
