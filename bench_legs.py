@@ -204,8 +204,13 @@ def tp_parity_leg(dev, group, model: str = "tiny8", seed: int = 1, gap: float = 
     return rec
 
 
+_NVLINK_COUNTERS = [True]        # flips to False the first time NVML says the counters are not there (this pool: N/A)
+
+
 def _nvlink_kib(index: int):
     """(tx, rx) data KiB over all NVLink links of GPU `index` (NVML field counters), or None."""
+    if not _NVLINK_COUNTERS[0]:
+        return None
     try:
         import pynvml
         pynvml.nvmlInit()
@@ -213,9 +218,11 @@ def _nvlink_kib(index: int):
         v = pynvml.nvmlDeviceGetFieldValues(h, [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
                                                 (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)])
         if any(x.nvmlReturn != 0 for x in v):
+            _NVLINK_COUNTERS[0] = False
             return None
         return int(v[0].value.ullVal), int(v[1].value.ullVal)
     except Exception:                                                         # noqa: BLE001
+        _NVLINK_COUNTERS[0] = False
         return None
 
 
