@@ -237,6 +237,14 @@ B2_API int b2_rope_and_cache_ex(void* qkv, const int32_t* positions, const float
                       void* k_cache, void* v_cache, const int64_t* slot_mapping, int T, int Hq, int Hkv,
                       int d, int bs, int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
                       int kv_dtype, const float* k_scale, const float* v_scale, int write_k, void* stream);
+/* The projections of a DECODE step (VLLMConfig.max_num_seqs rows, reference benchmark-vllm/models.py:9):
+ * out[M, N] = x[M, K] . W[N, K]^T, bf16 in, fp32 accumulate, one rounding.  M <= 256, K % 64 == 0, N % 4 == 0; ldx / ldo
+ * are row strides in elements.  A weight-streaming tcgen05 kernel (swap-AB, split-K over a thread-block cluster with the
+ * partial sums reduced through distributed shared memory; csrc/gemm_tc5.cu) for the regime where a library GEMM leaves
+ * most of the HBM bandwidth unused; prompt chunks (M > 256) stay on the library.  vLLM: the ColumnParallelLinear /
+ * RowParallelLinear forward of a decode step. */
+B2_API int b2_skinny_gemm(void* out, const void* x, const void* w, int M, int N, int K, int64_t ldx, int64_t ldo,
+                          void* stream);
 B2_API int b2_sample(int64_t* tokens, const void* logits, int B, int V, int64_t stride, const float* temperature,
               const int64_t* seeds, void* stream);
 /* b2_sample with the OpenAI / vLLM sampling filters (top_k int32 [B], top_p fp32 [B]; either may be NULL): for rows

@@ -138,6 +138,14 @@ if a.only in ("all", "gemm"):
             byt = N * K * 2 + M * K * 2 + M * N * 2
             emit(op="decode_gemm", name=name, tp=tp, M=M, K=K, N=N, us=med * 1e3 / 16, GBps=byt * 16 / med / 1e6,
                  frac_hbm=byt * 16 / med / 1e6 / HBM, note="cuBLAS via torch.mm, 16 distinct weights back to back")
+
+            def run2():
+                for wgt in ws:
+                    ops.skinny_gemm(xg, wgt, out=og)
+            med2, best2 = timeit(run2, iters=20)
+            emit(op="decode_gemm_tc5", name=name, tp=tp, M=M, K=K, N=N, us=med2 * 1e3 / 16, GBps=byt * 16 / med2 / 1e6,
+                 frac_hbm=byt * 16 / med2 / 1e6 / HBM, vs_cublas=round(med / med2, 3),
+                 note="b2_skinny_gemm (tcgen05, swap-AB, cluster split-K), same 16 weights")
             del ws
 
 if a.skip_model:

@@ -53,6 +53,7 @@ SIGNATURES = {
     "b2_silu_and_mul": (i32, [vp, vp, i32, i32, i64, i64, vp]),
     "b2_rope_and_cache": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, vp, vp, vp]),
     "b2_rope_and_cache_ex": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, vp, vp, i32, vp]),
+    "b2_skinny_gemm": (i32, [vp, vp, vp, i32, i32, i32, i64, i64, vp]),
     "b2_sample": (i32, [vp, vp, i32, i32, i64, vp, vp, vp]),
     "b2_sample_filtered": (i32, [vp, vp, i32, i32, i64, vp, vp, vp, vp, vp]),
     "b2_bm_create": (vp, [i64, i32]),

@@ -477,6 +477,29 @@ def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_sin: torch.Te
                                         _ptr(k_scale), _ptr(v_scale), 1 if write_k else 0, _stream(dev)))
 
 
+SKINNY_GEMM_MAX_M = 256
+
+
+def skinny_gemm(x: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[M, N] = x[M, K] @ w[N, K]^T for the rows of a decode step (M <= 256): the weight-streaming tcgen05 kernel
+    b2_skinny_gemm.  x bf16 [M, K] (row stride allowed), w bf16 [N, K] contiguous, out bf16 [M, N] (row stride allowed)."""
+    lib = _lib.load()
+    dev = _need_cuda(x=x, w=w, out=out)
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or x.dim() != 2 or w.dim() != 2 or x.shape[1] != w.shape[1]:
+        raise ValueError("skinny_gemm: x [M, K] and w [N, K] must be bf16 with the same K")
+    if x.stride(1) != 1 or not w.is_contiguous():
+        raise ValueError("skinny_gemm: x rows and w must be contiguous")
+    M, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    elif out.dtype != torch.bfloat16 or out.shape != (M, N) or out.stride(1) != 1:
+        raise ValueError(f"skinny_gemm: out must be bf16 [{M}, {N}] with contiguous rows")
+    _lib.check(lib.b2_skinny_gemm(_ptr(out), _ptr(x), _ptr(w), M, N, K, x.stride(0) if M > 1 else K,
+                                  out.stride(0) if M > 1 else N, _stream(dev)))
+    return out
+
+
 def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, seeds: Optional[torch.Tensor] = None,
            out: Optional[torch.Tensor] = None, top_k: Optional[torch.Tensor] = None,
            top_p: Optional[torch.Tensor] = None) -> torch.Tensor:
