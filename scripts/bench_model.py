@@ -131,17 +131,31 @@ if a.only in ("all", "gemm"):
             ws = [torch.randn(N, K, device=dev).to(torch.bfloat16) for _ in range(16)]
             og = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
 
+            def graphed(fn):
+                """the loop as ONE CUDA graph: device time per GEMM without the host launch cost (how a decode step runs)"""
+                st_ = torch.cuda.Stream()
+                with torch.cuda.stream(st_):
+                    fn()
+                    st_.synchronize()
+                    gr = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gr, stream=st_):
+                        fn()
+                st_.synchronize()
+                return gr.replay
+
             def run():
                 for wgt in ws:
                     torch.mm(xg, wgt.t(), out=og)
+            run = graphed(run)
             med, best = timeit(run, iters=20)
             byt = N * K * 2 + M * K * 2 + M * N * 2
             emit(op="decode_gemm", name=name, tp=tp, M=M, K=K, N=N, us=med * 1e3 / 16, GBps=byt * 16 / med / 1e6,
-                 frac_hbm=byt * 16 / med / 1e6 / HBM, note="cuBLAS via torch.mm, 16 distinct weights back to back")
+                 frac_hbm=byt * 16 / med / 1e6 / HBM, note="cuBLAS via torch.mm, 16 distinct weights back to back, replayed as one CUDA graph")
 
             def run2():
                 for wgt in ws:
                     ops.skinny_gemm(xg, wgt, out=og)
+            run2 = graphed(run2)
             med2, best2 = timeit(run2, iters=20)
             emit(op="decode_gemm_tc5", name=name, tp=tp, M=M, K=K, N=N, us=med2 * 1e3 / 16, GBps=byt * 16 / med2 / 1e6,
                  frac_hbm=byt * 16 / med2 / 1e6 / HBM, vs_cublas=round(med / med2, 3),

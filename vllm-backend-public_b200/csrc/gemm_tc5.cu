@@ -4,7 +4,7 @@
 // Why it exists (SURVEY.md section 8(f) rank 3 lets the GEMMs be library calls, and for prompt chunks they stay cuBLAS):
 // at M = 64 the op is a weight STREAM -- 64 flop per weight byte, bounded by HBM, not by the tensor pipe -- and the
 // library reaches 35-50 % of the HBM bandwidth on the q|k|v and o projections of Llama-3-8B and 7-40 % on the per-rank
-// shapes of --tensor-parallel-size 8 (profiles/r2_decode_gemm_cublas.jsonl): too few CTAs pull on the memory system.
+// shapes of --tensor-parallel-size 8 (profiles/r2_decode_gemm.jsonl): too few CTAs pull on the memory system.
 //
 // Shape of the kernel (swap-AB, split-K over a thread-block cluster):
 //   * the WEIGHT tile is the M side of the MMA: one CTA owns 128 output features (rows of W), the activations are the N
@@ -19,6 +19,8 @@
 //     No workspace, no second kernel, no atomics.
 // Warps: 0-3 epilogue (one TMEM lane = one feature each), 4 TMA producer, 5 MMA issuer + TMEM allocation.
 #include "b2_common.cuh"
+
+#include <stdlib.h>
 
 #include <mutex>
 #include <unordered_map>
@@ -278,14 +280,19 @@ extern "C" int b2_skinny_gemm(void* out, const void* x, const void* w, int M, in
         if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
         return n;
     }();
+    static const int fixed_cost = [] { const char* e = getenv("B2_GEMM_FIXED"); return e ? atoi(e) : 16; }();
+    static const int force_ks = [] { const char* e = getenv("B2_GEMM_KSPLIT"); return e ? atoi(e) : 0; }();
     int best = 1;
     long best_cost = -1;
     for (int ksp = 1; ksp <= 8; ksp *= 2) {
         if (ksp > nk) break;
         const long waves = ((long)n_tiles * ksp + sm_count - 1) / sm_count;
-        const long cost = waves * ((nk + ksp - 1) / ksp + (ksp > 1 ? 3 : 1));
+        // a CTA's fixed cost (launch, TMEM allocation, pipeline ramp, epilogue; + the cluster barriers and the DSMEM
+        // pass when K is split) is worth ~16-18 chunks of streaming: B2_GEMM_FIXED overrides (experiments)
+        const long cost = waves * ((nk + ksp - 1) / ksp + (ksp > 1 ? fixed_cost + 2 : fixed_cost));
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = ksp; }
     }
+    if (force_ks == 1 || force_ks == 2 || force_ks == 4 || force_ks == 8) best = force_ks <= nk ? force_ks : best;
     p.ksplit = best;
     // the fp32 tile parked for the reduction shares the ring's memory: n_mma x 128 x 4 bytes
     const int part_bytes = p.n_mma * BF * 4;
