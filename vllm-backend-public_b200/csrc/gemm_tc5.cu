@@ -1,10 +1,12 @@
 // gemm_tc5.cu -- the projections of a DECODE step on the 5th-gen tensor cores: out[M, N] = x[M, K] . W[N, K]^T, bf16,
 // M <= 256 rows (one per running sequence), W a model weight that is read exactly once per step.
 //
-// Why it exists (SURVEY.md section 8(f) rank 3 lets the GEMMs be library calls, and for prompt chunks they stay cuBLAS):
-// at M = 64 the op is a weight STREAM -- 64 flop per weight byte, bounded by HBM, not by the tensor pipe -- and the
-// library reaches 35-50 % of the HBM bandwidth on the q|k|v and o projections of Llama-3-8B and 7-40 % on the per-rank
-// shapes of --tensor-parallel-size 8 (profiles/r2_decode_gemm.jsonl): too few CTAs pull on the memory system.
+// Status: an EXPERIMENT, parity-green (tests/test_gpu_gemm.py) but not on the engine's path.  SURVEY.md section 8(f)
+// rank 3 lets the GEMMs be library calls; at M = 64 the op is a weight STREAM (64 flop per weight byte, HBM-bound), and
+// in-graph cuBLAS reaches 53-88 % of the HBM bandwidth on the Llama-3-8B decode shapes and 13-49 % on the per-rank
+// shapes of --tensor-parallel-size 8.  This kernel was written to beat that and does not yet: 0.47-0.81x of the
+// library's speed (profiles/r2_decode_gemm.jsonl) -- one non-persistent CTA per (feature tile, K slice) pays TMEM
+// allocation, pipeline ramp and two cluster barriers on <= 0.5 MB of weights.  DESIGN.md section 8 says what would.
 //
 // Shape of the kernel (swap-AB, split-K over a thread-block cluster):
 //   * the WEIGHT tile is the M side of the MMA: one CTA owns 128 output features (rows of W), the activations are the N
