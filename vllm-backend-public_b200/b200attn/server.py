@@ -427,6 +427,29 @@ def create_app(runner: EngineRunner):
                      "model": args.public_name, "choices": [c]}
                 return "data: " + json.dumps(d) + "\n\n"
             try:
+                if len(choices) == 1 and not chat and not choices[0].echo_text:
+                    # the common case (one prompt, n = 1): no task per token, and only the delta goes through the JSON
+                    # encoder -- at tensor-parallel speeds the event loop, not the GPU, bounds the tokens per second
+                    ch = choices[0]
+                    head = ('data: {"id": ' + json.dumps(rid) + ', "object": ' + json.dumps(obj) + ', "created": '
+                            + str(created) + ', "model": ' + json.dumps(args.public_name)
+                            + ', "choices": [{"index": ' + str(ch.index) + ', "text": ')
+                    tail_none = ', "logprobs": null, "finish_reason": null}]}\n\n'
+                    while True:
+                        delta = await ch.next_delta(runner)
+                        if delta is None:
+                            break
+                        if ch.finish_reason is not None:
+                            yield (head + json.dumps(delta) + ', "logprobs": null, "finish_reason": '
+                                   + json.dumps(ch.finish_reason) + '}]}\n\n')
+                            break
+                        if delta:
+                            yield head + json.dumps(delta) + tail_none
+                    if include_usage:
+                        yield "data: " + json.dumps({"id": rid, "object": obj, "created": created,
+                                                     "model": args.public_name, "choices": [], "usage": usage()}) + "\n\n"
+                    yield "data: [DONE]\n\n"
+                    return
                 pending = {asyncio.ensure_future(ch.next_delta(runner)): ch for ch in choices}
                 for ch in choices:
                     if chat:
