@@ -438,7 +438,9 @@ def run_ours(args, wl_name, wl):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+        from datetime import timedelta
+        # a rank that fails alone must not leave the others waiting for NCCL's default 10 minutes
+        dist.init_process_group("nccl", device_id=dev, timeout=timedelta(minutes=4))
 
     tp = world
     if wl["Hkv"] % tp:

@@ -31,7 +31,8 @@ def main():
     rank, local = int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", "0"))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev)
+    from datetime import timedelta
+    dist.init_process_group("nccl", device_id=dev, timeout=timedelta(minutes=4))
     import bench_legs
     from b200attn.tp import TPGroup
     group = TPGroup(dev)

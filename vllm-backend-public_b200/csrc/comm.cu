@@ -41,7 +41,7 @@ constexpr int PUSH_MAX_ROWS = 256;   // <= 2 CTAs x 148 SMs (see push_allreduce_
 struct Ctrl {                       // first CTRL_BYTES of every rank's region
     uint32_t epoch;                 // barriers this rank has completed (only this rank's kernels write it)
     uint32_t done;                  // CTAs of the running kernel that have finished
-    uint32_t lam;                   // push exchanges this rank has completed (selects the landing buffer, mod 3)
+    uint32_t lam;                   // landing buffer of the next push exchange: 0, 1, 2, 0, ... (kept below 3, so no wrap)
     uint32_t pad[13];
     uint64_t dbg[8];                // B2_COMM_DEBUG=1: globaltimer stamps of CTA 0 / thread 0 of the last push exchange
     uint32_t flag[MAX_TP][32];      // flag[src][0] = last epoch rank `src` has reached (one 128-byte line per source)
@@ -341,8 +341,8 @@ const Peers peers, int rank, size_t lam_off, size_t lam_src_bytes, size_t lam_bu
     }
     if (threadIdx.x == 0) s_lam = ld_volatile(&me->lam);
     __syncthreads();
-    const uint32_t call = s_lam;
-    const size_t buf_off = lam_off + (size_t)(call % 3u) * lam_buf_bytes;
+    const uint32_t call = s_lam;                                  // 0, 1 or 2
+    const size_t buf_off = lam_off + (size_t)call * lam_buf_bytes;
 
     // push: one 16-byte store per peer and vector, into the slot [buffer][src = rank][row][v] of every peer
 #pragma unroll
@@ -446,7 +446,7 @@ const Peers peers, int rank, size_t lam_off, size_t lam_src_bytes, size_t lam_bu
         __threadfence();
         if (atomicAdd(&me->done, 1u) == gridDim.x - 1) {
             me->done = 0;
-            me->lam = call + 1;
+            me->lam = call == 2u ? 0u : call + 1u;
             __threadfence();
         }
     }
