@@ -965,9 +965,28 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
         uint32_t run_c0 = 0;
         int run_k0 = 0;
         ChunkPos cp{0, 0, 0, 1, 0};
+        // the NEXT static chunk's position and block-table entries are fetched while the current chunk streams: a chunk
+        // boundary otherwise costs the producer two dependent global loads (seq_lens, then the table row) with nothing
+        // new in flight -- on ragged batches (a chunk or two per item) that was ~1 us per item
+        bool have_next = false;
+        ChunkPos cp_next{0, 0, 0, 1, 0};
+        int tbl_next = 0;
+        auto table_entries = [&](const ChunkPos& c) {
+            const int nb_ = (c.seq_len + BS - 1) / BS;
+            const int nblk_ = min(CB, nb_ - c.k * CB);
+            return lane < nblk_ ? p.block_tables[(int64_t)c.b * p.max_nb + c.k * CB + lane] : 0;
+        };
         while (cid < Ctot) {
-            if (cont_prev) ++cp.k;                      // next chunk of the same item
-            else cp = locate_chunk(cid, s_pre, E, gs, p.seq_lens, p.B, IPB, ct);
+            int tbl;
+            if (have_next) {
+                cp = cp_next;
+                tbl = tbl_next;
+            } else {
+                if (cont_prev) ++cp.k;                  // next chunk of the same item
+                else cp = locate_chunk(cid, s_pre, E, gs, p.seq_lens, p.B, IPB, ct);
+                tbl = table_entries(cp);
+            }
+            have_next = false;
             if (run_first) {
                 run_c0 = cid;
                 run_k0 = cp.k;
@@ -975,7 +994,6 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
             const int nb = (cp.seq_len + BS - 1) / BS;
             const int blk0 = cp.k * CB;
             const int nblk = min(CB, nb - blk0);
-            const int tbl = lane < nblk ? p.block_tables[(int64_t)cp.b * p.max_nb + blk0 + lane] : 0;
             // the id after this one: static ids are known, a dynamic one is claimed now and read late
             const bool next_static = cur_static && stat_cur < stat_end;
             uint32_t pend = 0;
@@ -987,6 +1005,16 @@ paged_decode_dynamic_kernel(const __grid_constant__ CUtensorMap tmK, const __gri
                 if (lane == 0) pend = atomicAdd(p.counter, 1u);
             }
             const bool cont = next_static && (cp.k + 1 < cp.nck);
+            if (next_static) {                          // stat_cur is the next chunk id: fetch it under this chunk's stages
+                if (cont) {
+                    cp_next = cp;
+                    ++cp_next.k;
+                } else {
+                    cp_next = locate_chunk(stat_cur, s_pre, E, gs, p.seq_lens, p.B, IPB, ct);
+                }
+                tbl_next = table_entries(cp_next);
+                have_next = true;
+            }
             const int ntok = min(ct, cp.seq_len - cp.k * ct);
             const int n_stage = (ntok + TOK - 1) / TOK;
             const int kvh = cp.j / p.HG;
