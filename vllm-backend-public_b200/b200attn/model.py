@@ -176,24 +176,10 @@ class LlamaModel:
     def _put(self, name: str, full: torch.Tensor) -> None:
         """Store this rank's shard of the full tensor `name` (the whole tensor at tp = 1).  Shards are taken from the
         full tensor, so every tp size holds exactly the weights of the tp = 1 model (same seed or same checkpoint)."""
-        n, r, c = self.tp_size, self.tp_rank, self.cfg
-        kind = name.rsplit(".", 1)[-1]
-        if n > 1:
-            d = c.d
-            if kind in ("wqkv", "bqkv"):
-                q, k, v = full.split([c.Hq * d, c.Hkv * d, c.Hkv * d], dim=0)
-                full = torch.cat([q[r * self.Hq * d:(r + 1) * self.Hq * d], k[r * self.Hkv * d:(r + 1) * self.Hkv * d],
-                                  v[r * self.Hkv * d:(r + 1) * self.Hkv * d]])
-            elif kind == "wo":
-                full = full[:, r * self.Hq * d:(r + 1) * self.Hq * d].contiguous()
-            elif kind == "wgu":
-                g, u = full.split([c.inter, c.inter], dim=0)
-                full = torch.cat([g[r * self.inter:(r + 1) * self.inter], u[r * self.inter:(r + 1) * self.inter]])
-            elif kind == "wdown":
-                full = full[:, r * self.inter:(r + 1) * self.inter].contiguous()
-            elif kind == "lm_head" and self.vocab_parallel:
-                vs = c.vocab // n
-                full = full[r * vs:(r + 1) * vs].clone()           # a copy: the full tensor can then be freed
+        from .parallel import shard_weight
+        c = self.cfg
+        full = shard_weight(name.rsplit(".", 1)[-1], full, self.tp_size, self.tp_rank, c.Hq, c.Hkv, c.d, c.inter,
+                            self.vocab_parallel)
         self.w[name] = full
 
     def _random_init(self, seed: int) -> None:

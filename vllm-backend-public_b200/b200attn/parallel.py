@@ -83,3 +83,37 @@ def gather_heads(out_local: torch.Tensor, shard: HeadShard, group: Optional[dist
     buf = torch.empty(shard.tp * B, Hl, d, dtype=out_local.dtype, device=out_local.device)   # rank-major rows
     dist.all_gather_into_tensor(buf, out_local.contiguous(), group=group)
     return buf.view(shard.tp, B, Hl, d).permute(1, 0, 2, 3).reshape(B, shard.Hq, d)
+
+
+def shard_weight(kind: str, full: torch.Tensor, tp: int, rank: int, Hq: int, Hkv: int, d: int, inter: int,
+                 vocab_parallel: bool = True) -> torch.Tensor:
+    """Rank `rank`'s shard of one decoder weight for tensor-parallel serving (b200attn.model / b200attn.tp).
+
+    kind (the last component of the model's weight names):
+      wqkv / bqkv  [(Hq + 2 Hkv) d, hidden] (or its bias)   column-parallel: this rank's q heads | its kv heads | its v heads
+      wo           [hidden, Hq d]                           row-parallel: the input columns of this rank's q heads
+      wgu          [2 inter, hidden] = gate | up            column-parallel: this rank's slice of gate | of up
+      wdown        [hidden, inter]                          row-parallel: the input columns of that slice
+      lm_head      [vocab, hidden]                          vocabulary-parallel rows (when vocab_parallel)
+    anything else (embedding, norms) is replicated.  Row-parallel outputs are PARTIAL sums: the caller adds them over
+    the ranks (csrc/comm.cu or an all-reduce).  Shards are cut from the full tensor, so sum / concatenation over the
+    ranks reproduces the tp = 1 model exactly."""
+    if tp == 1:
+        return full
+    Hq_l, Hkv_l, inter_l = Hq // tp, Hkv // tp, inter // tp
+    r = rank
+    if kind in ("wqkv", "bqkv"):
+        q, k, v = full.split([Hq * d, Hkv * d, Hkv * d], dim=0)
+        return torch.cat([q[r * Hq_l * d:(r + 1) * Hq_l * d], k[r * Hkv_l * d:(r + 1) * Hkv_l * d],
+                          v[r * Hkv_l * d:(r + 1) * Hkv_l * d]])
+    if kind == "wo":
+        return full[:, r * Hq_l * d:(r + 1) * Hq_l * d].contiguous()
+    if kind == "wgu":
+        g, u = full.split([inter, inter], dim=0)
+        return torch.cat([g[r * inter_l:(r + 1) * inter_l], u[r * inter_l:(r + 1) * inter_l]])
+    if kind == "wdown":
+        return full[:, r * inter_l:(r + 1) * inter_l].contiguous()
+    if kind == "lm_head" and vocab_parallel:
+        vs = full.shape[0] // tp
+        return full[r * vs:(r + 1) * vs].clone()          # a copy: the full tensor can then be freed
+    return full
