@@ -568,7 +568,7 @@ def run_ours(args, wl_name, wl):
                                 "staging copy), " if e2e_zero_copy else "H2D copy of the q|k|v rows, ")
                              + "reshape_and_cache_decode + decode-plan run, result rows stored by the kernels into pinned "
                                "host memory as 16-byte vectors (the D2H leg), stream sync; one CUDA-graph replay per "
-                               "step, schedule planned on the host per step")},
+                               "step, schedule re-planned on the host every 8 steps (lengths grow by one token per step)")},
             "gpu_launches": launches_per_step * K,
             "clocks": clocks,
         }

@@ -67,6 +67,10 @@ class DecodeStep:
         self._stream = torch.cuda.Stream(self.dev)
         self._plan_fn = _lib.load().b2_paged_decode_plan_splits
         self._sl_ptr = self.h_seq_lens.data_ptr()
+        # the schedule choice is a performance heuristic over lengths that grow by one token per step: it is refreshed
+        # every `plan_every` steps (and whenever the batch size changes), not recomputed on the critical path of each
+        self.plan_every = 8
+        self._plan_cache = (0, 0, 0)            # (B, num_splits, steps left)
 
     # ------------------------------------------------------------------------------------------
     @property
@@ -118,7 +122,13 @@ class DecodeStep:
         if not 0 < B <= self.max_batch:
             raise ValueError(f"B={B} outside (0, {self.max_batch}]")
         if num_splits is None:
-            num_splits = self.plan(B)
+            cb, cs, left = self._plan_cache
+            if cb == B and left > 0:
+                num_splits = cs
+                self._plan_cache = (cb, cs, left - 1)
+            else:
+                num_splits = self.plan(B)
+                self._plan_cache = (B, num_splits, self.plan_every - 1)
         # everything runs on the caller's current stream (a stream context per step costs ~7 us of host time);
         # only the one-time capture uses the private stream
         cur = torch.cuda.current_stream(self.dev)
