@@ -639,6 +639,10 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
             b2::tma_prefetch_desc(&tmV);
         }
         const uint64_t pol = b2::policy_evict_first();
+        // programmatic dependent launch: this grid may have started under the tail of the step's KV write (which
+        // triggers launch_dependents at its start).  Everything above -- barrier init, descriptor prefetch, the
+        // consumers' q loads -- overlaps it; the cache and the block tables are only touched from here on.
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         produce_segment<C, NSTAGE>(&tmK, &tmV, p.block_tables + (int64_t)b * p.max_nb + t_begin / BS,
                                    (n_tok + BS - 1) / BS, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
         B2_TRACE_AT(cta_lin, 4);
@@ -1455,8 +1459,19 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         attr_set2 = true;
     }
     dim3 grid(p.num_splits, p.Hkv * p.HG, p.B);
-    kern<<<grid, NTHREADS, C::SMEM_BYTES, st>>>(tmK, tmV, p);
-    B2_CUDA_OK(cudaGetLastError());
+    {
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(NTHREADS);
+        cfg.dynamicSmemBytes = C::SMEM_BYTES;
+        cfg.stream = st;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        B2_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmK, tmV, p));
+    }
     if (pl.num_splits > 1) {
         merge_splits_kernel<<<dim3(p.Hq, p.B), D, 0, st>>>(p.out, p.ws_o, p.ws_lse, p.seq_lens, p.Hq, p.num_splits,
                                                            p.split_tokens, p.out_stride);

@@ -24,6 +24,9 @@ reshape_and_cache_kernel(const __nv_bfloat16* __restrict__ k_new,
                          int64_t cache_block_stride, int64_t cache_head_stride,
                          const float* __restrict__ k_scale, const float* __restrict__ v_scale,
                          int32_t* __restrict__ block_tables, const int32_t* __restrict__ seq_lens, int max_nb) {
+    // the decode kernel that follows in the stream may be launched now (programmatic dependent launch): its prologue
+    // runs under this kernel; it waits (griddepcontrol.wait) before it touches the cache or the block tables
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int t = blockIdx.x;
     const int64_t slot = slot_mapping[t];
     if (slot < 0) return;  // padding token
