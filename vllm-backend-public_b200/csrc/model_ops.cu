@@ -165,6 +165,9 @@ rope_and_cache_kernel(__nv_bfloat16* __restrict__ qkv, const int32_t* __restrict
                       void* __restrict__ v_cache, const int64_t* __restrict__ slot_mapping, int Hq, int Hkv, int d, int bs,
                       int64_t token_stride, int64_t cache_block_stride, int64_t cache_head_stride,
                       const float* __restrict__ k_scale, const float* __restrict__ v_scale) {
+    // the attention kernel that follows may be launched now (programmatic dependent launch): it waits
+    // (griddepcontrol.wait) before it reads q, the cache or the block tables
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int t = blockIdx.x;
     const int half = d >> 1;
     const int pairs_per_head = half >> 3;              // vector pairs of 8 elements

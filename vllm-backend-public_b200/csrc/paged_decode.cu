@@ -654,6 +654,8 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
             vs = *p.v_scale;     // V dequant scale folds into the epilogue
         }
         QFrags<NT> qf;
+        // q may be the output of the kernel this grid was launched under (rotary + KV write in the engine)
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         load_q_frags<FP8, NT>(qf, reinterpret_cast<const uint32_t*>(p.q + b * p.q_stride + (int64_t)head0 * D), nheads, lane);
         WarpAcc<NT> acc;
         acc.reset();
