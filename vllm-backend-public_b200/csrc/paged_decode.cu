@@ -1471,7 +1471,8 @@ int launch_decode(const CUtensorMap& tmK, const CUtensorMap& tmV, const DecodePa
         cfg.dynamicSmemBytes = C::SMEM_BYTES;
         cfg.stream = st;
         cfg.attrs = at;
-        cfg.numAttrs = 1;
+        static const int pdl = env_int("B2_DECODE_PDL", 1);      // 0: ordinary stream order (A/B)
+        cfg.numAttrs = pdl ? 1 : 0;
         B2_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tmK, tmV, p));
     }
     if (pl.num_splits > 1) {
