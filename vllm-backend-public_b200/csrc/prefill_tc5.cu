@@ -13,6 +13,19 @@
 // Issue order  QK_A(0) QK_B(0) | PV_A(j) QK_A(j+1) PV_B(j) QK_B(j+1) ...  lets the softmax of one tile run under the
 // MMAs of the other.  Rescaling of O is lazy: a row keeps its stale maximum until the true one exceeds it by 2^8.
 //
+// Round-2 experiment, not adopted (scripts/experiments_prefill_two_threads_per_row.cu.txt, ncu summary in
+// profiles/r2_ncu_prefill_two_threads_per_row.md): TWO threads per query row -- 16 softmax warps, the halves of a row
+// meeting through shared memory and a 64-thread named barrier once per step, 576 threads, no setmaxnreg.  Parity-green,
+// 1038 vs 1055 TF/s at 8k / 8k: no gain, so the softmax warps are not short of latency hiding.  What ncu shows in both
+// versions: tensor pipe 48 % and XU pipe 48 % with the softmax warps waiting for S in 56 % of their samples -- the two
+// pipes ALTERNATE.  Per 128 x 128 tile a step needs 1084 tensor cycles (P.V + Q.K^T) and >= 1024 XU cycles (16 384 exp2
+// at 16 per clock) plus the row-maximum pass, TMEM load / store and fences in front of and behind them; a tile's own
+// chain softmax(j) -> P.V(j) -> Q.K^T(j+1) -> softmax(j+1) cannot overlap itself (P overwrites S), so the other tile
+// must cover it, which needs a tile's softmax to fit in the 1084 cycles of the other tile's MMAs -- it takes about
+// twice that.  The polynomial exp2 (B2_PREFILL_POLY) is still slower in both versions.  Next: take the maximum pass
+// off the chain (exponentiate against the previous maximum while the new one is computed, redo on the rare overflow),
+// and double-buffer S at 64 columns per thread so Q.K^T(j+1) does not wait for P.V(j).
+//
 // Shared memory (1024-byte aligned, 128-byte swizzle, the canonical UMMA layouts):
 //   Q_A, Q_B     2 x [2 halves][128 rows][64 el]           K-major operand A           64 KiB
 //   stage s      K: [2 halves][128 tok][64 el]  K-major operand B (QK^T)
@@ -26,8 +39,7 @@ constexpr int D = 128;
 constexpr int BM = 128;             // rows per q tile
 constexpr int BN = 128;             // kv tokens per stage
 constexpr int NSTAGE = 2;
-constexpr int NTHREADS = 576;       // 16 softmax warps (two per 32 rows of tiles A and B) + TMA producer + MMA issuer:
-                                    // 113 registers each at launch, so no setmaxnreg re-division is needed any more
+constexpr int NTHREADS = 384;       // 3 warpgroups: softmax A, softmax B, {TMA producer, MMA issuer, 2 idle warps}
 constexpr int SUB_BYTES = 128 * 128;               // one [128 rows][64 el] sub-tile
 constexpr int TILE_BYTES = 2 * SUB_BYTES;          // 32 KiB: a 128 x 128 bf16 tile
 constexpr int Q_BYTES = 2 * TILE_BYTES;
@@ -103,20 +115,6 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
           "r"(taddr)
         : "memory");
 }
-__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
-                 : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x8.b32 [%8], {%0, %1, %2, %3, %4, %5, %6, %7};"
-        ::"r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void pair_sync(int id) {       // the two warps that share 32 query rows
-    asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
-}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
@@ -159,8 +157,6 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ int s_tile[4];
     __shared__ uint32_t s_tmem;
-    __shared__ float s_mx[2][2][2][128];      // [step parity][tile][column half][row]: row maxima of the two half-rows
-    __shared__ float s_l[2][2][128];          // [tile][column half][row]: the halves of the denominator
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int hq = blockIdx.x, kvh = hq / p.G;
@@ -192,12 +188,12 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
         for (int x = 0; x < 2; ++x) {
             b2::mbar_init(bar(BAR_S + x), 1);
-            b2::mbar_init(bar(BAR_P + x), 8);      // one arrive per softmax warp of the tile
+            b2::mbar_init(bar(BAR_P + x), 4);      // one arrive per softmax warp of the tile
             b2::mbar_init(bar(BAR_PV + x), 1);
         }
         b2::fence_mbar_init();
     }
-    if (warp == 17) {                              // TMEM: all 512 columns (one CTA per SM)
+    if (warp == 9) {                               // TMEM: all 512 columns (one CTA per SM)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(b2::smem_u32(&s_tmem)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -222,8 +218,9 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const int kv_hi = max(hiX[0], hiX[1]);
         const int row0 = active ? p.cu_q[chunk] + q0 : 0;       // first token row in q / out
 
-        if (warp >= 16) {
-        if (active && warp == 16) {
+        if (warp >= 8) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        if (active && warp == 8) {
             // ------------------------------------------ TMA producer ------------------------------------------
             if (lane == 0) {
                 b2::tma_prefetch_desc(&tmQ);
@@ -277,7 +274,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 load_tile(it, 1, wv);
             }
         }
-        else if (active && warp == 17) {
+        else if (active && warp == 9) {
             // ------------------------------------------ MMA issuer (one lane) ------------------------------------------
             if (lane == 0) {
                 constexpr uint32_t ID_QK = idesc_bf16(128, 128, 0), ID_PV = idesc_bf16(128, 128, 1);
@@ -332,54 +329,43 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
         }
         else {
+            asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
             if (active) {
-            // ------------------------------------------ softmax warps ------------------------------------------
-            // TWO threads per query row (round 2): tile x = warp / 8, TMEM lane quadrant wq = warp % 4, column half
-            // ch = (warp / 4) % 2.  With one thread per row a scheduler saw one warp per tile -- nothing hid the
-            // TMEM-load / max / exp2 / pack chain of a 128-wide row, and ncu showed the softmax warps waiting while the
-            // tensor pipe sat at 49 %.  Now four softmax warps share a scheduler and each row's work is halved; the halves
-            // meet once per step (row maximum, through shared memory and a 64-thread named barrier) and once at the
-            // end (denominator).
-            const int x = warp >> 3, wq = warp & 3, ch = (warp >> 2) & 1;
+            // ------------------------------------------ softmax warps: tile x = warp / 4 ------------------------------------------
+            const int x = warp >> 2, wq = warp & 3;
             const int row = wq * 32 + lane;                       // query row in the tile = TMEM lane
             const uint32_t lane_off = (uint32_t)(wq * 32) << 16;
-            const uint32_t s_tile = tmem + lane_off + x * 128;    // S_x; P_x overwrites its first 64 columns
-            const uint32_t s_addr = s_tile + ch * 64;             // this thread's 64 score columns
-            const uint32_t o_addr = tmem + lane_off + 256 + x * 128 + ch * 64;   // ... and its 64 output columns
-            const int pbar = 1 + x * 4 + wq;
+            const uint32_t s_addr = tmem + lane_off + x * 128, o_addr = tmem + lane_off + 256 + x * 128;
             const int n = nX[x];
             const float sl2 = p.scale_log2 * (p.k_scale ? *p.k_scale : 1.f);
             const int lim = start + q0 + x * BM + min(row, max(rowsX[x] - 1, 0));   // last key this row may see
             const int lim_min = start + q0 + x * BM;                                 // ... of the tile's first row
-            float m = -INFINITY, l = 0.f;                         // l: this thread's half of the row's denominator
+            float m = -INFINITY, l = 0.f;
             for (int j = 0; j < n; ++j) {
                 b2::mbar_wait(bar(BAR_S + x), j & 1);
                 tc_fence_after();
-                uint32_t sr[2][32];
+                uint32_t sr[4][32];
 #pragma unroll
-                for (int c = 0; c < 2; ++c) tmem_ld32(s_addr + c * 32, sr[c]);
+                for (int c = 0; c < 4; ++c) tmem_ld32(s_addr + c * 32, sr[c]);
                 tmem_wait_ld();
-                const int j0 = j * BN + ch * 64;                  // first key of this thread's columns
-                if (j * BN + BN - 1 > lim_min) {                  // tile touches the diagonal (or the end of the sequence)
+                const int j0 = j * BN;
+                if (j0 + BN - 1 > lim_min) {                      // tile touches the diagonal (or the end of the sequence)
 #pragma unroll
-                    for (int c = 0; c < 2; ++c)
+                    for (int c = 0; c < 4; ++c)
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
                             if (j0 + c * 32 + i > lim) sr[c][i] = 0xff800000u;   // -inf
                 }
-                float mxp[4];
+                // one warp per tile and scheduler: nothing hides a 128-long dependent chain, so reduce in 8 short ones
+                float mxp[8];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) mxp[k] = -INFINITY;
+                for (int k = 0; k < 8; ++k) mxp[k] = -INFINITY;
 #pragma unroll
-                for (int c = 0; c < 2; ++c)
+                for (int c = 0; c < 4; ++c)
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) mxp[i & 3] = fmaxf(mxp[i & 3], __uint_as_float(sr[c][i]));
-                float mx = fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3]));
-                // the other half of the row: both threads have their S in registers once they pass this barrier, so P may
-                // overwrite the score columns afterwards
-                s_mx[j & 1][x][ch][row] = mx;
-                pair_sync(pbar);
-                mx = fmaxf(mx, s_mx[j & 1][x][ch ^ 1][row]);
+                    for (int i = 0; i < 32; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], __uint_as_float(sr[c][i]));
+                const float mx = fmaxf(fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3])),
+                                       fmaxf(fmaxf(mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7])));
                 const float m_new = fmaxf(m, mx);                 // finite: key 0 is visible to every row, tiles in order
                 if (j == 0) {
                     m = m_new;
@@ -391,13 +377,13 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         const float alpha = need ? b2::fast_exp2((m - m_new) * sl2) : 1.f;
                         if (need) { m = m_new; l *= alpha; }
 #pragma unroll
-                        for (int c = 0; c < 8; ++c) {             // 8 columns at a time: the row's scores stay in registers
-                            uint32_t orr[8];
-                            tmem_ld8(o_addr + c * 8, orr);
+                        for (int c = 0; c < 4; ++c) {
+                            uint32_t orr[32];
+                            tmem_ld32(o_addr + c * 32, orr);
                             tmem_wait_ld();
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) orr[i] = __float_as_uint(__uint_as_float(orr[i]) * alpha);
-                            tmem_st8(o_addr + c * 8, orr);
+                            for (int i = 0; i < 32; ++i) orr[i] = __float_as_uint(__uint_as_float(orr[i]) * alpha);
+                            tmem_st32(o_addr + c * 32, orr);
                         }
                     }
                 }
@@ -405,19 +391,20 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 // l sums the fp32 weights (the bf16 rounding of P is zero-mean; FlashAttention convention), 4 chains
                 float sum[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {                     // 16 keys -> 8 packed bf16 pairs per store
-                    uint32_t pk[8];
+                for (int c = 0; c < 2; ++c) {                     // 64 keys -> 32 packed bf16 pairs per store
+                    uint32_t pk[32];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int e = (c & 1) * 16 + 2 * i;
+                    for (int i = 0; i < 32; ++i) {
+                        const int cc = 2 * c + (i >> 4), ii = (2 * i) & 31;
                         float x0, x1;
-                        fma_x2(x0, x1, __uint_as_float(sr[c >> 1][e]), __uint_as_float(sr[c >> 1][e + 1]), sl2, -ms);
+                        fma_x2(x0, x1, __uint_as_float(sr[cc][ii]), __uint_as_float(sr[cc][ii + 1]), sl2, -ms);
+                        // (i & 1, element) -> slot 0..3 of the group of four; slots < POLY go to the polynomial
                         const float p0 = (POLY >= 2 && (i & 1)) || POLY >= 3 ? poly_exp2(x0) : b2::fast_exp2(x0);
                         const float p1 = (POLY >= 1 && (i & 1)) || POLY >= 4 ? poly_exp2(x1) : b2::fast_exp2(x1);
                         pk[i] = b2::pack_bf16x2(p0, p1);
                         add_x2(sum[2 * (i & 1)], sum[2 * (i & 1) + 1], p0, p1);
                     }
-                    tmem_st8(s_tile + ch * 32 + c * 8, pk);       // P columns of keys [ch*64 + c*16, +16)
+                    tmem_st32(s_addr + c * 32, pk);               // P overwrites the first 64 columns of S_x
                 }
                 l += (sum[0] + sum[1]) + (sum[2] + sum[3]);
                 tmem_wait_st();
@@ -426,17 +413,13 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 if (lane == 0) b2::mbar_arrive(bar(BAR_P + x));
             }
             if (n > 0) {
-                // the row's denominator = both halves
-                s_l[x][ch][row] = l;
-                pair_sync(pbar);
-                l += s_l[x][ch ^ 1][row];
                 b2::mbar_wait(bar(BAR_PV + x), (n - 1) & 1);
                 tc_fence_after();
                 const float inv = (p.v_scale ? *p.v_scale : 1.f) / l;
                 const bool valid = row < rowsX[x];
-                __nv_bfloat16* orow = p.out + (int64_t)(row0 + x * BM + row) * p.out_stride + (int64_t)hq * D + ch * 64;
+                __nv_bfloat16* orow = p.out + (int64_t)(row0 + x * BM + row) * p.out_stride + (int64_t)hq * D;
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
+                for (int c = 0; c < 4; ++c) {
                     uint32_t orr[32];
                     tmem_ld32(o_addr + c * 32, orr);
                     tmem_wait_ld();
@@ -460,7 +443,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     // ------------------------------------------ teardown ------------------------------------------
     tc_fence_before();
     __syncthreads();
-    if (warp == 17) {
+    if (warp == 9) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
     }
