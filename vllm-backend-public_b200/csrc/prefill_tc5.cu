@@ -22,9 +22,11 @@
 // at 16 per clock) plus the row-maximum pass, TMEM load / store and fences in front of and behind them; a tile's own
 // chain softmax(j) -> P.V(j) -> Q.K^T(j+1) -> softmax(j+1) cannot overlap itself (P overwrites S), so the other tile
 // must cover it, which needs a tile's softmax to fit in the 1084 cycles of the other tile's MMAs -- it takes about
-// twice that.  The polynomial exp2 (B2_PREFILL_POLY) is still slower in both versions.  Next: take the maximum pass
-// off the chain (exponentiate against the previous maximum while the new one is computed, redo on the rare overflow),
-// and double-buffer S at 64 columns per thread so Q.K^T(j+1) does not wait for P.V(j).
+// twice that.  The polynomial exp2 (B2_PREFILL_POLY) is still slower in both versions, and so is taking the
+// maximum pass off the chain (exponentiating against the row's previous maximum while the tile's own is tracked in
+// the same sweep, redo on the rare overflow: parity-green, 947 TF/s) -- every instruction added to the exp2 sweep costs
+// more than the pass it removes, i.e. the sweep itself is issue-limited around the 16-per-clock MUFU.  What is left is
+// structural: S double-buffered (Q.K^T(j+1) must not wait for P.V(j)) and fewer instructions per exponentiated element.
 //
 // Shared memory (1024-byte aligned, 128-byte swizzle, the canonical UMMA layouts):
 //   Q_A, Q_B     2 x [2 halves][128 rows][64 el]           K-major operand A           64 KiB
