@@ -1,0 +1,39 @@
+"""Timeline of the prefill kernel's softmax warps (diagnostic; needs `make -C vllm-backend-public_b200/csrc trace`):
+clock64 stamps of tile A / tile B of CTA (0, 0) for the first 32 key tiles of an 8k chunk over an 8k prefix."""
+import ctypes as C
+import os
+import sys
+from pathlib import Path
+ROOT = Path(__file__).resolve().parent.parent
+os.environ.setdefault("B200ATTN_LIB", str(ROOT / "vllm-backend-public_b200/lib/libb200attn_trace.so"))
+sys.path.insert(0, str(ROOT / "vllm-backend-public_b200"))
+import numpy as np
+import torch
+import b200attn
+from b200attn import ops
+dev = torch.device("cuda:0")
+Hq, Hkv, d, bs, chunk, start = 32, 8, 128, 16, 8192, 8192
+nb = (start + chunk) // bs
+kc = torch.randn(nb + 8, Hkv, bs, d, device=dev).to(torch.bfloat16)
+vc = torch.randn(nb + 8, Hkv, bs, d, device=dev).to(torch.bfloat16)
+q = torch.randn(chunk, Hq, d, device=dev).to(torch.bfloat16)
+bt = torch.randperm(nb + 8, device=dev)[:nb].to(torch.int32).unsqueeze(0).contiguous()
+cu = torch.tensor([0, chunk], dtype=torch.int32, device=dev)
+st = torch.tensor([start], dtype=torch.int32, device=dev)
+for _ in range(3):
+    ops.prefill_attention(q, kc, vc, bt, cu, st)
+torch.cuda.synchronize()
+lib = b200attn.load()
+buf = np.zeros(2 * 32 * 5, dtype=np.uint64)
+lib.b2_debug_read_prefill_trace.argtypes = [C.c_void_p]
+lib.b2_debug_read_prefill_trace(buf.ctypes.data)
+t = buf.reshape(2, 32, 5).astype(np.int64)
+t0 = t[:, :, 0][t[:, :, 0] > 0].min()
+print("cycles relative to the first stamp; columns: S ready | S in regs | max known | P computed | P handed over")
+for j in range(8, 24):
+    for x in (0, 1):
+        r = t[x, j] - t0
+        print(f"step {j:2d} tile {'AB'[x]}: " + " ".join(f"{v:8d}" for v in r) +
+              f"   load {r[1]-r[0]:5d} max {r[2]-r[1]:5d} exp {r[3]-r[2]:5d} hand {r[4]-r[3]:5d}  wait-for-next-S {t[x, j+1, 0]-t[x, j, 4]:6d}")
+a = t[0, 8:24]
+print("period (tile A, S ready to next S ready): mean", float(np.diff(a[:, 0]).mean()))

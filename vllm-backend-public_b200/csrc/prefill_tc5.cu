@@ -26,7 +26,16 @@
 // maximum pass off the chain (exponentiating against the row's previous maximum while the tile's own is tracked in
 // the same sweep, redo on the rare overflow: parity-green, 947 TF/s) -- every instruction added to the exp2 sweep costs
 // more than the pass it removes, i.e. the sweep itself is issue-limited around the 16-per-clock MUFU.  What is left is
-// structural: S double-buffered (Q.K^T(j+1) must not wait for P.V(j)) and fewer instructions per exponentiated element.
+// structural.  The clock64 timeline of the softmax warps (`make trace` + scripts/trace_prefill.py,
+// profiles/r2_trace_prefill_softmax.txt) finally shows where the period goes: per 128-key step a tile's softmax takes
+// ~1750 cycles (TMEM load 45, maximum 370, exponentiate + pack 1300, hand-over 35) and then waits ~2300 cycles for its
+// next S -- and in that window the tensor pipe is busy the whole time with the tile's P.V + Q.K^T AND the other tile's
+// (their intervals overlap by ~500 cycles): 16 tcgen05.mma 128x128x16 take ~2050 cycles of pipe time, 126-130 cycles per
+// instruction against 68 at the 2.25 PFLOP/s rate.  So the kernel is TENSOR-ISSUE bound at about half rate, not softmax
+// bound: in SS mode at 128x128 a cta_group::1 MMA reads 4 KiB of A and 4 KiB of B from shared memory per instruction,
+// 128 B per clock at full rate -- the SM's whole shared-memory bandwidth.  That is why the softmax experiments above
+// changed nothing, and it is what `cta_group::2` is for (each CTA of the pair stages half of K / V, halving the
+// per-SM operand traffic): the next version of this kernel is a 2-CTA cluster with 256 query rows per q-tile pair.
 //
 // Shared memory (1024-byte aligned, 128-byte swizzle, the canonical UMMA layouts):
 //   Q_A, Q_B     2 x [2 halves][128 rows][64 el]           K-major operand A           64 KiB
@@ -34,6 +43,15 @@
 //                V: [2 halves][128 tok][64 el]  MN-major operand B (P.V)               2 x 64 KiB
 // One TMA box = one 64-element half of one (block, kv head) tile: bs rows x 128 B, contiguous in HBM.
 #include "b2_common.cuh"
+
+#ifdef B2_TRACE
+// diagnostic build (make trace): clock64 stamps of the softmax warps 0 (tile A) and 4 (tile B) of CTA (0, 0), lane 0,
+// for the first 32 steps: [tile][step][S ready | S in registers | maximum known | P computed | P handed to the MMA warp]
+__device__ unsigned long long g_pf_trace[2][32][5];
+#define PF_STAMP(k) do { if (trace_on && j < 32) g_pf_trace[x][j][k] = clock64(); } while (0)
+#else
+#define PF_STAMP(k) do { } while (0)
+#endif
 
 namespace {
 
@@ -343,13 +361,18 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             const int lim = start + q0 + x * BM + min(row, max(rowsX[x] - 1, 0));   // last key this row may see
             const int lim_min = start + q0 + x * BM;                                 // ... of the tile's first row
             float m = -INFINITY, l = 0.f;
+#ifdef B2_TRACE
+            const bool trace_on = blockIdx.x == 0 && blockIdx.y == 1 && wq == 0 && lane == 0;   // y = 0 is the spare (inactive) CTA of a single chunk
+#endif
             for (int j = 0; j < n; ++j) {
                 b2::mbar_wait(bar(BAR_S + x), j & 1);
                 tc_fence_after();
+                PF_STAMP(0);
                 uint32_t sr[4][32];
 #pragma unroll
                 for (int c = 0; c < 4; ++c) tmem_ld32(s_addr + c * 32, sr[c]);
                 tmem_wait_ld();
+                PF_STAMP(1);
                 const int j0 = j * BN;
                 if (j0 + BN - 1 > lim_min) {                      // tile touches the diagonal (or the end of the sequence)
 #pragma unroll
@@ -389,6 +412,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         }
                     }
                 }
+                PF_STAMP(2);
                 const float ms = m * sl2;
                 // l sums the fp32 weights (the bf16 rounding of P is zero-mean; FlashAttention convention), 4 chains
                 float sum[4] = {0.f, 0.f, 0.f, 0.f};
@@ -409,10 +433,12 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     tmem_st32(s_addr + c * 32, pk);               // P overwrites the first 64 columns of S_x
                 }
                 l += (sum[0] + sum[1]) + (sum[2] + sum[3]);
+                PF_STAMP(3);
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) b2::mbar_arrive(bar(BAR_P + x));
+                PF_STAMP(4);
             }
             if (n > 0) {
                 b2::mbar_wait(bar(BAR_PV + x), (n - 1) & 1);
@@ -504,3 +530,9 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
     B2_CUDA_OK(cudaGetLastError());
     return B2_OK;
 }
+
+#ifdef B2_TRACE
+extern "C" B2_API int b2_debug_read_prefill_trace(unsigned long long* dst) {
+    return cudaMemcpyFromSymbol(dst, g_pf_trace, sizeof(g_pf_trace)) == cudaSuccess ? 0 : B2_ECUDA;
+}
+#endif
