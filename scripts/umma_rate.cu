@@ -20,13 +20,19 @@ __device__ __forceinline__ uint32_t idesc_bf16(int M, int N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-template <int N, bool TS>
+// MODE 0: SS   1: TS, B K-major   2: TS, B MN-major (the P.V of prefill_tc5: V tile [2 halves][128 tok][64 el])
+//      3: the kernel's pair -- 8 x (TS, MN-major B) then 8 x SS, all 128 x 128 x 16
+// LOAD > 0: warps 1..3 hammer TMEM with tcgen05.ld / tcgen05.st (32 columns each) while warp 0 issues, as softmax warps do
+template <int N, int MODE, int LOAD>
 __global__ void __launch_bounds__(128, 1) probe(long long* cycles) {
-    extern __shared__ __align__(1024) uint8_t smem[];        // A: 128 x 64 bf16 (16 KiB) | B: N x 64 bf16
+    constexpr bool TS = MODE == 1 || MODE == 2;
+    extern __shared__ __align__(1024) uint8_t smem[];        // A: 128 x 64 bf16 (16 KiB) | B: up to 32 KiB
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t s_tmem;
     const int tid = threadIdx.x;
-    for (int i = tid; i < (16384 + N * 128) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0u;
+    for (int i = tid; i < (16384 + 32768) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0u;
+    __shared__ volatile int s_stop;
+    if (tid == 0) s_stop = 0;
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -42,11 +48,27 @@ __global__ void __launch_bounds__(128, 1) probe(long long* cycles) {
     const uint32_t tmem = s_tmem;
     if (tid == 0) {
         const uint32_t a = smem_u32(smem), b = a + 16384;
-        const uint32_t idesc = idesc_bf16(128, N);
+        const uint32_t idesc = idesc_bf16(128, N) | ((MODE == 2 ? 1u : 0u) << 16);
         const long long t0 = clock64();
         for (int it = 0; it < ITERS; ++it) {
             const uint32_t off = (it & 3) * 32;                // the four 16-element k-steps of a 64-element swizzle row
-            const uint64_t bd = smem_desc(b + off, 16, 1024);
+            uint64_t bd = smem_desc(b + off, 16, 1024);
+            if (MODE == 2) bd = smem_desc(b + (it & 7) * 2048, 16384, 1024);       // 16 tokens x 128 d, MN-major
+            if (MODE == 3) {
+                const bool pv = ((it >> 3) & 1) == 0;
+                if (pv) {
+                    const uint64_t vd = smem_desc(b + (it & 7) * 2048, 16384, 1024);
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                                 ::"r"(tmem + 128), "r"(tmem + 256 + (it & 7) * 8), "l"(vd), "r"(idesc | (1u << 16)), "r"(1u) : "memory");
+                } else {
+                    const uint32_t o2 = ((it & 7) >> 2) * 16384 * 0 + (it & 3) * 32;
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                                 ::"r"(tmem), "l"(smem_desc(a + o2, 16, 1024)), "l"(smem_desc(b + o2, 16, 1024)), "r"(idesc), "r"(1u) : "memory");
+                }
+                continue;
+            }
             if (TS) {
                 // A = 128 x 16 bf16 from TMEM columns [256, 264); D = columns [0, N)
                 asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -65,6 +87,34 @@ __global__ void __launch_bounds__(128, 1) probe(long long* cycles) {
             asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                          : "=r"(ok) : "r"(smem_u32(&bar)) : "memory");
         cycles[blockIdx.x] = clock64() - t0;
+        s_stop = 1;
+    } else if (LOAD > 0 && tid >= 32) {
+        // TMEM traffic of "softmax" warps: load 32 columns, store them back, on columns [384, 512) (not used by the MMAs)
+        const uint32_t taddr = tmem + ((uint32_t)((tid >> 5) * 32) << 16) + 384 + ((tid >> 5) - 1) * 32;
+        while (!s_stop) {
+            uint32_t r[32];
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                  "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                  "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            asm volatile(
+                "tcgen05.st.sync.aligned.32x32b.x32.b32 [%32], "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31};"
+                ::"r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                  "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+                  "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+                  "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]),
+                  "r"(taddr)
+                : "memory");
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -74,11 +124,12 @@ __global__ void __launch_bounds__(128, 1) probe(long long* cycles) {
     }
 }
 
-template <int N, bool TS>
+template <int N, int MODE, int LOAD = 0>
 void run(const char* name, int sms, long long* d, long long* h) {
-    const int smem = 16384 + N * 128;
-    cudaFuncSetAttribute(probe<N, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    for (int rep = 0; rep < 2; ++rep) probe<N, TS><<<sms, 128, smem>>>(d);
+    constexpr bool TS = MODE == 1 || MODE == 2;
+    const int smem = 16384 + 32768;
+    cudaFuncSetAttribute(probe<N, MODE, LOAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    for (int rep = 0; rep < 2; ++rep) probe<N, MODE, LOAD><<<sms, 128, smem>>>(d);
     if (cudaDeviceSynchronize() != cudaSuccess) { printf("%s: %s\n", name, cudaGetErrorString(cudaGetLastError())); return; }
     cudaMemcpy(h, d, sms * sizeof(long long), cudaMemcpyDeviceToHost);
     double mean = 0;
@@ -98,11 +149,16 @@ int main() {
     long long *d, *h = new long long[sms];
     cudaMalloc(&d, sms * sizeof(long long));
     printf("tcgen05.mma cta_group::1 kind::f16, M = 128, K = 16, %d back-to-back instructions per SM, all SMs busy\n", ITERS);
-    run<64, false>("SS  128 x  64 x 16", sms, d, h);
-    run<128, false>("SS  128 x 128 x 16", sms, d, h);
-    run<256, false>("SS  128 x 256 x 16", sms, d, h);
-    run<64, true>("TS  128 x  64 x 16", sms, d, h);
-    run<128, true>("TS  128 x 128 x 16", sms, d, h);
-    run<256, true>("TS  128 x 256 x 16", sms, d, h);
+    run<64, 0>("SS  128 x  64 x 16", sms, d, h);
+    run<128, 0>("SS  128 x 128 x 16", sms, d, h);
+    run<256, 0>("SS  128 x 256 x 16", sms, d, h);
+    run<64, 1>("TS  128 x  64 x 16", sms, d, h);
+    run<128, 1>("TS  128 x 128 x 16", sms, d, h);
+    run<256, 1>("TS  128 x 256 x 16", sms, d, h);
+    run<128, 2>("TS  128x128x16 B MN", sms, d, h);
+    run<128, 3>("pair 8 TS-MN + 8 SS", sms, d, h);
+    run<128, 0, 1>("SS  128x128 +TMEM io", sms, d, h);
+    run<128, 2, 1>("TS-MN 128x128 +TMEM io", sms, d, h);
+    run<128, 3, 1>("pair        +TMEM io", sms, d, h);
     return 0;
 }
