@@ -54,19 +54,33 @@ __global__ void __launch_bounds__(128, 1) probe(long long* cycles) {
             const uint32_t off = (it & 3) * 32;                // the four 16-element k-steps of a 64-element swizzle row
             uint64_t bd = smem_desc(b + off, 16, 1024);
             if (MODE == 2) bd = smem_desc(b + (it & 7) * 2048, 16384, 1024);       // 16 tokens x 128 d, MN-major
-            if (MODE == 3) {
-                const bool pv = ((it >> 3) & 1) == 0;
-                if (pv) {
-                    const uint64_t vd = smem_desc(b + (it & 7) * 2048, 16384, 1024);
+            if (MODE >= 3) {
+                // groups of GROUP instructions alternate between two kinds X / Y:
+                //   3: X = TS, B MN-major (P.V)   Y = SS (Q.K^T)          -- the prefill kernel's pair, GROUP 8
+                //   4: X = TS, B MN-major         Y = TS, B K-major       -- only the B layout (idesc) changes
+                //   5: X = SS into D columns 0    Y = SS into D columns 128 -- only the accumulator changes
+                //   6: X = TS, B K-major          Y = SS                  -- only the A source changes
+                //   7: as 3 with GROUP 16        8: as 3 with GROUP 32
+                constexpr int GROUP = MODE == 7 ? 16 : MODE == 8 ? 32 : 8;
+                const bool first = ((it / GROUP) & 1) == 0;
+                const uint32_t o2 = (it & 3) * 32;
+                const uint64_t vd = smem_desc(b + (it & 7) * 2048, 16384, 1024), kd = smem_desc(b + o2, 16, 1024);
+                const uint64_t ad = smem_desc(a + o2, 16, 1024);
+                const uint32_t ta = tmem + 256 + (it & 7) * 8;
+                const int kind = MODE == 4 ? (first ? 0 : 1) : MODE == 5 ? (first ? 2 : 3) : MODE == 6 ? (first ? 1 : 2)
+                                                                                           : (first ? 0 : 2);
+                if (kind == 0)          // TS, MN-major B, D at +128
                     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                                  "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                                 ::"r"(tmem + 128), "r"(tmem + 256 + (it & 7) * 8), "l"(vd), "r"(idesc | (1u << 16)), "r"(1u) : "memory");
-                } else {
-                    const uint32_t o2 = ((it & 7) >> 2) * 16384 * 0 + (it & 3) * 32;
+                                 ::"r"(tmem + 128), "r"(ta), "l"(vd), "r"(idesc | (1u << 16)), "r"(1u) : "memory");
+                else if (kind == 1)     // TS, K-major B, D at 0
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                                 ::"r"(tmem), "r"(ta), "l"(kd), "r"(idesc), "r"(1u) : "memory");
+                else                    // SS, D at 0 (kind 2) or +128 (kind 3)
                     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                                  "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                                 ::"r"(tmem), "l"(smem_desc(a + o2, 16, 1024)), "l"(smem_desc(b + o2, 16, 1024)), "r"(idesc), "r"(1u) : "memory");
-                }
+                                 ::"r"(tmem + (kind == 3 ? 128 : 0)), "l"(ad), "l"(kd), "r"(idesc), "r"(1u) : "memory");
                 continue;
             }
             if (TS) {
@@ -156,9 +170,13 @@ int main() {
     run<128, 1>("TS  128 x 128 x 16", sms, d, h);
     run<256, 1>("TS  128 x 256 x 16", sms, d, h);
     run<128, 2>("TS  128x128x16 B MN", sms, d, h);
-    run<128, 3>("pair 8 TS-MN + 8 SS", sms, d, h);
+    run<128, 3>("8 TS-MN | 8 SS (pair)", sms, d, h);
+    run<128, 4>("8 TS-MN | 8 TS-K", sms, d, h);
+    run<128, 5>("8 SS D0 | 8 SS D128", sms, d, h);
+    run<128, 6>("8 TS-K  | 8 SS", sms, d, h);
+    run<128, 7>("16 TS-MN | 16 SS", sms, d, h);
+    run<128, 8>("32 TS-MN | 32 SS", sms, d, h);
     run<128, 0, 1>("SS  128x128 +TMEM io", sms, d, h);
-    run<128, 2, 1>("TS-MN 128x128 +TMEM io", sms, d, h);
     run<128, 3, 1>("pair        +TMEM io", sms, d, h);
     return 0;
 }
