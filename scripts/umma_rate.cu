@@ -49,40 +49,54 @@ __global__ void __launch_bounds__(128, 1) probe(long long* cycles) {
     if (tid == 0) {
         const uint32_t a = smem_u32(smem), b = a + 16384;
         const uint32_t idesc = idesc_bf16(128, N) | ((MODE == 2 ? 1u : 0u) << 16);
+        if (MODE >= 3) {
+            // groups of GROUP instructions alternate between two kinds X / Y (descriptors precomputed, groups unrolled,
+            // so the issuing thread executes almost nothing but the MMAs):
+            //   3: X = TS, B MN-major (P.V)   Y = SS (Q.K^T)            -- the prefill kernel's pair, GROUP 8
+            //   4: X = TS, B MN-major         Y = TS, B K-major         -- only the B layout (idesc) changes
+            //   5: X = SS into D columns 0    Y = SS into D columns 128 -- only the accumulator changes
+            //   6: X = TS, B K-major          Y = SS                    -- only the A source changes
+            //   7: as 3 with GROUP 16         8: as 3 with GROUP 32
+            constexpr int GROUP = MODE == 7 ? 16 : MODE == 8 ? 32 : 8;
+            constexpr int KX = MODE == 4 ? 0 : MODE == 5 ? 2 : MODE == 6 ? 1 : 0;
+            constexpr int KY = MODE == 4 ? 1 : MODE == 5 ? 3 : 2;
+            uint64_t vd[8], kd[4], ad[4];
+            for (int i = 0; i < 8; ++i) vd[i] = smem_desc(b + i * 2048, 16384, 1024);
+            for (int i = 0; i < 4; ++i) { kd[i] = smem_desc(b + i * 32, 16, 1024); ad[i] = smem_desc(a + i * 32, 16, 1024); }
+            auto issue = [&](int kind, int i) {
+                if (kind == 0)          // TS, MN-major B, D at +128
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                                 ::"r"(tmem + 128), "r"(tmem + 256 + (i & 7) * 8), "l"(vd[i & 7]), "r"(idesc | (1u << 16)), "r"(1u) : "memory");
+                else if (kind == 1)     // TS, K-major B, D at 0
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                                 ::"r"(tmem), "r"(tmem + 256 + (i & 7) * 8), "l"(kd[i & 3]), "r"(idesc), "r"(1u) : "memory");
+                else                    // SS, D at 0 (kind 2) or +128 (kind 3)
+                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                                 ::"r"(tmem + (kind == 3 ? 128 : 0)), "l"(ad[i & 3]), "l"(kd[i & 3]), "r"(idesc), "r"(1u) : "memory");
+            };
+            const long long t0 = clock64();
+            for (int it = 0; it < ITERS; it += 2 * GROUP) {
+#pragma unroll
+                for (int i = 0; i < GROUP; ++i) issue(KX, i);
+#pragma unroll
+                for (int i = 0; i < GROUP; ++i) issue(KY, i);
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+            uint32_t ok = 0;
+            while (!ok)
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(ok) : "r"(smem_u32(&bar)) : "memory");
+            cycles[blockIdx.x] = clock64() - t0;
+            s_stop = 1;
+        } else {
         const long long t0 = clock64();
         for (int it = 0; it < ITERS; ++it) {
             const uint32_t off = (it & 3) * 32;                // the four 16-element k-steps of a 64-element swizzle row
             uint64_t bd = smem_desc(b + off, 16, 1024);
             if (MODE == 2) bd = smem_desc(b + (it & 7) * 2048, 16384, 1024);       // 16 tokens x 128 d, MN-major
-            if (MODE >= 3) {
-                // groups of GROUP instructions alternate between two kinds X / Y:
-                //   3: X = TS, B MN-major (P.V)   Y = SS (Q.K^T)          -- the prefill kernel's pair, GROUP 8
-                //   4: X = TS, B MN-major         Y = TS, B K-major       -- only the B layout (idesc) changes
-                //   5: X = SS into D columns 0    Y = SS into D columns 128 -- only the accumulator changes
-                //   6: X = TS, B K-major          Y = SS                  -- only the A source changes
-                //   7: as 3 with GROUP 16        8: as 3 with GROUP 32
-                constexpr int GROUP = MODE == 7 ? 16 : MODE == 8 ? 32 : 8;
-                const bool first = ((it / GROUP) & 1) == 0;
-                const uint32_t o2 = (it & 3) * 32;
-                const uint64_t vd = smem_desc(b + (it & 7) * 2048, 16384, 1024), kd = smem_desc(b + o2, 16, 1024);
-                const uint64_t ad = smem_desc(a + o2, 16, 1024);
-                const uint32_t ta = tmem + 256 + (it & 7) * 8;
-                const int kind = MODE == 4 ? (first ? 0 : 1) : MODE == 5 ? (first ? 2 : 3) : MODE == 6 ? (first ? 1 : 2)
-                                                                                           : (first ? 0 : 2);
-                if (kind == 0)          // TS, MN-major B, D at +128
-                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                                 ::"r"(tmem + 128), "r"(ta), "l"(vd), "r"(idesc | (1u << 16)), "r"(1u) : "memory");
-                else if (kind == 1)     // TS, K-major B, D at 0
-                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                                 ::"r"(tmem), "r"(ta), "l"(kd), "r"(idesc), "r"(1u) : "memory");
-                else                    // SS, D at 0 (kind 2) or +128 (kind 3)
-                    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                                 ::"r"(tmem + (kind == 3 ? 128 : 0)), "l"(ad), "l"(kd), "r"(idesc), "r"(1u) : "memory");
-                continue;
-            }
             if (TS) {
                 // A = 128 x 16 bf16 from TMEM columns [256, 264); D = columns [0, N)
                 asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -102,6 +116,7 @@ __global__ void __launch_bounds__(128, 1) probe(long long* cycles) {
                          : "=r"(ok) : "r"(smem_u32(&bar)) : "memory");
         cycles[blockIdx.x] = clock64() - t0;
         s_stop = 1;
+        }
     } else if (LOAD > 0 && tid >= 32) {
         // TMEM traffic of "softmax" warps: load 32 columns, store them back, on columns [384, 512) (not used by the MMAs)
         const uint32_t taddr = tmem + ((uint32_t)((tid >> 5) * 32) << 16) + 384 + ((tid >> 5) - 1) * 32;
