@@ -22,6 +22,7 @@ ap.add_argument("--steps", type=int, default=100)
 ap.add_argument("--only", choices=["all", "prefill", "ops", "decode", "gemm"], default="all")
 ap.add_argument("--batch", type=int, default=64)
 ap.add_argument("--ctx", type=int, default=4096)
+ap.add_argument("--prefill-bs", type=int, default=16, help="KV block size of the prefill attention runs (one TMA box = bs rows)")
 ap.add_argument("--kv", choices=["auto", "fp8"], default="auto", help="KV cache dtype of the whole-model decode run")
 a = ap.parse_args()
 dev = torch.device("cuda:0")
@@ -58,7 +59,7 @@ def emit(**kw):
 
 
 # ---------------------------------------------------------------- prefill attention
-Hq, Hkv, d, bs = 32, 8, 128, 16
+Hq, Hkv, d, bs = 32, 8, 128, a.prefill_bs
 g = torch.Generator(device=dev).manual_seed(0)
 for chunk, start in ((8192, 0), (8192, 8192), (8192, 24576), (2048, 0), (512, 3584)) if a.only in ("all", "prefill") else ():
     total = start + chunk
@@ -74,7 +75,7 @@ for chunk, start in ((8192, 0), (8192, 8192), (8192, 24576), (2048, 0), (512, 35
     med, best = timeit(lambda: ops.prefill_attention(q, kc, vc, bt, cu, st, out=out), iters=10)
     pairs = chunk * start + chunk * (chunk + 1) // 2
     flops = 4 * d * Hq * pairs
-    emit(op="prefill_attention", chunk=chunk, prefix=start, Hq=Hq, Hkv=Hkv, ms=med, ms_min=best,
+    emit(op="prefill_attention", chunk=chunk, prefix=start, block_size=bs, Hq=Hq, Hkv=Hkv, ms=med, ms_min=best,
          tflops=flops / med / 1e9, frac_of_measured_bf16=flops / med / 1e9 / TF, peak_tflops=TF,
          note="causal flops only (4*d per visible (q,k) pair)")
 

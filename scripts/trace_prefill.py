@@ -24,16 +24,20 @@ for _ in range(3):
     ops.prefill_attention(q, kc, vc, bt, cu, st)
 torch.cuda.synchronize()
 lib = b200attn.load()
-buf = np.zeros(2 * 32 * 5, dtype=np.uint64)
+buf = np.zeros(2 * 32 * 12, dtype=np.uint64)
 lib.b2_debug_read_prefill_trace.argtypes = [C.c_void_p]
 lib.b2_debug_read_prefill_trace(buf.ctypes.data)
-t = buf.reshape(2, 32, 5).astype(np.int64)
+t = buf.reshape(2, 32, 12).astype(np.int64)
 t0 = t[:, :, 0][t[:, :, 0] > 0].min()
 print("cycles relative to the first stamp; columns: S ready | S in regs | max known | P computed | P handed over")
 for j in range(8, 24):
     for x in (0, 1):
-        r = t[x, j] - t0
+        r = t[x, j, :5] - t0
+        i = t[x, j, 5:] - t0
+        w = t[x, j, 9:12] - t[x, j, 4]
         print(f"step {j:2d} tile {'AB'[x]}: " + " ".join(f"{v:8d}" for v in r) +
-              f"   load {r[1]-r[0]:5d} max {r[2]-r[1]:5d} exp {r[3]-r[2]:5d} hand {r[4]-r[3]:5d}  wait-for-next-S {t[x, j+1, 0]-t[x, j, 4]:6d}")
+              f"   load {r[1]-r[0]:5d} max {r[2]-r[1]:5d} exp {r[3]-r[2]:5d} hand {r[4]-r[3]:5d}  wait-for-next-S {t[x, j+1, 0]-t[x, j, 4]:6d}"
+              f" | issuer: P seen +{i[0]-r[4]:5d} PV issued +{i[1]-i[0]:5d} QK issued +{i[2]-i[1]:5d} -> S ready +{t[x, j+1, 0]-t0-i[2]:5d}"
+              f" | warps 1-3 hand over {w[0]:+5d} {w[1]:+5d} {w[2]:+5d} after warp 0" + (f" | V,K waits done {i[3]-r[4]:+6d} vs P handed" if x == 0 else ""))
 a = t[0, 8:24]
 print("period (tile A, S ready to next S ready): mean", float(np.diff(a[:, 0]).mean()))

@@ -47,10 +47,12 @@
 #ifdef B2_TRACE
 // diagnostic build (make trace): clock64 stamps of the softmax warps 0 (tile A) and 4 (tile B) of CTA (0, 0), lane 0,
 // for the first 32 steps: [tile][step][S ready | S in registers | maximum known | P computed | P handed to the MMA warp]
-__device__ unsigned long long g_pf_trace[2][32][5];
+__device__ unsigned long long g_pf_trace[2][32][12];  // 5..8: the MMA issuer -- P seen | P.V issued | Q.K^T issued | V, K waits done; 9..11: P handed over by warps 1..3 of the tile
 #define PF_STAMP(k) do { if (trace_on && j < 32) g_pf_trace[x][j][k] = clock64(); } while (0)
+#define PF_ISSUE_STAMP(k) do { if (blockIdx.x == 0 && blockIdx.y == 1 && j < 32) g_pf_trace[x][j][k] = clock64(); } while (0)
 #else
 #define PF_STAMP(k) do { } while (0)
+#define PF_ISSUE_STAMP(k) do { } while (0)
 #endif
 
 namespace {
@@ -104,6 +106,18 @@ __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
                  ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"((uint32_t)acc) : "memory");
+}
+// The descriptor of a tile is constant except for the 14-bit start address (bytes >> 4) in its low word: the issuing
+// thread keeps one low word per operand and advances it with an immediate add per k-step.  (Round 2: building both
+// 64-bit descriptors from scratch for every instruction made the ONE issuing thread the bottleneck -- ~130 cycles per
+// MMA against the 64 the tensor pipe needs, scripts/umma_rate.cu.)
+__device__ __forceinline__ uint32_t desc_lo(uint32_t addr, uint32_t lbo_bytes) {
+    return ((addr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
+}
+__device__ __forceinline__ uint64_t desc_join(uint32_t lo) {           // SBO = 1024 B, version 1, SWIZZLE_128B
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"((1024u >> 4) | (1u << 14) | (2u << 29)));
+    return d;
 }
 __device__ __forceinline__ void mma_commit(uint32_t bar) {       // arrives on `bar` when all MMAs issued so far are done
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -240,17 +254,22 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 
         if (warp >= 8) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
-        if (active && warp == 8) {
-            // ------------------------------------------ TMA producer ------------------------------------------
+        if (active && (warp == 8 || warp == 10)) {
+            // ------------------------------------------ TMA producers: warp 8 streams K (and Q), warp 10 streams V ------------------------------------------
+            // One box = one 64-element half of one (block, kv head) tile = bs x 128 B; at block_size 16 a 128-token tile
+            // is 16 boxes.  Each box is issued by its own lane (a lone lane issuing all 32 boxes of a step one after the
+            // other took longer than the step: the MMA warp waited ~800 cycles per step for V(j) / K(j+1), see
+            // profiles/r2_trace_prefill_issuer.txt), and K and V wait for their own empty barriers in separate warps.
+            const int kv = warp == 10;
+            const CUtensorMap* tm = kv ? &tmV : &tmK;
             if (lane == 0) {
-                b2::tma_prefetch_desc(&tmQ);
-                b2::tma_prefetch_desc(&tmK);
-                b2::tma_prefetch_desc(&tmV);
+                if (!kv) b2::tma_prefetch_desc(&tmQ);
+                b2::tma_prefetch_desc(tm);
             }
             uint64_t pol_keep, pol_once;
             asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
             asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_once));
-            if (lane == 0) {
+            if (!kv && lane == 0) {
                 b2::mbar_arrive_expect_tx(bar(BAR_Q), Q_BYTES);
                 for (int x = 0; x < 2; ++x)
                     for (int h = 0; h < 2; ++h)                 // rows past T are zero-filled by the TMA unit
@@ -261,49 +280,44 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             const int bps = BN / p.bs;
             const uint32_t box = p.bs * 128;                    // bytes of one half-tile box
             const int n_blk = (kv_hi + p.bs - 1) / p.bs;
-            // one 128-token K (kv = 0) or V (kv = 1) tile: two half-tile boxes per block
-            auto load_tile = [&](int it, int kv, int win) {
+            const int jb = lane >> 1, h = lane & 1;             // this lane's box of a tile: block jb, half h
+            int win = 0;                                        // the 32 table entries that hold the current tiles
+            for (int it = 0; it < n_tiles; ++it) {
+                if (((it * bps) & 31) == 0) {                   // bps divides 32: a tile never straddles a window
+                    const int first = it * bps;
+                    win = first + lane < n_blk ? bt[first + lane] : 0;
+                }
                 const uint32_t s = it % NSTAGE, ph = (it / NSTAGE) & 1;
                 b2::mbar_wait(bar((kv ? BAR_VE : BAR_KE) + s), ph ^ 1);
                 const int nb = min(bps, n_blk - it * bps);
-                const uint32_t dst0 = ring + s * STAGE_BYTES + kv * TILE_BYTES;
                 const uint32_t fb = bar((kv ? BAR_V : BAR_K) + s);
-                const CUtensorMap* tm = kv ? &tmV : &tmK;
                 if (lane == 0) b2::mbar_arrive_expect_tx(fb, nb * 2 * box);
-                for (int j = 0; j < bps; ++j) {         // bps divides 32: a tile never straddles a 32-entry window
-                    const int blk = __shfl_sync(0xffffffffu, win, (it * bps + j) & 31);
-                    if (j < nb && lane == 0) {
-                        b2::tma_load_5d(dst0 + j * box, tm, fb, 0, 0, 0, kvh, blk, pol_keep);
-                        b2::tma_load_5d(dst0 + SUB_BYTES + j * box, tm, fb, 0, 1, 0, kvh, blk, pol_keep);
-                    }
-                }
-            };
-            auto window = [&](int it) {                 // the 32 table entries that hold tile `it`
-                const int first = (it * bps) & ~31;
-                return first + lane < n_blk ? bt[first + lane] : 0;
-            };
-            // order of need: K(0) | K(1) V(0) | K(2) V(1) | ...
-            int wk = window(0), wv = wk;
-            load_tile(0, 0, wk);
-            for (int it = 0; it < n_tiles; ++it) {
-                if (it + 1 < n_tiles) {
-                    if ((((it + 1) * bps) & 31) == 0) wk = window(it + 1);
-                    load_tile(it + 1, 0, wk);
-                }
-                if (it > 0 && ((it * bps) & 31) == 0) wv = window(it);
-                load_tile(it, 1, wv);
+                __syncwarp();
+                const int blk = __shfl_sync(0xffffffffu, win, (it * bps + jb) & 31);
+                if (jb < nb)
+                    b2::tma_load_5d(ring + s * STAGE_BYTES + kv * TILE_BYTES + h * SUB_BYTES + jb * box, tm, fb, 0, h, 0, kvh,
+                                    blk, pol_keep);
             }
         }
         else if (active && warp == 9) {
             // ------------------------------------------ MMA issuer (one lane) ------------------------------------------
             if (lane == 0) {
                 constexpr uint32_t ID_QK = idesc_bf16(128, 128, 0), ID_PV = idesc_bf16(128, 128, 1);
+                // low descriptor words of the operands (see desc_lo): Q_x, the K half and the V half of each stage
+                const uint32_t q_lo[2] = {desc_lo(q_smem, 16), desc_lo(q_smem + TILE_BYTES, 16)};
+                uint32_t k_lo[NSTAGE], v_lo[NSTAGE];
+#pragma unroll
+                for (int s = 0; s < NSTAGE; ++s) {
+                    k_lo[s] = desc_lo(ring + s * STAGE_BYTES, 16);
+                    v_lo[s] = desc_lo(ring + s * STAGE_BYTES + TILE_BYTES, SUB_BYTES);
+                }
                 auto issue_qk = [&](int x, int j) {        // S_x = Q_x . K(j)^T : 8 k-steps of 16 over d
-                    const uint32_t kb = ring + (j % NSTAGE) * STAGE_BYTES, qb = q_smem + x * TILE_BYTES;
+                    const uint32_t kl = k_lo[j % NSTAGE], ql = q_lo[x];
 #pragma unroll
                     for (int kk = 0; kk < 8; ++kk) {
-                        const uint32_t off = (kk >> 2) * SUB_BYTES + (kk & 3) * 32;
-                        mma_ss(tmem + x * 128, smem_desc(qb + off, 16, 1024), smem_desc(kb + off, 16, 1024), ID_QK, kk > 0);
+                        constexpr int dummy = 0; (void)dummy;
+                        const uint32_t off16 = (uint32_t)(((kk >> 2) * SUB_BYTES + (kk & 3) * 32) >> 4);
+                        mma_ss(tmem + x * 128, desc_join(ql + off16), desc_join(kl + off16), ID_QK, kk > 0);
                     }
                     mma_commit(bar(BAR_S + x));
                 };
@@ -329,20 +343,34 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         b2::fence_proxy_async();
                     }
                     const bool more = j + 1 < n_tiles;
-                    if (more) b2::mbar_wait(bar(BAR_K + (j + 1) % NSTAGE), ((j + 1) / NSTAGE) & 1);
+                    { const int x = 0; PF_ISSUE_STAMP(8); }
                     for (int x = 0; x < 2; ++x) {
                         if (j < nX[x]) {
                             b2::mbar_wait(bar(BAR_P + x), j & 1);          // P_x(j) is in TMEM, O_x rescaled if needed
                             tc_fence_after();
+                            PF_ISSUE_STAMP(5);
                             const int ksteps = min(8, (hiX[x] - j * BN + 15) >> 4);
-                            for (int t = 0; t < ksteps; ++t)               // O_x += P_x . V(j) : k-steps of 16 tokens
-                                mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, smem_desc(vb + t * 2048, SUB_BYTES, 1024),
-                                       ID_PV, j > 0 || t > 0);
+                            const uint32_t vl = v_lo[s];
+                            if (ksteps == 8) {                             // O_x += P_x . V(j) : k-steps of 16 tokens
+#pragma unroll
+                                for (int t = 0; t < 8; ++t)
+                                    mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
+                                           j > 0 || t > 0);
+                            } else {
+                                for (int t = 0; t < ksteps; ++t)
+                                    mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
+                                           j > 0 || t > 0);
+                            }
                             mma_commit(bar(BAR_PV + x));
+                            PF_ISSUE_STAMP(6);
                         }
-                        if (j + 1 < nX[x]) issue_qk(x, j + 1);
+                        if (x == 1) mma_commit(bar(BAR_VE + s));            // V(j) consumed: its stage refills under the Q.K^T below
+                        if (j + 1 < nX[x]) {
+                            b2::mbar_wait(bar(BAR_K + (j + 1) % NSTAGE), ((j + 1) / NSTAGE) & 1);
+                            issue_qk(x, j + 1);
+                        }
+                        PF_ISSUE_STAMP(7);
                     }
-                    mma_commit(bar(BAR_VE + s));                            // V(j) consumed
                     if (more) mma_commit(bar(BAR_KE + (j + 1) % NSTAGE));  // K(j+1) consumed (both tiles issued above)
                 }
             }
@@ -439,6 +467,9 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 __syncwarp();
                 if (lane == 0) b2::mbar_arrive(bar(BAR_P + x));
                 PF_STAMP(4);
+#ifdef B2_TRACE
+                if (blockIdx.x == 0 && blockIdx.y == 1 && wq > 0 && lane == 0 && j < 32) g_pf_trace[x][j][8 + wq] = clock64();
+#endif
             }
             if (n > 0) {
                 b2::mbar_wait(bar(BAR_PV + x), (n - 1) & 1);
