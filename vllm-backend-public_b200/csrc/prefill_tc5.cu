@@ -47,9 +47,9 @@
 #ifdef B2_TRACE
 // diagnostic build (make trace): clock64 stamps of the softmax warps 0 (tile A) and 4 (tile B) of CTA (0, 0), lane 0,
 // for the first 32 steps: [tile][step][S ready | S in registers | maximum known | P computed | P handed to the MMA warp]
-__device__ unsigned long long g_pf_trace[2][32][12];  // 5..8: the MMA issuer -- P seen | P.V issued | Q.K^T issued | V, K waits done; 9..11: P handed over by warps 1..3 of the tile
+__device__ unsigned long long g_pf_trace[2][32][16];  // 5..8: the MMA issuer -- P seen | P.V issued | Q.K^T issued | V, K waits done; 9..11: P handed over by warps 1..3 of the tile; 12, 13: producer of K (x = 0) / V (x = 1) -- stage free | boxes issued; 14: K(j+1) (x = 0) / V(j) (x = 1) seen full by the issuer; 15: ... landed (watcher warp 11)
 #define PF_STAMP(k) do { if (trace_on && j < 32) g_pf_trace[x][j][k] = clock64(); } while (0)
-#define PF_ISSUE_STAMP(k) do { if (blockIdx.x == 0 && blockIdx.y == 1 && j < 32) g_pf_trace[x][j][k] = clock64(); } while (0)
+#define PF_ISSUE_STAMP(k) do { if ((threadIdx.x & 31) == 0 && blockIdx.x == 0 && blockIdx.y == 1 && j < 32) g_pf_trace[x][j][k] = clock64(); } while (0)
 #else
 #define PF_STAMP(k) do { } while (0)
 #define PF_ISSUE_STAMP(k) do { } while (0)
@@ -122,6 +122,11 @@ __device__ __forceinline__ uint64_t desc_join(uint32_t lo) {           // SBO = 
 __device__ __forceinline__ void mma_commit(uint32_t bar) {       // arrives on `bar` when all MMAs issued so far are done
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+__device__ __forceinline__ bool elect_one() {                   // true in exactly one lane of the (converged) warp
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -192,7 +197,8 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     __shared__ int s_tile[4];
     __shared__ uint32_t s_tmem;
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // warp-uniform for the compiler too (see the MMA issuer)
     const int hq = blockIdx.x, kvh = hq / p.G;
     const uint32_t sbase = b2::smem_u32(smem_raw);
     const uint32_t q_smem = sbase;
@@ -289,6 +295,9 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 }
                 const uint32_t s = it % NSTAGE, ph = (it / NSTAGE) & 1;
                 b2::mbar_wait(bar((kv ? BAR_VE : BAR_KE) + s), ph ^ 1);
+#ifdef B2_TRACE
+                if (blockIdx.x == 0 && blockIdx.y == 1 && lane == 0 && it < 32) g_pf_trace[kv][it][12] = clock64();
+#endif
                 const int nb = min(bps, n_blk - it * bps);
                 const uint32_t fb = bar((kv ? BAR_V : BAR_K) + s);
                 if (lane == 0) b2::mbar_arrive_expect_tx(fb, nb * 2 * box);
@@ -297,36 +306,56 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 if (jb < nb)
                     b2::tma_load_5d(ring + s * STAGE_BYTES + kv * TILE_BYTES + h * SUB_BYTES + jb * box, tm, fb, 0, h, 0, kvh,
                                     blk, pol_keep);
+#ifdef B2_TRACE
+                if (blockIdx.x == 0 && blockIdx.y == 1 && lane == 0 && it < 32) g_pf_trace[kv][it][13] = clock64();
+#endif
             }
         }
-        else if (active && warp == 9) {
-            // ------------------------------------------ MMA issuer (one lane) ------------------------------------------
-            if (lane == 0) {
-                constexpr uint32_t ID_QK = idesc_bf16(128, 128, 0), ID_PV = idesc_bf16(128, 128, 1);
-                // low descriptor words of the operands (see desc_lo): Q_x, the K half and the V half of each stage
-                const uint32_t q_lo[2] = {desc_lo(q_smem, 16), desc_lo(q_smem + TILE_BYTES, 16)};
-                uint32_t k_lo[NSTAGE], v_lo[NSTAGE];
-#pragma unroll
-                for (int s = 0; s < NSTAGE; ++s) {
-                    k_lo[s] = desc_lo(ring + s * STAGE_BYTES, 16);
-                    v_lo[s] = desc_lo(ring + s * STAGE_BYTES + TILE_BYTES, SUB_BYTES);
+#ifdef B2_TRACE
+        else if (active && warp == 11) {                // trace build only: when do the K / V tiles actually land
+            if (lane == 0 && blockIdx.x == 0 && blockIdx.y == 1)
+                for (int it = 0; it < min(n_tiles, 32); ++it) {
+                    const uint32_t s = it % NSTAGE, ph = (it / NSTAGE) & 1;
+                    b2::mbar_wait(bar(BAR_K + s), ph);
+                    g_pf_trace[0][it][15] = clock64();
+                    b2::mbar_wait(bar(BAR_V + s), ph);
+                    g_pf_trace[1][it][15] = clock64();
                 }
+        }
+#endif
+        else if (active && warp == 9) {
+            // ------------------------------------------ MMA issuer ------------------------------------------
+            // The WHOLE warp runs this loop with warp-uniform control flow and operands (`warp` comes from a shuffle,
+            // every address below derives from kernel parameters and loop counters), and one elected lane issues each
+            // group of instructions.  Round 2: with the loop inside `if (lane == 0)` the operands lived in per-thread
+            // registers and ptxas wrapped EVERY tcgen05.mma in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop of ~12
+            // dependent instructions; sharing its scheduler with two softmax warps, the issuing thread then needed
+            // 80-105 cycles per instruction where the pipe needs 64 (profiles/r2_trace_prefill_issuer.txt).
+            {
+                constexpr uint32_t ID_QK = idesc_bf16(128, 128, 0), ID_PV = idesc_bf16(128, 128, 1);
+                // low descriptor words of the operands (see desc_lo): Q_x, the K half and the V half of stage 0
+                const uint32_t q_lo0 = desc_lo(q_smem, 16);
+                const uint32_t k_lo0 = desc_lo(ring, 16), v_lo0 = desc_lo(ring + TILE_BYTES, SUB_BYTES);
                 auto issue_qk = [&](int x, int j) {        // S_x = Q_x . K(j)^T : 8 k-steps of 16 over d
-                    const uint32_t kl = k_lo[j % NSTAGE], ql = q_lo[x];
+                    const uint32_t kl = k_lo0 + (uint32_t)(j % NSTAGE) * (STAGE_BYTES >> 4);
+                    const uint32_t ql = q_lo0 + (uint32_t)x * (TILE_BYTES >> 4);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int kk = 0; kk < 8; ++kk) {
-                        constexpr int dummy = 0; (void)dummy;
-                        const uint32_t off16 = (uint32_t)(((kk >> 2) * SUB_BYTES + (kk & 3) * 32) >> 4);
-                        mma_ss(tmem + x * 128, desc_join(ql + off16), desc_join(kl + off16), ID_QK, kk > 0);
+                        for (int kk = 0; kk < 8; ++kk) {
+                            const uint32_t off16 = (uint32_t)(((kk >> 2) * SUB_BYTES + (kk & 3) * 32) >> 4);
+                            mma_ss(tmem + x * 128, desc_join(ql + off16), desc_join(kl + off16), ID_QK, kk > 0);
+                        }
+                        mma_commit(bar(BAR_S + x));
                     }
-                    mma_commit(bar(BAR_S + x));
+                    __syncwarp();
                 };
                 b2::mbar_wait(bar(BAR_Q), 0);
                 b2::mbar_wait(bar(BAR_K + 0), 0);
                 tc_fence_after();
                 for (int x = 0; x < 2; ++x)
                     if (nX[x] > 0) issue_qk(x, 0);
-                mma_commit(bar(BAR_KE + 0));                                   // K(0) consumed
+                if (elect_one()) mma_commit(bar(BAR_KE + 0));                  // K(0) consumed
+                __syncwarp();
                 for (int j = 0; j < n_tiles; ++j) {
                     const uint32_t s = j % NSTAGE;
                     const uint32_t vb = ring + s * STAGE_BYTES + TILE_BYTES;
@@ -336,13 +365,14 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         // zero the ones the last 16-token k-step still reads, so 0 * NaN cannot reach an accumulator
                         const int valid = kv_hi - j * BN;
                         const int upto = min(BN, (valid + 15) & ~15);
-                        for (int r = valid; r < upto; ++r)
-                            for (int h = 0; h < 2; ++h)
-                                for (int c = 0; c < 8; ++c)
-                                    asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(vb + h * SUB_BYTES + r * 128 + c * 16), "r"(0) : "memory");
+                        if (lane < 16)                            // lane = (half, 16-byte column)
+                            for (int r = valid; r < upto; ++r)
+                                asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(vb + (lane >> 3) * SUB_BYTES + r * 128 + (lane & 7) * 16), "r"(0) : "memory");
                         b2::fence_proxy_async();
+                        __syncwarp();
                     }
                     const bool more = j + 1 < n_tiles;
+                    { const int x = 1; PF_ISSUE_STAMP(14); }
                     { const int x = 0; PF_ISSUE_STAMP(8); }
                     for (int x = 0; x < 2; ++x) {
                         if (j < nX[x]) {
@@ -350,28 +380,40 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                             tc_fence_after();
                             PF_ISSUE_STAMP(5);
                             const int ksteps = min(8, (hiX[x] - j * BN + 15) >> 4);
-                            const uint32_t vl = v_lo[s];
-                            if (ksteps == 8) {                             // O_x += P_x . V(j) : k-steps of 16 tokens
+                            const uint32_t vl = v_lo0 + s * (STAGE_BYTES >> 4);
+                            if (elect_one()) {                             // O_x += P_x . V(j) : k-steps of 16 tokens
+                                if (ksteps == 8) {
 #pragma unroll
-                                for (int t = 0; t < 8; ++t)
-                                    mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
-                                           j > 0 || t > 0);
-                            } else {
-                                for (int t = 0; t < ksteps; ++t)
-                                    mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
-                                           j > 0 || t > 0);
+                                    for (int t = 0; t < 8; ++t)
+                                        mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
+                                               j > 0 || t > 0);
+                                } else {
+                                    for (int t = 0; t < ksteps; ++t)
+                                        mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
+                                               j > 0 || t > 0);
+                                }
+                                mma_commit(bar(BAR_PV + x));
+                                if (x == 1) mma_commit(bar(BAR_VE + s));    // V(j) consumed: its stage refills under the Q.K^T below
                             }
-                            mma_commit(bar(BAR_PV + x));
+                            __syncwarp();
                             PF_ISSUE_STAMP(6);
+                        } else if (x == 1) {
+                            if (elect_one()) mma_commit(bar(BAR_VE + s));
+                            __syncwarp();
                         }
-                        if (x == 1) mma_commit(bar(BAR_VE + s));            // V(j) consumed: its stage refills under the Q.K^T below
                         if (j + 1 < nX[x]) {
                             b2::mbar_wait(bar(BAR_K + (j + 1) % NSTAGE), ((j + 1) / NSTAGE) & 1);
+#ifdef B2_TRACE
+                            if (x == 0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 1 && j + 1 < 32) g_pf_trace[0][j + 1][14] = clock64();
+#endif
                             issue_qk(x, j + 1);
                         }
                         PF_ISSUE_STAMP(7);
                     }
-                    if (more) mma_commit(bar(BAR_KE + (j + 1) % NSTAGE));  // K(j+1) consumed (both tiles issued above)
+                    if (more) {
+                        if (elect_one()) mma_commit(bar(BAR_KE + (j + 1) % NSTAGE));   // K(j+1) consumed (both tiles issued above)
+                        __syncwarp();
+                    }
                 }
             }
         }
