@@ -72,7 +72,7 @@ constexpr float RESCALE_THRESHOLD = 8.f;           // log2 units
 
 // barrier slots (8 bytes each) after the tiles
 enum { BAR_Q = 0, BAR_K = 1, BAR_V = BAR_K + NSTAGE, BAR_KE = BAR_V + NSTAGE, BAR_VE = BAR_KE + NSTAGE,
-       BAR_S = BAR_VE + NSTAGE, BAR_P = BAR_S + 2, BAR_PV = BAR_P + 2, BAR_COUNT = BAR_PV + 2 };
+       BAR_S = BAR_VE + NSTAGE, BAR_P = BAR_S + 2, BAR_P2 = BAR_P + 2, BAR_PV = BAR_P2 + 2, BAR_COUNT = BAR_PV + 2 };
 static_assert(BAR_COUNT * 8 + 16 <= 256, "barrier area");
 
 struct Tc5Params {
@@ -228,7 +228,8 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
         for (int x = 0; x < 2; ++x) {
             b2::mbar_init(bar(BAR_S + x), 1);
-            b2::mbar_init(bar(BAR_P + x), 4);      // one arrive per softmax warp of the tile
+            b2::mbar_init(bar(BAR_P + x), 4);      // one arrive per softmax warp of the tile: keys 0-63 of P are in TMEM
+            b2::mbar_init(bar(BAR_P2 + x), 4);     // ... keys 64-127
             b2::mbar_init(bar(BAR_PV + x), 1);
         }
         b2::fence_mbar_init();
@@ -376,22 +377,26 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     { const int x = 0; PF_ISSUE_STAMP(8); }
                     for (int x = 0; x < 2; ++x) {
                         if (j < nX[x]) {
-                            b2::mbar_wait(bar(BAR_P + x), j & 1);          // P_x(j) is in TMEM, O_x rescaled if needed
+                            b2::mbar_wait(bar(BAR_P + x), j & 1);          // keys 0-63 of P_x(j) are in TMEM, O_x rescaled if needed
                             tc_fence_after();
                             PF_ISSUE_STAMP(5);
                             const int ksteps = min(8, (hiX[x] - j * BN + 15) >> 4);
                             const uint32_t vl = v_lo0 + s * (STAGE_BYTES >> 4);
                             if (elect_one()) {                             // O_x += P_x . V(j) : k-steps of 16 tokens
-                                if (ksteps == 8) {
 #pragma unroll
-                                    for (int t = 0; t < 8; ++t)
+                                for (int t = 0; t < 4; ++t)
+                                    if (t < ksteps)
                                         mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
                                                j > 0 || t > 0);
-                                } else {
-                                    for (int t = 0; t < ksteps; ++t)
-                                        mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
-                                               j > 0 || t > 0);
-                                }
+                            }
+                            __syncwarp();
+                            b2::mbar_wait(bar(BAR_P2 + x), j & 1);         // keys 64-127
+                            tc_fence_after();
+                            if (elect_one()) {
+#pragma unroll
+                                for (int t = 4; t < 8; ++t)
+                                    if (t < ksteps)
+                                        mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV, true);
                                 mma_commit(bar(BAR_PV + x));
                                 if (x == 1) mma_commit(bar(BAR_VE + s));    // V(j) consumed: its stage refills under the Q.K^T below
                             }
@@ -501,13 +506,19 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         add_x2(sum[2 * (i & 1)], sum[2 * (i & 1) + 1], p0, p1);
                     }
                     tmem_st32(s_addr + c * 32, pk);               // P overwrites the first 64 columns of S_x
+                    if (c == 0) {                                 // hand the first 64 keys over: their P.V runs under the
+                        tmem_wait_st();                           // exponentials of the other 64
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) b2::mbar_arrive(bar(BAR_P + x));
+                    }
                 }
                 l += (sum[0] + sum[1]) + (sum[2] + sum[3]);
                 PF_STAMP(3);
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) b2::mbar_arrive(bar(BAR_P + x));
+                if (lane == 0) b2::mbar_arrive(bar(BAR_P2 + x));
                 PF_STAMP(4);
 #ifdef B2_TRACE
                 if (blockIdx.x == 0 && blockIdx.y == 1 && wq > 0 && lane == 0 && j < 32) g_pf_trace[x][j][8 + wq] = clock64();
