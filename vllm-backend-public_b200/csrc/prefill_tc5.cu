@@ -3,39 +3,42 @@
 // Same contract as prefill_attention.cu (include/b200attn.h `b2_prefill_attention`); this is the default kernel,
 // the mma.sync one is kept as the A/B (B2_PREFILL_IMPL=mma).
 //
-// One CTA = 256 query tokens of one q head = two 128-row tiles A and B, 10 warps:
+// One CTA = 256 query tokens of one q head = two 128-row tiles A and B, 11 warps:
 //   warps 0-3  softmax of tile A   (one thread = one query row = one TMEM lane)
 //   warps 4-7  softmax of tile B
-//   warp  8    TMA producer: Q (two 128x128 tiles) once, then the chunk's block table -> K|V stages of 128 tokens
-//   warp  9    MMA issuer (one lane): S = Q.K^T and O += P.V as tcgen05.mma 128x128x16, bf16 -> fp32 in TMEM
+//   warp  8    TMA producer: Q (two 128x128 tiles) once, then the chunk's block table -> K tiles of 128 tokens
+//   warp  10   TMA producer: V tiles                            (one box of bs x 128 B per lane in both)
+//   warp  9    MMA issuer (warp-uniform loop, one elected lane per instruction group): S = Q.K^T and O += P.V as
+//              tcgen05.mma 128x128x16, bf16 -> fp32 in TMEM
 // TMEM (512 columns x 128 lanes): S_A [0,128) S_B [128,256) O_A [256,384) O_B [384,512); P (bf16 pairs) overwrites the
 // first 64 columns of its S tile and is fed back as the A operand straight from TMEM, so P never touches shared memory.
 // Issue order  QK_A(0) QK_B(0) | PV_A(j) QK_A(j+1) PV_B(j) QK_B(j+1) ...  lets the softmax of one tile run under the
-// MMAs of the other.  Rescaling of O is lazy: a row keeps its stale maximum until the true one exceeds it by 2^8.
+// MMAs of the other; P.V(j) is issued in two halves as the softmax hands over keys 0-63 and 64-127.  Rescaling of O is lazy: a row keeps its stale maximum until the true one exceeds it by 2^8.
 //
-// Round-2 experiment, not adopted (scripts/experiments_prefill_two_threads_per_row.cu.txt, ncu summary in
-// profiles/r2_ncu_prefill_two_threads_per_row.md): TWO threads per query row -- 16 softmax warps, the halves of a row
-// meeting through shared memory and a 64-thread named barrier once per step, 576 threads, no setmaxnreg.  Parity-green,
-// 1038 vs 1055 TF/s at 8k / 8k: no gain, so the softmax warps are not short of latency hiding.  What ncu shows in both
-// versions: tensor pipe 48 % and XU pipe 48 % with the softmax warps waiting for S in 56 % of their samples -- the two
-// pipes ALTERNATE.  Per 128 x 128 tile a step needs 1084 tensor cycles (P.V + Q.K^T) and >= 1024 XU cycles (16 384 exp2
-// at 16 per clock) plus the row-maximum pass, TMEM load / store and fences in front of and behind them; a tile's own
-// chain softmax(j) -> P.V(j) -> Q.K^T(j+1) -> softmax(j+1) cannot overlap itself (P overwrites S), so the other tile
-// must cover it, which needs a tile's softmax to fit in the 1084 cycles of the other tile's MMAs -- it takes about
-// twice that.  The polynomial exp2 (B2_PREFILL_POLY) is still slower in both versions, and so is taking the
-// maximum pass off the chain (exponentiating against the row's previous maximum while the tile's own is tracked in
-// the same sweep, redo on the rare overflow: parity-green, 947 TF/s) -- every instruction added to the exp2 sweep costs
-// more than the pass it removes, i.e. the sweep itself is issue-limited around the 16-per-clock MUFU.  What is left is
-// structural.  The clock64 timeline of the softmax warps (`make trace` + scripts/trace_prefill.py,
-// profiles/r2_trace_prefill_softmax.txt) finally shows where the period goes: per 128-key step a tile's softmax takes
-// ~1750 cycles (TMEM load 45, maximum 370, exponentiate + pack 1300, hand-over 35) and then waits ~2300 cycles for its
-// next S -- and in that window the tensor pipe is busy the whole time with the tile's P.V + Q.K^T AND the other tile's
-// (their intervals overlap by ~500 cycles): 16 tcgen05.mma 128x128x16 take ~2050 cycles of pipe time, 126-130 cycles per
-// instruction against 68 at the 2.25 PFLOP/s rate.  So the kernel is TENSOR-ISSUE bound at about half rate, not softmax
-// bound: in SS mode at 128x128 a cta_group::1 MMA reads 4 KiB of A and 4 KiB of B from shared memory per instruction,
-// 128 B per clock at full rate -- the SM's whole shared-memory bandwidth.  That is why the softmax experiments above
-// changed nothing, and it is what `cta_group::2` is for (each CTA of the pair stages half of K / V, halving the
-// per-SM operand traffic): the next version of this kernel is a 2-CTA cluster with 256 query rows per q-tile pair.
+// Round 2, what bounded the kernel and what did not (8k chunk over an 8k prefix, Llama-3-8B heads, block_size 16;
+// clock64 timeline from `make trace` + scripts/trace_prefill.py, profiles/r2_trace_prefill_issuer*.txt):
+//   1055 TF/s  round-1 kernel.  ncu: tensor pipe 48 %, XU pipe 48 %, softmax warps waiting for S in 56 % of samples.
+//   not it     softmax latency hiding: TWO threads per query row (scripts/experiments_prefill_two_threads_per_row.cu.txt,
+//              profiles/r2_ncu_prefill_two_threads_per_row.md) 1038; maximum pass off the chain (speculative maximum) 947;
+//              polynomial exp2 for 1-3 of every 4 weights (B2_PREFILL_POLY) slower then and now (1371 / 1266 / 1164).
+//   not it     shared-memory operand bandwidth of cta_group::1 (an earlier reading of the timeline, WRONG):
+//              scripts/umma_rate.cu shows SS, TS, MN-major B, the kernel's own P.V | Q.K^T mix and all of them under
+//              concurrent TMEM traffic at 64.1 cycles per 128x128x16 = full rate (profiles/r2_umma_rate.txt).
+//   +8 %       the producer: ONE lane issued the 32 TMA boxes of a step (block_size 16: 2 KiB boxes) one after the other,
+//              ~70 cycles each.  Now warp 8 streams K and warp 10 streams V, one box per lane, and the V stage is released
+//              before the next Q.K^T is issued.  Tiles land ~1500 cycles after their stage frees (1140 TF/s).
+//   +21 %      the issuer: the loop ran inside `if (lane == 0)`, so every operand lived in a per-thread register and ptxas
+//              wrapped EVERY tcgen05.mma in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop, ~12 dependent instructions that
+//              the issuing thread -- sharing its scheduler with two softmax warps -- needed 80-105 cycles for, where the
+//              pipe needs 64.  The whole warp now runs the loop with warp-uniform operands and elect.sync picks the lane
+//              per instruction group (what CUTLASS does): 1-3 SASS instructions between UTCHMMAs (1375 TF/s).
+//   +2.5 %     P is handed over in two halves, so P.V of keys 0-63 runs under the exponentials of keys 64-127 (1409 TF/s,
+//              0.845 of the measured cuBLAS bf16 burst).  Quarters would cost the softmax as much as they save the chain.
+// What is left is the dependency chain of a tile, softmax(j) -> P.V(j) -> Q.K^T(j+1) -> softmax(j+1): ~1680 cycles of
+// softmax (TMEM load 30, maximum 300, 16 384 exp2 at 16 per clock + pack 1310, hand-over 40) + ~1170 until the next S
+// (4 P.V + 8 Q.K^T instructions = 768 pipe cycles, the rest barrier and commit latency) = the measured period of
+// 2850 cycles per 128-key step, in which the tensor pipe and the XU pipe are each busy 2048 (72 %).  P overwrites S, so
+// a tile cannot overlap its own chain; TMEM (2 x S + 2 x O = 512 columns) has no room for a second S per tile.
 //
 // Shared memory (1024-byte aligned, 128-byte swizzle, the canonical UMMA layouts):
 //   Q_A, Q_B     2 x [2 halves][128 rows][64 el]           K-major operand A           64 KiB
@@ -108,9 +111,7 @@ __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_
                  ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"((uint32_t)acc) : "memory");
 }
 // The descriptor of a tile is constant except for the 14-bit start address (bytes >> 4) in its low word: the issuing
-// thread keeps one low word per operand and advances it with an immediate add per k-step.  (Round 2: building both
-// 64-bit descriptors from scratch for every instruction made the ONE issuing thread the bottleneck -- ~130 cycles per
-// MMA against the 64 the tensor pipe needs, scripts/umma_rate.cu.)
+// warp keeps one low word per operand and advances it by a constant per k-step (uniform-register arithmetic).
 __device__ __forceinline__ uint32_t desc_lo(uint32_t addr, uint32_t lbo_bytes) {
     return ((addr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
 }
