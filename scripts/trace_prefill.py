@@ -32,7 +32,8 @@ lib.b2_debug_read_prefill_trace(buf.ctypes.data)
 t = buf.reshape(2, 32, 16).astype(np.int64)
 t0 = t[:, :, 0][t[:, :, 0] > 0].min()
 print("cycles relative to the first stamp; columns: S ready | S in regs | max known | P computed | P handed over")
-for j in range(8, 24):
+lo, hi = (int(v) for v in os.environ.get("TRACE_STEPS", "8:24").split(":"))
+for j in range(lo, hi):
     for x in (0, 1):
         r = t[x, j, :5] - t0
         i = t[x, j, 5:] - t0
@@ -42,8 +43,8 @@ for j in range(8, 24):
               f" | issuer: P seen +{i[0]-r[4]:5d} PV issued +{i[1]-i[0]:5d} QK issued +{i[2]-i[1]:5d} -> S ready +{t[x, j+1, 0]-t0-i[2]:5d}"
               f" | warps 1-3 hand over {w[0]:+5d} {w[1]:+5d} {w[2]:+5d} after warp 0" + (f" | V,K waits done {i[3]-r[4]:+6d} vs P handed" if x == 0 else ""))
 print("TMA: tile | stage free -> boxes issued -> seen full by the MMA warp (cycles)")
-for j in range(8, 24):
+for j in range(lo, hi):
     print(f"  K({j}): free {t[0, j, 12]-t0:7d} issue +{t[0, j, 13]-t[0, j, 12]:4d} landed +{t[0, j, 15]-t[0, j, 12]:5d} full-seen +{t[0, j, 14]-t[0, j, 12]:6d}"
           f"   V({j}): free {t[1, j, 12]-t0:7d} issue +{t[1, j, 13]-t[1, j, 12]:4d} landed +{t[1, j, 15]-t[1, j, 12]:5d} full-seen +{t[1, j, 14]-t[1, j, 12]:6d}")
-a = t[0, 8:24]
+a = t[0, lo:hi]
 print("period (tile A, S ready to next S ready): mean", float(np.diff(a[:, 0]).mean()))
