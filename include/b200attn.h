@@ -133,6 +133,27 @@ B2_API int b2_paged_decode(void* out, const void* q,
                     void* workspace, size_t workspace_bytes, int num_splits,
                     void* stream);
 
+/* b2_paged_decode for callers that may not allocate: code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc.  No counterpart in the reference.
+ * Same operation, arguments and results as b2_paged_decode, minus the workspace: the split-K partials and the claim
+ * counter live in a file-scope device array of B2_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the
+ * library holds it until exit).  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).
+ * A call whose schedule needs more scratch than that (large B x max_nb; b2_paged_decode_workspace_bytes tells) returns
+ * B2_ENOMEM with the sizes in b2_last_error -- use b2_paged_decode with a caller-owned workspace then.
+ * Every call on a GPU shares the one array: calls must be ordered on the GPU (same stream, or event-ordered); calls
+ * whose kernels overlap race on it. */
+#define B2_STATIC_SCRATCH_BYTES (32u << 20)
+B2_API int b2_paged_decode_static(void* out, const void* q,
+                           const void* k_cache, const void* v_cache,
+                           const int32_t* block_tables, const int32_t* seq_lens,
+                           int B, int Hq, int Hkv, int d, int bs, int max_nb,
+                           int64_t num_blocks,
+                           int64_t q_stride, int64_t out_stride,
+                           int64_t cache_block_stride, int64_t cache_head_stride,
+                           float scale, int kv_dtype,
+                           const float* k_scale, const float* v_scale,
+                           int num_splits, void* stream);
+
 /* Per-engine decode handle: the same operation as b2_paged_decode with everything that does not change between
  * steps fixed at creation -- cache pointers / strides (their two TMA descriptors are encoded once, a driver call
  * each), geometry, scale, kv dtype and scales, the workspace.  A call then is argument checks + kernel launches:

@@ -28,6 +28,7 @@
 
 #include <stdlib.h>
 #include <algorithm>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1693,6 +1694,74 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
                           kn.two_box != 0);
     if (rc != B2_OK) return rc;
     const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
+    return run_decode(g, maps, kn, /*zero_first=*/true, out, q, block_tables, seq_lens, B, q_stride, out_stride, num_splits,
+                      static_cast<cudaStream_t>(stream));
+}
+
+// ---------------------------------------------------------------------------------------------
+// b2_paged_decode_static: b2_paged_decode for callers that may not allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc).  The split-K partials and the claim counter live in a file-scope device
+// array of B2_STATIC_SCRATCH_BYTES that every GPU loading this library holds until exit.  No counterpart in the
+// reference.  Nothing here allocates: no cudaMalloc / cudaFree, no
+// allocating library call.  Every call on a GPU shares the ONE array (it keeps the previous call's partials; the
+// claim counter is re-zeroed on `stream` by the stateless path, and partials are always written before they are
+// read), so two calls whose kernels overlap on the GPU (different streams) race.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[B2_STATIC_SCRATCH_BYTES];
+
+namespace {
+// `g_static_scratch` in host code is the host-side shadow of the symbol, not a device address: ask the runtime for
+// the address once per device, with that device current.
+int static_scratch_ptr(void** out) {
+    static std::mutex mu;
+    static void* ptrs[64] = {};
+    int dev = -1;
+    B2_REQUIRE(cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64, B2_ECUDA,
+               "paged_decode_static: cudaGetDevice failed or device index %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+        B2_REQUIRE(e == cudaSuccess && ptr != nullptr, B2_ECUDA, "paged_decode_static: cudaGetSymbolAddress: %s",
+                   cudaGetErrorString(e));
+        ptrs[dev] = ptr;
+    }
+    *out = ptrs[dev];
+    return B2_OK;
+}
+}  // namespace
+
+extern "C" int b2_paged_decode_static(void* out, const void* q, const void* k_cache, const void* v_cache,
+                                      const int32_t* block_tables, const int32_t* seq_lens, int B, int Hq,
+                                      int Hkv, int d, int bs, int max_nb, int64_t num_blocks,
+                                      int64_t q_stride, int64_t out_stride, int64_t cache_block_stride,
+                                      int64_t cache_head_stride, float scale, int kv_dtype,
+                                      const float* k_scale, const float* v_scale, int num_splits, void* stream) {
+    B2_REQUIRE(B >= 0, B2_EINVAL, "paged_decode_static: bad batch size %d", B);
+    if (B == 0) return B2_OK;
+    int rc = check_geom(Hq, Hkv, d, bs, max_nb, num_blocks, k_cache, v_cache, cache_block_stride, cache_head_stride, scale,
+                        kv_dtype, k_scale, v_scale);
+    if (rc != B2_OK) return rc;
+    B2_REQUIRE(num_splits >= 0, B2_EINVAL, "paged_decode_static: num_splits must be >= 0");
+    const Knobs kn = read_knobs();
+    {   // what THIS call needs (the same plan run_decode makes), checked against the built-in maximum first
+        Plan pl;
+        make_plan(&pl, B, Hkv, Hq / Hkv, bs, max_nb, num_splits,
+                  ctas_per_sm(kv_dtype == B2_KV_FP8_E4M3, Hq / Hkv, kn.fp8_ctas), kn);
+        const size_t need = plan_workspace(pl, B, Hq);
+        B2_REQUIRE(need <= (size_t)B2_STATIC_SCRATCH_BYTES, B2_ENOMEM,
+                   "paged_decode_static: B=%d Hq=%d max_nb=%d num_splits=%d needs %zu bytes of scratch, the built-in array "
+                   "holds %zu (B2_STATIC_SCRATCH_BYTES); use b2_paged_decode with a caller-owned workspace",
+                   B, Hq, max_nb, num_splits, need, (size_t)B2_STATIC_SCRATCH_BYTES);
+    }
+    void* scratch = nullptr;
+    rc = static_scratch_ptr(&scratch);
+    if (rc != B2_OK) return rc;
+    CacheMaps maps;
+    rc = make_decode_maps(&maps, k_cache, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride,
+                          kn.two_box != 0);
+    if (rc != B2_OK) return rc;
+    const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, scratch, (size_t)B2_STATIC_SCRATCH_BYTES};
     return run_decode(g, maps, kn, /*zero_first=*/true, out, q, block_tables, seq_lens, B, q_stride, out_stride, num_splits,
                       static_cast<cudaStream_t>(stream));
 }
