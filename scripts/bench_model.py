@@ -72,14 +72,29 @@ for chunk, start in ((8192, 0), (8192, 8192), (8192, 24576), (2048, 0), (512, 35
     cu = torch.tensor([0, chunk], dtype=torch.int32, device=dev)
     st = torch.tensor([start], dtype=torch.int32, device=dev)
     out = torch.empty_like(q)
-    # back-to-back launches inside one event pair: a lone 2k-chunk launch (~50 us of kernel) between two events also
-    # times the host side of the call (three tensor-map encodes + launch), which the serving step overlaps with the
-    # kernels in front of it
+    # small chunks: 8 launches captured in a CUDA graph and replayed inside one event pair.  A lone 2k-chunk launch
+    # (~30 us of kernel) between two events -- or eight eager ones -- times the host side of the call (python argument
+    # checks, three tensor-map encodes, the launch: ~50 us), which the serving step overlaps with the kernels in front
     reps = 1 if chunk >= 8192 else 8
-    med, best = timeit(lambda: ops.prefill_attention(q, kc, vc, bt, cu, st, out=out), iters=10, reps=reps)
+    call = lambda: ops.prefill_attention(q, kc, vc, bt, cu, st, out=out)
+    if reps > 1:
+        call()
+        torch.cuda.synchronize()
+        side = torch.cuda.Stream()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            call()
+            side.synchronize()
+            with torch.cuda.graph(gr, stream=side):
+                for _ in range(reps):
+                    call()
+        med, best = timeit(gr.replay, iters=10)
+        med, best = med / reps, best / reps
+    else:
+        med, best = timeit(call, iters=10)
     pairs = chunk * start + chunk * (chunk + 1) // 2
     flops = 4 * d * Hq * pairs
-    emit(op="prefill_attention", chunk=chunk, prefix=start, block_size=bs, Hq=Hq, Hkv=Hkv, launches_per_timing=reps, ms=med, ms_min=best,
+    emit(op="prefill_attention", chunk=chunk, prefix=start, block_size=bs, Hq=Hq, Hkv=Hkv, launches_per_timing=reps, timed="cuda graph of the launches" if reps > 1 else "eager launch", ms=med, ms_min=best,
          tflops=flops / med / 1e9, frac_of_measured_bf16=flops / med / 1e9 / TF, peak_tflops=TF,
          note="causal flops only (4*d per visible (q,k) pair)")
 

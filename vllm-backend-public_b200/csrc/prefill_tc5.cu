@@ -34,6 +34,10 @@
 //              per instruction group (what CUTLASS does): 1-3 SASS instructions between UTCHMMAs (1375 TF/s).
 //   +2.5 %     P is handed over in two halves, so P.V of keys 0-63 runs under the exponentials of keys 64-127 (1409 TF/s,
 //              0.845 of the measured cuBLAS bf16 burst).  Quarters would cost the softmax as much as they save the chain.
+//   small      launches of less than one wave at 256 rows per CTA (a 512-token chunk over a long prefix) run 128 rows per
+//              CTA; with a single tile the tensor pipe idled during the tile's own softmax.  The SPLIT kernel (below)
+//              gives both slots the same 128 rows and interleaves the key tiles between them: 512 / 3.5k 55.7 -> 36-41 us
+//              (578 -> 760-880 TF/s), and at 8k / 8k it is within 6 % of the 256-row kernel (B2_PREFILL_ROWS=128).
 // What is left is the dependency chain of a tile, softmax(j) -> P.V(j) -> Q.K^T(j+1) -> softmax(j+1): ~1680 cycles of
 // softmax (TMEM load 30, maximum 300, 16 384 exp2 at 16 per clock + pack 1310, hand-over 40) + ~1170 until the next S
 // (4 P.V + 8 Q.K^T instructions = 768 pipe cycles, the rest barrier and commit latency) = the measured period of
@@ -190,13 +194,20 @@ __device__ __forceinline__ void add_x2(float& d0, float& d1, float a0, float a1)
 // =============================================================================================
 // the kernel.  POLY of every 4 consecutive softmax weights take poly_exp2, the rest MUFU.EX2.
 // =============================================================================================
-template <int POLY>
+// SPLIT (rows_per_cta = 128: launches that would leave SMs idle at 256 rows per CTA, e.g. a 512-token chunk over a long
+// prefix): both slots work on the SAME 128 query rows and share the keys between them -- slot x takes the 128-key
+// tiles x, x + 2, ... (always ring stage x), so the two slots still cover each other's softmax -> P.V -> Q.K^T chain
+// instead of one tile leaving the tensor pipe idle during its own softmax.  Their (m, l, O) are merged by the warps
+// of slot 0 at the end: a thread reads O of both slots from TMEM (same lane, other columns), m and l of slot 1 come
+// through shared memory.
+template <int POLY, bool SPLIT>
 __global__ void __launch_bounds__(NTHREADS, 1)
 prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const Tc5Params p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ int s_tile[4];
     __shared__ uint32_t s_tmem;
+    __shared__ float s_ml[SPLIT ? 2 * BM : 2];    // SPLIT: (m, l) of slot 1 per query row
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // warp-uniform for the compiler too (see the MMA issuer)
@@ -252,11 +263,13 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const bool active = chunk >= 0;               // CTA-uniform
     {
         const int rows = min(p.rows_per_cta, len - q0);         // valid query rows of the CTA
-        const int rowsX[2] = {min(BM, rows), max(0, rows - BM)};
+        const int rowsX[2] = {min(BM, rows), SPLIT ? min(BM, rows) : max(0, rows - BM)};
         // keys [0, hiX) are visible to the last row of tile X; tiles of 128 keys
-        const int hiX[2] = {start + q0 + rowsX[0], rowsX[1] ? start + q0 + BM + rowsX[1] : 0};
-        const int nX[2] = {(hiX[0] + BN - 1) / BN, (hiX[1] + BN - 1) / BN};
-        const int n_tiles = max(nX[0], nX[1]);
+        const int hiX[2] = {start + q0 + rowsX[0],
+                            SPLIT ? start + q0 + rowsX[0] : rowsX[1] ? start + q0 + BM + rowsX[1] : 0};
+        const int n_tiles = (max(hiX[0], hiX[1]) + BN - 1) / BN;
+        // steps of slot x; its step i works on key tile SPLIT ? 2 i + x : i
+        const int nX[2] = {SPLIT ? (n_tiles + 1) / 2 : (hiX[0] + BN - 1) / BN, SPLIT ? n_tiles / 2 : (hiX[1] + BN - 1) / BN};
         const int kv_hi = max(hiX[0], hiX[1]);
         const int row0 = active ? p.cu_q[chunk] + q0 : 0;       // first token row in q / out
 
@@ -278,8 +291,8 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
             asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_once));
             if (!kv && lane == 0) {
-                b2::mbar_arrive_expect_tx(bar(BAR_Q), Q_BYTES);
-                for (int x = 0; x < 2; ++x)
+                b2::mbar_arrive_expect_tx(bar(BAR_Q), SPLIT ? TILE_BYTES : Q_BYTES);
+                for (int x = 0; x < (SPLIT ? 1 : 2); ++x)       // SPLIT: one Q tile serves both slots
                     for (int h = 0; h < 2; ++h)                 // rows past T are zero-filled by the TMA unit
                         b2::tma_load_4d(q_smem + x * TILE_BYTES + h * SUB_BYTES, &tmQ, bar(BAR_Q), 0, h, hq,
                                         row0 + x * BM, pol_once);
@@ -340,7 +353,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 const uint32_t k_lo0 = desc_lo(ring, 16), v_lo0 = desc_lo(ring + TILE_BYTES, SUB_BYTES);
                 auto issue_qk = [&](int x, int j) {        // S_x = Q_x . K(j)^T : 8 k-steps of 16 over d
                     const uint32_t kl = k_lo0 + (uint32_t)(j % NSTAGE) * (STAGE_BYTES >> 4);
-                    const uint32_t ql = q_lo0 + (uint32_t)x * (TILE_BYTES >> 4);
+                    const uint32_t ql = q_lo0 + (SPLIT ? 0u : (uint32_t)x * (TILE_BYTES >> 4));
                     if (elect_one()) {
 #pragma unroll
                         for (int kk = 0; kk < 8; ++kk) {
@@ -351,7 +364,69 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     }
                     __syncwarp();
                 };
+                // rows of the last tile past the sequence hold whatever the cache (or an older stage) held: zero the
+                // ones the last 16-token k-step still reads, so 0 * NaN cannot reach an accumulator
+                auto zero_tail = [&](int jt) {
+                    const uint32_t vb = ring + (jt % NSTAGE) * STAGE_BYTES + TILE_BYTES;
+                    const int valid = kv_hi - jt * BN;
+                    const int upto = min(BN, (valid + 15) & ~15);
+                    if (lane < 16)                            // lane = (half, 16-byte column)
+                        for (int r = valid; r < upto; ++r)
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(vb + (lane >> 3) * SUB_BYTES + r * 128 + (lane & 7) * 16), "r"(0) : "memory");
+                    b2::fence_proxy_async();
+                    __syncwarp();
+                };
                 b2::mbar_wait(bar(BAR_Q), 0);
+                if constexpr (SPLIT) {
+                    // slot x owns ring stage x: its step i works on tile 2 i + x, barrier phases follow i
+                    for (int x = 0; x < 2; ++x)
+                        if (nX[x] > 0) {
+                            b2::mbar_wait(bar(BAR_K + x), 0);
+                            tc_fence_after();
+                            issue_qk(x, x);
+                            if (elect_one()) mma_commit(bar(BAR_KE + x));
+                            __syncwarp();
+                        }
+                    for (int i = 0; i < nX[0]; ++i) {
+                        for (int x = 0; x < 2; ++x) {
+                            const int jt = 2 * i + x;
+                            if (i < nX[x]) {
+                                b2::mbar_wait(bar(BAR_V + x), i & 1);
+                                if (jt == n_tiles - 1) zero_tail(jt);
+                                b2::mbar_wait(bar(BAR_P + x), i & 1);      // keys 0-63 of P_x are in TMEM, O_x rescaled if needed
+                                tc_fence_after();
+                                const int ksteps = min(8, (kv_hi - jt * BN + 15) >> 4);
+                                const uint32_t vl = v_lo0 + x * (STAGE_BYTES >> 4);
+                                if (elect_one()) {
+#pragma unroll
+                                    for (int t = 0; t < 4; ++t)
+                                        if (t < ksteps)
+                                            mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV,
+                                                   i > 0 || t > 0);
+                                }
+                                __syncwarp();
+                                b2::mbar_wait(bar(BAR_P2 + x), i & 1);     // keys 64-127
+                                tc_fence_after();
+                                if (elect_one()) {
+#pragma unroll
+                                    for (int t = 4; t < 8; ++t)
+                                        if (t < ksteps)
+                                            mma_ts(tmem + 256 + x * 128, tmem + x * 128 + t * 8, desc_join(vl + t * (2048 >> 4)), ID_PV, true);
+                                    mma_commit(bar(BAR_PV + x));
+                                    mma_commit(bar(BAR_VE + x));
+                                }
+                                __syncwarp();
+                            }
+                            if (i + 1 < nX[x]) {
+                                b2::mbar_wait(bar(BAR_K + x), (i + 1) & 1);
+                                tc_fence_after();
+                                issue_qk(x, jt + 2);
+                                if (elect_one()) mma_commit(bar(BAR_KE + x));
+                                __syncwarp();
+                            }
+                        }
+                    }
+                } else {
                 b2::mbar_wait(bar(BAR_K + 0), 0);
                 tc_fence_after();
                 for (int x = 0; x < 2; ++x)
@@ -360,19 +435,8 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 __syncwarp();
                 for (int j = 0; j < n_tiles; ++j) {
                     const uint32_t s = j % NSTAGE;
-                    const uint32_t vb = ring + s * STAGE_BYTES + TILE_BYTES;
                     b2::mbar_wait(bar(BAR_V + s), (j / NSTAGE) & 1);
-                    if (j == n_tiles - 1) {
-                        // rows of the last stage past the sequence hold whatever the cache (or an older stage) held:
-                        // zero the ones the last 16-token k-step still reads, so 0 * NaN cannot reach an accumulator
-                        const int valid = kv_hi - j * BN;
-                        const int upto = min(BN, (valid + 15) & ~15);
-                        if (lane < 16)                            // lane = (half, 16-byte column)
-                            for (int r = valid; r < upto; ++r)
-                                asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(vb + (lane >> 3) * SUB_BYTES + r * 128 + (lane & 7) * 16), "r"(0) : "memory");
-                        b2::fence_proxy_async();
-                        __syncwarp();
-                    }
+                    if (j == n_tiles - 1) zero_tail(j);
                     const bool more = j + 1 < n_tiles;
                     { const int x = 1; PF_ISSUE_STAMP(14); }
                     { const int x = 0; PF_ISSUE_STAMP(8); }
@@ -421,6 +485,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                         __syncwarp();
                     }
                 }
+                }
             }
         }
         }
@@ -434,8 +499,9 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             const uint32_t s_addr = tmem + lane_off + x * 128, o_addr = tmem + lane_off + 256 + x * 128;
             const int n = nX[x];
             const float sl2 = p.scale_log2 * (p.k_scale ? *p.k_scale : 1.f);
-            const int lim = start + q0 + x * BM + min(row, max(rowsX[x] - 1, 0));   // last key this row may see
-            const int lim_min = start + q0 + x * BM;                                 // ... of the tile's first row
+            const int xrow = SPLIT ? 0 : x * BM;                  // first query row of the slot (SPLIT: the same rows in both)
+            const int lim = start + q0 + xrow + min(row, max(rowsX[x] - 1, 0));     // last key this row may see
+            const int lim_min = start + q0 + xrow;                                   // ... of the tile's first row
             float m = -INFINITY, l = 0.f;
 #ifdef B2_TRACE
             const bool trace_on = blockIdx.x == 0 && blockIdx.y == 1 && wq == 0 && lane == 0;   // y = 0 is the spare (inactive) CTA of a single chunk
@@ -449,7 +515,7 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 for (int c = 0; c < 4; ++c) tmem_ld32(s_addr + c * 32, sr[c]);
                 tmem_wait_ld();
                 PF_STAMP(1);
-                const int j0 = j * BN;
+                const int j0 = (SPLIT ? 2 * j + x : j) * BN;      // first key of this step's tile
                 if (j0 + BN - 1 > lim_min) {                      // tile touches the diagonal (or the end of the sequence)
 #pragma unroll
                     for (int c = 0; c < 4; ++c)
@@ -467,7 +533,9 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     for (int i = 0; i < 32; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], __uint_as_float(sr[c][i]));
                 const float mx = fmaxf(fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3])),
                                        fmaxf(fmaxf(mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7])));
-                const float m_new = fmaxf(m, mx);                 // finite: key 0 is visible to every row, tiles in order
+                // finite: key 0 is visible to every row, tiles in order.  SPLIT: slot 1 starts at key 128, which a row of a
+                // chunk that starts inside the first tile may not see -- a finite floor keeps exp2(-inf - m) = 0, not NaN
+                const float m_new = SPLIT ? fmaxf(fmaxf(m, mx), -1e30f) : fmaxf(m, mx);
                 if (j == 0) {
                     m = m_new;
                 } else {
@@ -525,7 +593,53 @@ prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                 if (blockIdx.x == 0 && blockIdx.y == 1 && wq > 0 && lane == 0 && j < 32) g_pf_trace[x][j][8 + wq] = clock64();
 #endif
             }
-            if (n > 0) {
+            if constexpr (SPLIT) {
+                // merge the two slots (same rows, interleaved key tiles): slot 1 publishes (m, l), the thread of slot 0
+                // that owns the row reads O of both slots from TMEM (same lane, columns 256.. and 384..)
+                if (x == 1) {
+                    s_ml[row] = n > 0 ? m : -1e30f;
+                    s_ml[BM + row] = n > 0 ? l : 0.f;
+                    __threadfence_block();
+                    asm volatile("bar.arrive 1, 256;" ::: "memory");
+                } else {
+                    b2::mbar_wait(bar(BAR_PV + 0), (n - 1) & 1);                  // n >= 1: slot 0 owns tile 0
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    const int n1 = nX[1];
+                    // commits complete in issue order, so PV_1 lags PV_0 by less than one phase here (parity wait is safe)
+                    if (n1 > 0) b2::mbar_wait(bar(BAR_PV + 1), (n1 - 1) & 1);
+                    tc_fence_after();
+                    const float m1 = s_ml[row], l1 = s_ml[BM + row];
+                    const float mm = fmaxf(m, m1);
+                    float a0 = b2::fast_exp2((m - mm) * sl2), a1 = n1 > 0 ? b2::fast_exp2((m1 - mm) * sl2) : 0.f;
+                    const float inv = (p.v_scale ? *p.v_scale : 1.f) / (a0 * l + a1 * l1);
+                    a0 *= inv;
+                    a1 *= inv;
+                    const bool valid = row < rowsX[0];
+                    __nv_bfloat16* orow = p.out + (int64_t)(row0 + row) * p.out_stride + (int64_t)hq * D;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t oa[32], ob[32];
+                        tmem_ld32(o_addr + c * 32, oa);
+                        if (n1 > 0) tmem_ld32(o_addr + 128 + c * 32, ob);
+                        tmem_wait_ld();
+                        if (valid) {
+                            float r[32];
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                r[i] = n1 > 0 ? fmaf(__uint_as_float(ob[i]), a1, __uint_as_float(oa[i]) * a0) : __uint_as_float(oa[i]) * a0;
+#pragma unroll
+                            for (int i = 0; i < 32; i += 8) {
+                                int4 v;
+                                v.x = (int)b2::pack_bf16x2(r[i], r[i + 1]);
+                                v.y = (int)b2::pack_bf16x2(r[i + 2], r[i + 3]);
+                                v.z = (int)b2::pack_bf16x2(r[i + 4], r[i + 5]);
+                                v.w = (int)b2::pack_bf16x2(r[i + 6], r[i + 7]);
+                                *reinterpret_cast<int4*>(orow + c * 32 + i) = v;
+                            }
+                        }
+                    }
+                }
+            } else if (n > 0) {
                 b2::mbar_wait(bar(BAR_PV + x), (n - 1) & 1);
                 tc_fence_after();
                 const float inv = (p.v_scale ? *p.v_scale : 1.f) / l;
@@ -571,7 +685,9 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
                             const float* k_scale, const float* v_scale, void* stream) {
     // 256 query rows per CTA share each K/V stage between two tiles; when that leaves SMs idle, 128 rows per CTA
     static const int n_sm = []() { int dev = 0, n = 148; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); return n; }();
-    const int rows_per_cta = ((int64_t)T / (2 * BM) + n_chunks) * Hq < n_sm ? BM : 2 * BM;      // less than one wave
+    static const int force_rows = []() { const char* e = getenv("B2_PREFILL_ROWS"); return e && *e ? atoi(e) : 0; }();   // A/B knob
+    const int rows_per_cta = force_rows == BM || force_rows == 2 * BM ? force_rows
+                             : ((int64_t)T / (2 * BM) + n_chunks) * Hq < n_sm ? BM : 2 * BM;    // less than one wave
     const int64_t n_qtiles = (int64_t)T / rows_per_cta + n_chunks;        // upper bound of sum ceil(len_c / rows_per_cta)
     B2_REQUIRE(n_qtiles <= 65535, B2_EUNSUPPORTED, "prefill_attention: %lld q tiles exceed the grid", (long long)n_qtiles);
     B2_REQUIRE(bs <= 64 && BN % bs == 0, B2_EUNSUPPORTED, "prefill_attention: block_size %d", bs);
@@ -608,8 +724,13 @@ int b2_internal_prefill_tc5(void* out, const void* q, const void* k_cache, const
     p.v_scale = v_scale;
     // share of the softmax weights computed by polynomial (B2_PREFILL_POLY = 0..3 of every 4; A/B knob)
     static const int poly = []() { const char* e = getenv("B2_PREFILL_POLY"); return e && *e ? atoi(e) : 0; }();
-    auto kern = poly <= 0 ? prefill_tc5_kernel<0> : poly == 1 ? prefill_tc5_kernel<1> : poly == 2 ? prefill_tc5_kernel<2>
-                                                                                     : prefill_tc5_kernel<3>;
+    // 128 rows per CTA run the SPLIT kernel (both slots on the same rows, key tiles interleaved); B2_PREFILL_SPLIT=0
+    // keeps the single-tile kernel as the A/B
+    static const bool split_on = []() { const char* e = getenv("B2_PREFILL_SPLIT"); return !(e && *e == '0'); }();
+    using KernFn = void (*)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Tc5Params);
+    KernFn kern = poly <= 0 ? prefill_tc5_kernel<0, false> : poly == 1 ? prefill_tc5_kernel<1, false>
+                : poly == 2 ? prefill_tc5_kernel<2, false> : prefill_tc5_kernel<3, false>;
+    if (rows_per_cta == BM && split_on && poly <= 0) kern = prefill_tc5_kernel<0, true>;
     B2_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     kern<<<dim3(Hq, (unsigned)n_qtiles), NTHREADS, SMEM_BYTES, static_cast<cudaStream_t>(stream)>>>(tmQ, tmK, tmV, p);
     B2_CUDA_OK(cudaGetLastError());
