@@ -55,9 +55,12 @@ def server(cuda):
     finally:
         proc.terminate()
         try:
-            proc.wait(10)
+            rc = proc.wait(20)
         except subprocess.TimeoutExpired:
             proc.kill()
+            rc = None
+    # SIGTERM must end in the server's own shutdown path (exit code 0), not in the re-raised signal (-15)
+    assert rc == 0, f"server exit code {rc} after SIGTERM"
 
 
 def test_models_and_completion(server):

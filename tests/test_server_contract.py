@@ -329,3 +329,58 @@ def test_evaljob_renders_like_the_reference_and_describes_a_runnable_job():
     import pytest
     with pytest.raises(ValueError):
         evaljob.render_for_model("m", "u", template="kind: [unclosed")
+
+
+_SIGTERM_CHILD = r'''
+import sys, threading
+from b200attn import server
+from b200attn.tokenizer import ByteTokenizer
+
+class Runner(server.EngineRunner):
+    """No engine: ready at once, and stop() leaves a mark -- what rank 0 must reach to release its worker ranks."""
+    def _main(self):
+        self.tokenizer = ByteTokenizer(1024)
+        self.ready.set()
+        while not self._stop:
+            self._wake.wait(0.05)
+    def stop(self):
+        super().stop()
+        open(sys.argv[2], "w").write("stopped")
+
+server.EngineRunner = Runner
+sys.exit(server.main(["--model", "tiny", "--host", "127.0.0.1", "--port", sys.argv[1]]))
+'''
+
+
+def test_sigterm_runs_the_shutdown_path(tmp_path):
+    """The pod's SIGTERM must reach EngineRunner.stop() and exit 0.  uvicorn re-raises the signal once its loop has
+    drained; with the default handler the process died inside server.run() and a tensor-parallel rank 0 never told
+    ranks 1..N-1 to stop (they stayed behind spinning inside a barrier)."""
+    import os
+    import signal
+    import subprocess
+    import sys
+    import requests
+    port = _free_port()
+    mark = tmp_path / "stopped"
+    env = dict(os.environ, PYTHONPATH=str(Path(__file__).resolve().parent.parent / "vllm-backend-public_b200"))
+    proc = subprocess.Popen([sys.executable, "-c", _SIGTERM_CHILD, str(port), str(mark)], env=env,
+                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    try:
+        for _ in range(300):
+            assert proc.poll() is None, proc.stdout.read().decode()[-2000:]
+            try:
+                if requests.get(f"http://127.0.0.1:{port}/health", timeout=1).status_code == 200:
+                    break
+            except requests.RequestException:
+                pass
+            time.sleep(0.1)
+        else:
+            raise AssertionError("server did not become healthy")
+        proc.send_signal(signal.SIGTERM)
+        rc = proc.wait(20)
+    finally:
+        if proc.poll() is None:
+            proc.kill()
+    assert rc == 0, f"exit code {rc}: {proc.stdout.read().decode()[-2000:]}"
+    assert mark.read_text() == "stopped"

@@ -504,22 +504,24 @@ class LLMEngine:
         return n
 
     # ------------------------------------------------------------------------------------ tensor-parallel ranks
-    def worker_loop(self) -> None:
+    def worker_loop(self) -> bool:
         """Ranks 1..tp-1: mirror rank 0 step by step.  Each message carries what rank 0 admitted / aborted before its
-        step; the plan, the schedule, the CUDA graph and the sampled ids then follow from identical state."""
+        step; the plan, the schedule, the CUDA graph and the sampled ids then follow from identical state.
+        Returns True after rank 0's shutdown message (every rank then closes together), False when the launcher
+        disappeared -- the caller must then leave without any collective (close() holds a barrier)."""
         from . import tp as _tp
         assert self.tp is not None and not self.is_driver
         parent = os.getppid()
         while True:
             try:
-                payload = self.tp.channel.recv(timeout=5.0)
+                payload = self.tp.channel.recv(timeout=1.0)
             except TimeoutError:
                 if os.getppid() != parent:            # the launcher is gone: do not keep a GPU spinning
-                    return
+                    return False
                 continue
             cmd, reqs, aborts = _tp.decode_step(payload)
             if cmd == _tp.MSG_SHUTDOWN:
-                return
+                return True
             if cmd == _tp.MSG_CAPTURE:
                 self.capture_all()
                 continue

@@ -73,6 +73,12 @@ class EngineRunner:
                     p.wait(timeout=10)
                 except Exception:
                     p.kill()
+            try:                                     # leave no NCCL communicator for interpreter shutdown to wait on
+                import torch.distributed as dist
+                if dist.is_initialized() and all(p.poll() is not None for p in self.workers):
+                    dist.destroy_process_group()
+            except Exception:
+                pass
 
     def _main(self) -> None:
         try:
@@ -569,6 +575,19 @@ def main(argv: Optional[List[str]] = None) -> int:
             server.should_exit = True
 
     threading.Thread(target=watchdog, daemon=True).start()
+
+    # uvicorn handles SIGTERM / SIGINT itself, but when its loop has drained it restores the previous handlers and
+    # RE-RAISES the signal: with the default handler the process would die inside server.run(), runner.stop() would
+    # never run and the tensor-parallel ranks would be orphaned.  A handler of our own makes the re-raise harmless.
+    def on_signal(signum, frame):
+        server.should_exit = True
+
+    try:
+        import signal
+        for sig in (signal.SIGTERM, signal.SIGINT):
+            signal.signal(sig, on_signal)
+    except ValueError:                            # not the main thread (embedded use): the embedder owns the signals
+        pass
     server.run()
     runner.stop()
     return 1 if runner.failed else 0

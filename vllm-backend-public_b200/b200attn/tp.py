@@ -332,15 +332,28 @@ def free_port() -> int:
         return s.getsockname()[1]
 
 
+def _exit_when_orphaned(launcher_pid: int) -> None:
+    """Watcher thread of a worker rank: leave at once when the launcher (rank 0) is gone, whatever the main thread is
+    doing.  A rank without rank 0 can only wait inside a collective with its GPU spinning; the driver releases the
+    device with the process.  (Polling, not PR_SET_PDEATHSIG: that signal follows the launching THREAD, and rank 0
+    starts its workers from the engine thread, which ends before the orderly shutdown does.)"""
+    while True:
+        time.sleep(1.0)
+        if os.getppid() != launcher_pid:
+            os._exit(1)
+
+
 def launch_workers(world: int, spec: dict, master_port: int, log_dir: Optional[str] = None) -> List[subprocess.Popen]:
     """Start ranks 1..world-1 (`python -m b200attn.tp`), each bound to GPU `rank` of this node, with the engine spec
     rank 0 was started with.  The caller is rank 0 and must then call init_distributed(0, world, ...)."""
     procs = []
+    launcher = os.getpid()
     pkg_parent = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for r in range(1, world):
         env = dict(os.environ)
         env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(world), "MASTER_ADDR": "127.0.0.1",
                     "MASTER_PORT": str(master_port), "B200ATTN_TP_SPEC": json.dumps(spec), "OMP_NUM_THREADS": "1",
+                    "B200ATTN_TP_LAUNCHER_PID": str(launcher),
                     "PYTHONPATH": pkg_parent + os.pathsep + env.get("PYTHONPATH", "")})
         out = None
         if log_dir:
@@ -363,15 +376,30 @@ def worker_main() -> int:
     """Entry point of ranks 1..N-1: build the same engine as rank 0 and mirror its steps until told to stop."""
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     spec = json.loads(os.environ["B200ATTN_TP_SPEC"])
+    launcher = int(os.environ.get("B200ATTN_TP_LAUNCHER_PID", os.getppid()))
+    if os.getppid() != launcher:
+        return 1
+    import threading
+    threading.Thread(target=_exit_when_orphaned, args=(launcher,), name="b200attn-orphan-watch", daemon=True).start()
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
     torch.cuda.set_device(dev)
     init_distributed(rank, world, dev)
     group = TPGroup(dev)
     eng = build_engine_from_spec(spec, dev, group)
+    orderly = False
     try:
-        eng.worker_loop()
+        orderly = eng.worker_loop()
     finally:
-        eng.close()
+        if not orderly:
+            # rank 0 is gone (or this rank failed): eng.close() holds a barrier nobody will match, and the process
+            # group's destructor would wait on it too -- leave at once, the driver releases the GPU with the process
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(1)
+    eng.close()
+    import torch.distributed as dist
+    if dist.is_initialized():
+        dist.destroy_process_group()
     return 0
 
 
