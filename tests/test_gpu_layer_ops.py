@@ -80,6 +80,14 @@ def test_prefill_attention_block_sizes(cuda, bs):
     check_prefill(make_prefill_case([150, 70], [40, 0], Hq=4, Hkv=4, bs=bs, seed=bs), cuda)
 
 
+@pytest.mark.parametrize("Hq,Hkv", [(1, 1), (4, 1), (16, 2), (8, 1)])
+def test_prefill_attention_shard_geometries(cuda, Hq, Hkv):
+    """What one rank sees at --tensor-parallel-size 8 / 4 (Llama-3-8B: 4 q heads on 1 kv head; tiny8: 1 on 1; 70B at
+    tp 8: 8 on 1): few heads make small launches, i.e. the 128-row split kernel, also with a prefix that leaves slot 1
+    of a short row without any visible key tile (ragged chunk ends, prefix not a multiple of the 128-key tile)."""
+    check_prefill(make_prefill_case([513, 1, 130, 255], [0, 1000, 77, 3000], Hq=Hq, Hkv=Hkv, bs=16, seed=Hq * 7 + Hkv), cuda)
+
+
 def test_prefill_attention_llama_geometry(cuda):
     """Llama-3-8B heads, a 2k chunk after a 1k prefix and a whole 700-token prompt."""
     check_prefill(make_prefill_case([2048, 700], [1024, 0], Hq=32, Hkv=8, bs=16, seed=3), cuda)
