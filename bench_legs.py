@@ -302,7 +302,10 @@ def tp_comm_leg(dev, group, T: int = 64, H: int = 4096, iters: int = 200) -> dic
         group.barrier()
         group.close()
         res.update(T=T, H=H, tp=group.size, message_bytes=T * H * 2, iters=iters,
-                   note="per call, back-to-back eager launches; the fused kernel reads tp x message bytes over NVLink per rank")
+                   note="*_us: per call, back-to-back EAGER launches from Python on every rank -- host launch pacing and jitter of the "
+                        "slowest rank included (every exchange waits for all ranks' launches), so they vary run to run; "
+                        "*_in_graph_us: the same loop replayed as one CUDA graph = the device cost, and how the decode "
+                        "step runs it; the fused kernel reads tp x message bytes over NVLink per rank")
         return res
     except Exception as e:                                                    # noqa: BLE001
         return {"error": f"{type(e).__name__}: {e}"[:400]}
