@@ -208,11 +208,27 @@ def schedule_name(num_splits):
         num_splits, f"grid split x{num_splits} + merge")
 
 
-def time_resident(dev, prob, num_splits, K, W, barrier, clock_index=None):
-    """W warm-up steps, then K timed steps of [reshape_and_cache(1 new token / sequence) + paged_decode] with every
-    input resident in HBM; CUDA events on the launching stream.  -> (ms per step, mean / min ms of b2_paged_decode,
-    out tensor, clocks summary)."""
+def step_is_fused(prob, num_splits):
+    """The step runs as ONE launch (b2_paged_decode_append: the CTA that owns (row, kv head) writes the row's new K/V
+    itself) when the schedule is the single-pass grid and G <= 16; B2_BENCH_APPEND=0 keeps the two-call step (A/B)."""
     import b200attn
+    return os.environ.get("B2_BENCH_APPEND", "1") != "0" and b200attn.append_is_fused(prob["Hq"], prob["Hkv"], num_splits)
+
+
+def step_description(fused):
+    if fused:
+        return ("b2_paged_decode_append, one layer: KV write of 1 new token/seq fused into the single-pass decode grid "
+                "(one launch; same bits as reshape_and_cache + paged_decode)")
+    return "reshape_and_cache(1 new token/seq) + paged_decode, one layer"
+
+
+def time_resident(dev, prob, num_splits, K, W, barrier, clock_index=None):
+    """W warm-up steps, then K timed steps of [KV write of 1 new token / sequence + paged decode] with every input
+    resident in HBM; CUDA events on the launching stream.  The step is b2_paged_decode_append (one launch) when
+    step_is_fused, else b2_reshape_and_cache + b2_paged_decode.  -> (ms per step, mean / min ms of the decode call --
+    the fused call includes the write --, out tensor, clocks summary)."""
+    import b200attn
+    fused = step_is_fused(prob, num_splits)
     B = prob["B"]
     bt_d, sl_d, slot_d = prob["block_tables"].to(dev), prob["seq_lens"].to(dev), prob["slot_new"].to(dev)
     ks, vs = prob["scales"] or (None, None)
@@ -222,17 +238,38 @@ def time_resident(dev, prob, num_splits, K, W, barrier, clock_index=None):
     stream = torch.cuda.current_stream(dev)
 
     def kv_write():
-        b200attn.reshape_and_cache(prob["k_new"], prob["v_new"], prob["k_cache"], prob["v_cache"], slot_d, ks, vs)
+        if not fused:
+            b200attn.reshape_and_cache(prob["k_new"], prob["v_new"], prob["k_cache"], prob["v_cache"], slot_d, ks, vs)
 
     def decode():
-        b200attn.paged_decode(prob["q"], prob["k_cache"], prob["v_cache"], bt_d, sl_d, k_scale=ks, v_scale=vs,
-                              out=out, workspace=ws, num_splits=num_splits)
+        if fused:
+            b200attn.paged_decode_append(prob["q"], prob["k_new"], prob["v_new"], slot_d, prob["k_cache"],
+                                         prob["v_cache"], bt_d, sl_d, k_scale=ks, v_scale=vs, out=out, workspace=ws,
+                                         num_splits=num_splits)
+        else:
+            b200attn.paged_decode(prob["q"], prob["k_cache"], prob["v_cache"], bt_d, sl_d, k_scale=ks, v_scale=vs,
+                                  out=out, workspace=ws, num_splits=num_splits)
 
     for _ in range(W):
         kv_write()
         decode()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     ev_all = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+    if fused:
+        # the step IS one launch: one event between consecutive steps times each launch (interval i = launch i plus its
+        # launch gap) -- two records per step would only add instrumentation to the timed region
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+        barrier()
+        with ClockSampler(clock_index if clock_index is not None else 0) as clk:
+            ev_all[0].record(stream)
+            marks[0].record(stream)
+            for i in range(K):
+                decode()
+                marks[i + 1].record(stream)
+            ev_all[1].record(stream)
+            barrier()
+        dec_ms = [marks[i].elapsed_time(marks[i + 1]) for i in range(K)]
+        return ev_all[0].elapsed_time(ev_all[1]) / K, statistics.mean(dec_ms), min(dec_ms), out, clk.summary()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     barrier()
     with ClockSampler(clock_index if clock_index is not None else 0) as clk:
         ev_all[0].record(stream)
@@ -327,12 +364,13 @@ def run_reference_arm(args, wl_name, wl):
 # --------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------
-def roofline_record(bytes_rank, dec_mean_ms, dec_min_ms, traffic=None):
+def roofline_record(bytes_rank, dec_mean_ms, dec_min_ms, traffic=None, fused=False):
     peak, peak_src = measured_peak()
     achieved = bytes_rank / (dec_mean_ms * 1e-3) / 1e9
     return {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
             "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
-            "kernel": "b2_paged_decode (every kernel the call launches)",
+            "kernel": ("b2_paged_decode_append (one launch: the step's KV write + the decode grid)" if fused
+                       else "b2_paged_decode (every kernel the call launches)"),
             "kernel_ms": round(dec_mean_ms, 5), "kernel_ms_min": round(dec_min_ms, 5),
             "frac_of_8TBps": round(achieved / NOMINAL_HBM_GBS, 4)}
 
@@ -371,6 +409,7 @@ def sub_config_record(dev, name, K, W, splits_arg):
            "frac": round(nbytes / (dec_mean * 1e-3) / 1e9 / peak, 4),
            "frac_of_8TBps": round(nbytes / (dec_mean * 1e-3) / 1e9 / NOMINAL_HBM_GBS, 4),
            "num_splits": num_splits, "schedule": schedule_name(num_splits), "schedule_chosen_by": src,
+           "step_impl": step_description(step_is_fused(prob, num_splits)),
            "steps": K, "warmup": W, "clocks": clk}
     del prob
     torch.cuda.empty_cache()
@@ -470,7 +509,9 @@ def run_ours(args, wl_name, wl):
     # schedule: the engine's scheduler holds seq_lens on the host and picks the schedule from them (--splits -1)
     num_splits, schedule_src = pick_schedule(prob, args.splits)
     schedule = schedule_name(num_splits)
-    if num_splits == 1:
+    if step_is_fused(prob, num_splits):
+        launches_per_step = 1                                  # b2_paged_decode_append: the write rides in the decode grid
+    elif num_splits == 1:
         launches_per_step = 2                                  # reshape + decode
     elif num_splits == 0:
         launches_per_step = 4                                  # reshape + zero-counter + decode + merge
@@ -549,6 +590,7 @@ def run_ours(args, wl_name, wl):
             "collective": "none on the attention path" + (f"; optional NCCL all-gather of out [B, Hq, d]: {allgather_us} us"
                                                            if allgather_us is not None else ""),
             "per_gpu": {"B": B, "Hq": Hq_l, "Hkv": Hkv_l}, "num_splits": num_splits,
+            "step_impl": step_description(step_is_fused(prob, num_splits)),
             "schedule": schedule, "schedule_chosen_by": schedule_src,
             "algorithmic_bytes_per_step_per_gpu": bytes_rank,
             "l2": "KV working set per GPU >> 126 MB L2, every step streams it from HBM; no flush needed"})
@@ -558,7 +600,8 @@ def run_ours(args, wl_name, wl):
             "dtype": "bf16" if not fp8 else "fp8_e4m3 KV / bf16 q,out (fp32 accumulate)", "data": "synthetic",
             "config": cfg,
             "pct_of_8TBps": round(100.0 * value / world / NOMINAL_HBM_GBS, 2),
-            "roofline": roofline_record(bytes_rank, dec_mean_ms, dec_min_ms, committed_traffic(wl_name, B, Hq_l, Hkv_l)),
+            "roofline": roofline_record(bytes_rank, dec_mean_ms, dec_min_ms, committed_traffic(wl_name, B, Hq_l, Hkv_l),
+                                        fused=step_is_fused(prob, num_splits)),
             "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(e2e_ms, 5),
                     "path": ("b200attn.DecodeStep: block tables resident on the device (uploaded when a sequence takes a "

@@ -133,6 +133,34 @@ B2_API int b2_paged_decode(void* out, const void* q,
                     void* workspace, size_t workspace_bytes, int num_splits,
                     void* stream);
 
+/* The decode step of one layer in ONE call: the KV write of the step's new token per row, then the attention over the
+ * rows including it.  Replaces the pair vLLM issues per layer and decode step -- `reshape_and_cache` followed by
+ * `paged_attention_v1/_v2` -- inside the engine the reference launches (vllm_manager.py:371-374); sizes as above
+ * (models.py:9,10,11,15).  Result and cache contents are bit-identical to b2_reshape_and_cache(k_new, v_new, ...,
+ * slot_mapping, T = B, ...) followed by b2_paged_decode(...) with the same arguments.
+ *   k_new / v_new: bf16 [B, Hkv, d] rows (token strides in elements); slot_mapping[b] = the slot of row b's new token,
+ *   i.e. position seq_lens[b] - 1 of its block table (seq_lens COUNT the new token); slot < 0 skips the write.
+ *   The slot must belong to row b alone among the rows of the call (true of every engine: shared prefix blocks are full).
+ * With num_splits = 1 (the single-pass grid; b2_paged_decode_plan_splits picks it for long uniform batches) and
+ * Hq / Hkv <= 16 it is ONE kernel launch: the CTA that owns (row, kv head) stores the new K/V row itself before it
+ * streams the row, and makes the store visible to its own TMA loads (fence.proxy.async) -- the step has no second launch
+ * and no kernel boundary.  b2_paged_decode_append_fused tells (1 / 0; negative on bad arguments).  Every other schedule
+ * cuts a row over several CTAs: the call then launches the KV write in front of the decode grid (same results). */
+B2_API int b2_paged_decode_append_fused(int Hq, int Hkv, int num_splits);
+B2_API int b2_paged_decode_append(void* out, const void* q,
+                           const void* k_new, const void* v_new, const int64_t* slot_mapping,
+                           int64_t k_token_stride, int64_t v_token_stride,
+                           void* k_cache, void* v_cache,
+                           const int32_t* block_tables, const int32_t* seq_lens,
+                           int B, int Hq, int Hkv, int d, int bs, int max_nb,
+                           int64_t num_blocks,
+                           int64_t q_stride, int64_t out_stride,
+                           int64_t cache_block_stride, int64_t cache_head_stride,
+                           float scale, int kv_dtype,
+                           const float* k_scale, const float* v_scale,
+                           void* workspace, size_t workspace_bytes, int num_splits,
+                           void* stream);
+
 /* b2_paged_decode for callers that may not allocate: code under CUDA graph capture, tight serving loops, harnesses
  * that forbid cudaMalloc.  No counterpart in the reference.
  * Same operation, arguments and results as b2_paged_decode, minus the workspace: the split-K partials and the claim

@@ -41,6 +41,9 @@ SIGNATURES = {
     "b2_paged_decode_plan_splits": (i32, [vp, i32, i32, i32, i32, i32, i32]),
     "b2_paged_decode": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
                               f32, i32, vp, vp, vp, sz, i32, vp]),
+    "b2_paged_decode_append_fused": (i32, [i32, i32, i32]),
+    "b2_paged_decode_append": (i32, [vp, vp, vp, vp, vp, i64, i64, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64,
+                                     i64, i64, i64, i64, f32, i32, vp, vp, vp, sz, i32, vp]),
     "b2_paged_decode_static": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
                                      f32, i32, vp, vp, i32, vp]),
     "b2_decode_plan_create": (vp, [vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, f32, i32, vp, vp, vp, sz, vp]),

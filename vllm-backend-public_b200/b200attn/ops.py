@@ -219,6 +219,78 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
     return out
 
 
+def paged_decode_append(q: torch.Tensor, k_new: torch.Tensor, v_new: torch.Tensor, slot_mapping: torch.Tensor,
+                        k_cache: torch.Tensor, v_cache: torch.Tensor, block_tables: torch.Tensor, seq_lens: torch.Tensor,
+                        scale: Optional[float] = None, k_scale: Optional[torch.Tensor] = None,
+                        v_scale: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                        workspace: Optional[torch.Tensor] = None, num_splits: int = 0) -> torch.Tensor:
+    """One decode step of one layer in one call (b2_paged_decode_append): reshape_and_cache(k_new, v_new, ...,
+    slot_mapping) of the step's new token per row, then paged_decode over seq_lens (which count that token) -- same
+    bits in `out` and in the caches as the two calls.  With num_splits = 1 and Hq / Hkv <= 16 it is ONE launch: the CTA
+    that owns (row, kv head) writes the row's new K/V itself before it streams the row (append_is_fused)."""
+    lib = _lib.load()
+    dev = _need_cuda(q=q, k_new=k_new, v_new=v_new, slot_mapping=slot_mapping, k_cache=k_cache, v_cache=v_cache,
+                     block_tables=block_tables, seq_lens=seq_lens, k_scale=k_scale, v_scale=v_scale, out=out,
+                     workspace=workspace)
+    nb, Hkv, bs, d, bstride, hstride = _check_cache(k_cache, v_cache)
+    kvd = _kv_dtype_of(k_cache)
+    if q.dtype != torch.bfloat16 or q.dim() != 3 or q.shape[2] != d:
+        raise ValueError(f"q must be bf16 [B, Hq, {d}]")
+    B, Hq, _ = q.shape
+    if q.stride(2) != 1 or q.stride(1) != d:
+        raise ValueError("q: head and dim axes must be contiguous")
+    if k_new.dtype != torch.bfloat16 or v_new.dtype != torch.bfloat16:
+        raise ValueError("k_new / v_new must be bf16")
+    if k_new.shape != (B, Hkv, d) or v_new.shape != (B, Hkv, d):
+        raise ValueError(f"k_new / v_new must be [{B}, {Hkv}, {d}] (one new token per row)")
+    for t in (k_new, v_new):
+        if t.stride(2) != 1 or t.stride(1) != d:
+            raise ValueError("k_new / v_new: head and dim axes must be contiguous")
+    if slot_mapping.dtype != torch.int64 or slot_mapping.shape != (B,) or not slot_mapping.is_contiguous():
+        raise ValueError("slot_mapping must be a contiguous int64 [B]")
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B \
+            or not block_tables.is_contiguous():
+        raise ValueError("block_tables must be a contiguous int32 [B, max_nb]")
+    if seq_lens.dtype != torch.int32 or seq_lens.shape != (B,) or not seq_lens.is_contiguous():
+        raise ValueError("seq_lens must be a contiguous int32 [B]")
+    max_nb = block_tables.shape[1]
+    if out is None:
+        out = torch.empty(B, Hq, d, dtype=torch.bfloat16, device=dev)
+    elif out.dtype != torch.bfloat16 or out.shape != (B, Hq, d) or out.stride(2) != 1 or out.stride(1) != d:
+        raise ValueError("out must be bf16 [B, Hq, d] with contiguous head/dim axes")
+    if scale is None:
+        scale = 1.0 / math.sqrt(d)
+    if kvd == KV_FP8_E4M3:
+        for s in (k_scale, v_scale):
+            if s is None or s.dtype != torch.float32 or s.numel() != 1:
+                raise ValueError("fp8 KV cache needs 1-element fp32 device tensors k_scale / v_scale")
+    if B == 0:
+        return out
+    need = lib.b2_paged_decode_workspace_bytes(B, Hq, Hkv, d, bs, max_nb, num_splits)
+    if need and (workspace is None or workspace.numel() * workspace.element_size() < need):
+        if workspace is not None:
+            raise ValueError(f"workspace holds {workspace.numel() * workspace.element_size()} bytes, {need} required")
+        workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+    wbytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    one = Hkv * d
+    _lib.check(lib.b2_paged_decode_append(
+        _ptr(out), _ptr(q), _ptr(k_new), _ptr(v_new), _ptr(slot_mapping),
+        k_new.stride(0) if B > 1 else one, v_new.stride(0) if B > 1 else one,
+        _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), _ptr(seq_lens),
+        B, Hq, Hkv, d, bs, max_nb, nb, q.stride(0) if B > 1 else Hq * d, out.stride(0) if B > 1 else Hq * d,
+        bstride, hstride, float(scale), kvd, _ptr(k_scale), _ptr(v_scale), _ptr(workspace), wbytes, num_splits,
+        _stream(dev)))
+    return out
+
+
+def append_is_fused(Hq: int, Hkv: int, num_splits: int) -> bool:
+    """True when paged_decode_append runs as one launch for these heads and this schedule (b2_paged_decode_append_fused)."""
+    rc = _lib.load().b2_paged_decode_append_fused(Hq, Hkv, num_splits)
+    if rc < 0:
+        _lib.check(rc)
+    return rc == 1
+
+
 class DecodePlan:
     """Per-engine decode handle (b2_decode_plan_*): caches, geometry, scales and workspace are fixed at creation, where
     the two TMA descriptors are encoded and the workspace header is zeroed; run() is then argument checks + launches

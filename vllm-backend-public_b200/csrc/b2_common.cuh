@@ -172,5 +172,32 @@ __device__ __forceinline__ int4 ld_nc_16(const void* p) {
     return r;
 }
 
+// Generic-proxy global stores of this thread become visible to later async-proxy (TMA) reads of global memory.
+__device__ __forceinline__ void fence_proxy_async_global() {
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+// 8 bf16 (one 16-byte vector) -> 8 e4m3 bytes: cvt.rn.satfinite.e4m3x2.f32(x / scale), IEEE division -- the KV-write
+// encoding of b2_reshape_and_cache (bit-exact against the oracle), shared with the fused append of paged_decode.cu.
+__device__ __forceinline__ uint2 pack_e4m3x8(const int4& val, float s) {
+    const uint32_t w[4] = {static_cast<uint32_t>(val.x), static_cast<uint32_t>(val.y),
+                           static_cast<uint32_t>(val.z), static_cast<uint32_t>(val.w)};
+    uint32_t packed[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const uint32_t word = w[p * 2 + q];
+            // bf16 -> f32 is a 16-bit shift; the division is IEEE (matches the oracle)
+            const float lo = __fdiv_rn(__uint_as_float(word << 16), s);
+            const float hi = __fdiv_rn(__uint_as_float(word & 0xffff0000u), s);
+            const __nv_fp8x2_storage_t pr = __nv_cvt_float2_to_fp8x2(make_float2(lo, hi), __NV_SATFINITE, __NV_E4M3);
+            acc |= static_cast<uint32_t>(pr) << (16 * q);
+        }
+        packed[p] = acc;
+    }
+    return make_uint2(packed[0], packed[1]);
+}
+
 }  // namespace b2
 #endif  // __CUDACC__

@@ -70,6 +70,15 @@ struct DecodeParams {
     uint32_t* counter;              // dynamic schedule: claim counter (workspace header)
     int64_t q_stride, out_stride;
     float scale_log2;  // softmax scale * log2(e)
+    // b2_paged_decode_append, fused path (single-pass grid, one CTA per (row, kv head)): the CTA writes its row's new
+    // K/V token into the cache before it streams the row.  append = 0: every field below is unused.
+    int append;
+    const __nv_bfloat16* k_new;
+    const __nv_bfloat16* v_new;
+    const int64_t* slot_mapping;
+    void* k_cache_w;
+    void* v_cache_w;
+    int64_t k_new_stride, v_new_stride, cache_block_stride, cache_head_stride;
 };
 
 template <int BS, bool FP8, int NT, int NSTAGE>
@@ -594,6 +603,44 @@ __device__ __forceinline__ void init_pipeline(uint32_t bar_full, uint32_t bar_em
     __syncthreads();
 }
 
+// Fused KV write of b2_paged_decode_append: one warp stores the new token of (row b, kv head kvh) -- 16 lanes the K
+// row, 16 lanes the V row, one 16-byte vector of 8 bf16 each (bit-identical to b2_reshape_and_cache, e4m3 included).
+// The row is read back by THIS CTA's own TMA loads (async proxy): every writing lane fences generic -> async for
+// global memory, then the warp synchronises before its lane 0 issues the copy of the tile that holds the token.
+// Two halves so that the loads are in flight while the producer streams the row's earlier tiles and the store (with
+// its fences, ~1 us) sits in front of the LAST stage only, where two other stages cover it.
+struct AppendVec {
+    int64_t slot;
+    int4 val;
+};
+__device__ __forceinline__ AppendVec append_load(const DecodeParams& p, int b, int kvh, int lane) {
+    AppendVec a;
+    a.slot = p.slot_mapping[b];
+    const bool is_v = lane >= 16;
+    const int c = lane & 15;                          // D / 8 = 16 vectors per row
+    a.val = b2::ld_nc_16((is_v ? p.v_new + b * p.v_new_stride : p.k_new + b * p.k_new_stride) + kvh * D + c * 8);
+    return a;
+}
+template <int BS, bool FP8>
+__device__ __forceinline__ void append_store(const DecodeParams& p, const AppendVec& a, int kvh, int lane) {
+    if (a.slot >= 0) {                                // < 0: padding row, nothing to write
+        const int64_t blk = a.slot / BS;
+        const int off = (int)(a.slot - blk * BS);
+        const bool is_v = lane >= 16;
+        const int c = lane & 15;
+        const int64_t dst_elem = blk * p.cache_block_stride + kvh * p.cache_head_stride + (int64_t)off * D + c * 8;
+        if (!FP8) {
+            *reinterpret_cast<int4*>(static_cast<__nv_bfloat16*>(is_v ? p.v_cache_w : p.k_cache_w) + dst_elem) = a.val;
+        } else {
+            *reinterpret_cast<uint2*>(static_cast<uint8_t*>(is_v ? p.v_cache_w : p.k_cache_w) + dst_elem) =
+                b2::pack_e4m3x8(a.val, is_v ? *p.v_scale : *p.k_scale);
+        }
+    }
+    __threadfence();
+    b2::fence_proxy_async_global();
+    __syncwarp();
+}
+
 // =============================================================================================
 // schedule A: classic grid split, one CTA per (split, kv head x head group, sequence)
 // =============================================================================================
@@ -622,6 +669,10 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         if (p.num_splits == 1)
             for (int i = tid; i < nheads * D; i += NTHREADS)
                 p.out[b * p.out_stride + (int64_t)head0 * D + i] = __float2bfloat16(0.f);
+        if (p.append && warp == NCW) {                // the KV write does not depend on seq_len (as b2_reshape_and_cache)
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            append_store<BS, FP8>(p, append_load(p, b, kvh, lane), kvh, lane);
+        }
         return;
     }
     const int n_tok = min(seq_len, t_begin + p.split_tokens) - t_begin;
@@ -644,8 +695,21 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         // triggers launch_dependents at its start).  Everything above -- barrier init, descriptor prefetch, the
         // consumers' q loads -- overlaps it; the cache and the block tables are only touched from here on.
         asm volatile("griddepcontrol.wait;" ::: "memory");
-        produce_segment<C, NSTAGE>(&tmK, &tmV, p.block_tables + (int64_t)b * p.max_nb + t_begin / BS,
-                                   (n_tok + BS - 1) / BS, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
+        const int32_t* bt = p.block_tables + (int64_t)b * p.max_nb + t_begin / BS;
+        const int n_blk = (n_tok + BS - 1) / BS;
+        if (p.append) {
+            // fused KV write (single pass: this CTA streams the whole row, the new token sits in its last block): every
+            // stage but the last goes out first, then the store, then the stage that holds it
+            const AppendVec a = append_load(p, b, kvh, lane);
+            const int head = (n_blk - 1) / C::BLK_PER_STAGE * C::BLK_PER_STAGE;
+            if (head)
+                produce_segment<C, NSTAGE>(&tmK, &tmV, bt, head, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
+            append_store<BS, FP8>(p, a, kvh, lane);
+            produce_segment<C, NSTAGE>(&tmK, &tmV, bt + head, n_blk - head, kvh, ring, bar_full, bar_empty, it, lane, pol,
+                                       p.two_box);
+        } else {
+            produce_segment<C, NSTAGE>(&tmK, &tmV, bt, n_blk, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
+        }
         B2_TRACE_AT(cta_lin, 4);
     } else {
         if (warp == 0) B2_TRACE_AT(cta_lin, 1);
@@ -1529,10 +1593,25 @@ int check_geom(int Hq, int Hkv, int d, int bs, int max_nb, int64_t num_blocks, c
     return B2_OK;
 }
 
+// the KV write of b2_paged_decode_append (one new token per row), already validated by its entry point
+struct AppendArgs {
+    const void* k_new;
+    const void* v_new;
+    const int64_t* slot_mapping;
+    void* k_cache;
+    void* v_cache;
+    int64_t k_token_stride, v_token_stride, cache_block_stride, cache_head_stride;
+};
+
+// The append rides inside the decode grid when exactly one CTA reads a (row, kv head) -- the single-pass grid with all
+// q heads of a kv head in one CTA (G <= 16); every other schedule cuts a row over several CTAs, so the write is
+// launched in front of it (b2_reshape_and_cache) and the call is an ordinary b2_paged_decode.
+bool append_is_fused(const Plan& pl) { return pl.num_splits == 1 && pl.hg == 1; }
+
 // one call: validate the per-step arguments, plan, launch
 int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool zero_first, void* out, const void* q,
                const int32_t* block_tables, const int32_t* seq_lens, int B, int64_t q_stride, int64_t out_stride,
-               int num_splits, cudaStream_t st) {
+               int num_splits, cudaStream_t st, const AppendArgs* ap = nullptr) {
     B2_REQUIRE(out && q && block_tables && seq_lens, B2_EINVAL, "paged_decode: null pointer");
     B2_REQUIRE(b2_aligned16(out) && b2_aligned16(q), B2_EINVAL, "paged_decode: pointers must be 16-byte aligned");
     B2_REQUIRE(q_stride % 8 == 0 && out_stride % 8 == 0 && q_stride >= (int64_t)g.Hq * D && out_stride >= (int64_t)g.Hq * D,
@@ -1559,6 +1638,30 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
     p.scale_log2 = g.scale * LOG2E;
     p.ws_o = nullptr; p.ws_lse = nullptr;
     p.counter = nullptr;
+    p.append = 0;
+    p.k_new = p.v_new = nullptr;
+    p.slot_mapping = nullptr;
+    p.k_cache_w = p.v_cache_w = nullptr;
+    p.k_new_stride = p.v_new_stride = p.cache_block_stride = p.cache_head_stride = 0;
+    if (ap) {
+        if (append_is_fused(pl)) {
+            p.append = 1;
+            p.k_new = static_cast<const __nv_bfloat16*>(ap->k_new);
+            p.v_new = static_cast<const __nv_bfloat16*>(ap->v_new);
+            p.slot_mapping = ap->slot_mapping;
+            p.k_cache_w = ap->k_cache;
+            p.v_cache_w = ap->v_cache;
+            p.k_new_stride = ap->k_token_stride;
+            p.v_new_stride = ap->v_token_stride;
+            p.cache_block_stride = ap->cache_block_stride;
+            p.cache_head_stride = ap->cache_head_stride;
+        } else {
+            const int rc = b2_reshape_and_cache(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping, B, g.Hkv,
+                                                D, g.bs, ap->k_token_stride, ap->v_token_stride, ap->cache_block_stride,
+                                                ap->cache_head_stride, g.kv_dtype, g.k_scale, g.v_scale, st);
+            if (rc != B2_OK) return rc;
+        }
+    }
     p.chunk_tokens = pl.chunk_tokens;
     p.static_pct = pl.static_pct;
     p.two_box = maps.two_box;
@@ -1696,6 +1799,44 @@ extern "C" int b2_paged_decode(void* out, const void* q, const void* k_cache, co
     const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
     return run_decode(g, maps, kn, /*zero_first=*/true, out, q, block_tables, seq_lens, B, q_stride, out_stride, num_splits,
                       static_cast<cudaStream_t>(stream));
+}
+
+// b2_paged_decode_append: the decode step's KV write and its attention in ONE call -- and, for the single-pass grid
+// (num_splits = 1, G <= 16), in ONE launch: see append_row / append_is_fused.
+extern "C" int b2_paged_decode_append_fused(int Hq, int Hkv, int num_splits) {
+    if (Hq <= 0 || Hkv <= 0 || Hq % Hkv) return B2_EINVAL;
+    return num_splits == 1 && Hq / Hkv <= 16 ? 1 : 0;
+}
+
+extern "C" int b2_paged_decode_append(void* out, const void* q, const void* k_new, const void* v_new,
+                                      const int64_t* slot_mapping, int64_t k_token_stride, int64_t v_token_stride,
+                                      void* k_cache, void* v_cache, const int32_t* block_tables, const int32_t* seq_lens,
+                                      int B, int Hq, int Hkv, int d, int bs, int max_nb, int64_t num_blocks,
+                                      int64_t q_stride, int64_t out_stride, int64_t cache_block_stride,
+                                      int64_t cache_head_stride, float scale, int kv_dtype, const float* k_scale,
+                                      const float* v_scale, void* workspace, size_t workspace_bytes, int num_splits,
+                                      void* stream) {
+    B2_REQUIRE(B >= 0, B2_EINVAL, "paged_decode_append: bad batch size %d", B);
+    if (B == 0) return B2_OK;
+    int rc = check_geom(Hq, Hkv, d, bs, max_nb, num_blocks, k_cache, v_cache, cache_block_stride, cache_head_stride, scale,
+                        kv_dtype, k_scale, v_scale);
+    if (rc != B2_OK) return rc;
+    // the same argument rules as b2_reshape_and_cache
+    B2_REQUIRE(k_new && v_new && slot_mapping, B2_EINVAL, "paged_decode_append: null pointer");
+    B2_REQUIRE(b2_aligned16(k_new) && b2_aligned16(v_new) && k_token_stride % 8 == 0 && v_token_stride % 8 == 0, B2_EINVAL,
+               "paged_decode_append: k_new / v_new rows must keep 16-byte alignment");
+    B2_REQUIRE(k_token_stride >= (int64_t)Hkv * d && v_token_stride >= (int64_t)Hkv * d, B2_EINVAL,
+               "paged_decode_append: k_new / v_new strides overlap");
+    const Knobs kn = read_knobs();
+    CacheMaps maps;
+    rc = make_decode_maps(&maps, k_cache, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride, cache_head_stride,
+                          kn.two_box != 0);
+    if (rc != B2_OK) return rc;
+    const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
+    const AppendArgs ap{k_new, v_new, slot_mapping, k_cache, v_cache, k_token_stride, v_token_stride, cache_block_stride,
+                        cache_head_stride};
+    return run_decode(g, maps, kn, /*zero_first=*/true, out, q, block_tables, seq_lens, B, q_stride, out_stride, num_splits,
+                      static_cast<cudaStream_t>(stream), &ap);
 }
 
 // ---------------------------------------------------------------------------------------------

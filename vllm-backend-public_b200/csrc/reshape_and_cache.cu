@@ -61,27 +61,8 @@ reshape_and_cache_kernel(const __nv_bfloat16* __restrict__ k_new,
             __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(is_v ? v_cache : k_cache) + dst_elem;
             *reinterpret_cast<int4*>(dst) = val;
         } else {
-            const float s = is_v ? vs : ks;
-            const uint32_t w[4] = {static_cast<uint32_t>(val.x), static_cast<uint32_t>(val.y),
-                                   static_cast<uint32_t>(val.z), static_cast<uint32_t>(val.w)};
-            uint32_t packed[2];
-#pragma unroll
-            for (int p = 0; p < 2; ++p) {
-                uint32_t acc = 0;
-#pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    const uint32_t word = w[p * 2 + q];
-                    // bf16 -> f32 is a 16-bit shift; the division is IEEE (matches the oracle)
-                    const float lo = __fdiv_rn(__uint_as_float(word << 16), s);
-                    const float hi = __fdiv_rn(__uint_as_float(word & 0xffff0000u), s);
-                    const __nv_fp8x2_storage_t pr =
-                        __nv_cvt_float2_to_fp8x2(make_float2(lo, hi), __NV_SATFINITE, __NV_E4M3);
-                    acc |= static_cast<uint32_t>(pr) << (16 * q);
-                }
-                packed[p] = acc;
-            }
             uint8_t* dst = static_cast<uint8_t*>(is_v ? v_cache : k_cache) + dst_elem;
-            *reinterpret_cast<uint2*>(dst) = make_uint2(packed[0], packed[1]);
+            *reinterpret_cast<uint2*>(dst) = b2::pack_e4m3x8(val, is_v ? vs : ks);
         }
     }
 }
