@@ -203,6 +203,18 @@ B2_API void b2_decode_plan_destroy(b2_decode_plan* plan);
 B2_API int b2_decode_plan_run(b2_decode_plan* plan, void* out, const void* q,
                        const int32_t* block_tables, const int32_t* seq_lens, int B,
                        int64_t q_stride, int64_t out_stride, int num_splits, void* stream);
+/* The whole decode step of an engine that keeps its block tables resident on the device, in one call:
+ * b2_reshape_and_cache_decode (KV write of the step's new token per row + its table entry) followed by
+ * b2_decode_plan_run, with the same results in `out`, in the caches the plan was created over (they are WRITTEN here)
+ * and in block_tables.  Same vLLM pair as b2_paged_decode_append (`reshape_and_cache` + `paged_attention_v1/_v2`,
+ * reference vllm_manager.py:371-374).  One launch when b2_paged_decode_append_fused(Hq, Hkv, num_splits) is 1: the CTA
+ * that owns (row, kv head) stores the new K/V row and the table entry, and takes the id of the row's last block from
+ * the slot instead of from the entry it is writing.  k_new / v_new / q may be pinned host memory (read in place). */
+B2_API int b2_decode_plan_run_append(b2_decode_plan* plan, void* out, const void* q,
+                              const void* k_new, const void* v_new, const int64_t* slot_mapping,
+                              int64_t k_token_stride, int64_t v_token_stride,
+                              int32_t* block_tables, const int32_t* seq_lens, int B,
+                              int64_t q_stride, int64_t out_stride, int num_splits, void* stream);
 
 /* Diagnostic / A-B variant kept for the ncu comparison DESIGN.md cites: the same contract as
  * b2_paged_decode, computed by a plain CUDA-core kernel (no TMA, no tensor cores).  Not used by

@@ -139,3 +139,38 @@ def test_append_many_short_rows_config_shape(cuda):
     lens = torch.randint(1, 131, (256,), generator=g).tolist()
     _check(_case(cuda, lens, 32, 8, 16, False, seed=6), splits=1, oracle=False)
     _check(_case(cuda, lens[:128], 32, 8, 16, True, seed=7), splits=1, oracle=False)
+
+
+@pytest.mark.parametrize("fp8", [False, True])
+@pytest.mark.parametrize("splits", [1, 0])
+def test_plan_run_append_resident_tables(cuda, fp8, splits):
+    """b2_decode_plan_run_append over device-RESIDENT block tables: rows whose new token opens a block (length = n * bs + 1)
+    arrive with a stale table entry for it (a wrong block id here), exactly what an engine's resident table holds before
+    the step.  Bar: out, both caches and the table bit-identical to b2_reshape_and_cache_decode + b2_decode_plan_run."""
+    from b200attn import ops
+    bs = 16
+    lens = [1, 17, 33, 16, 65, 64, 129, 300, 2, 49]
+    c = _case(cuda, lens, 8, 2, bs, fp8, seed=21 + splits)
+    ks, vs = c["scales"]
+    stale = c["bt"].clone()
+    for b, L in enumerate(lens):
+        if (L - 1) % bs == 0:
+            stale[b, (L - 1) // bs] = 3                       # not the block the slot names
+    res = []
+    for fused in (False, True):
+        kc, vc, bt = c["kc0"].clone(), c["vc0"].clone(), stale.clone()
+        plan = ops.DecodePlan(kc, vc, len(lens), 8, bt.shape[1], k_scale=ks, v_scale=vs)
+        out = torch.full((len(lens), 8, 128), float("nan"), dtype=torch.bfloat16, device=cuda)
+        if fused:
+            plan.run_append(c["q"], c["k_new"], c["v_new"], c["slot_new"], bt, c["seq_lens"], out, splits)
+        else:
+            ops.reshape_and_cache_decode(c["k_new"], c["v_new"], kc, vc, c["slot_new"], bt, c["seq_lens"], ks, vs)
+            plan.run(c["q"], bt, c["seq_lens"], out, splits)
+        torch.cuda.synchronize()
+        res.append((out, kc, vc, bt))
+        plan.close()
+    (o0, k0, v0, t0), (o1, k1, v1, t1) = res
+    assert torch.equal(t0.cpu(), c["bt"].cpu()) and torch.equal(t1.cpu(), c["bt"].cpu()), "tables not brought up to date"
+    assert torch.equal(_bits(k1), _bits(k0)) and torch.equal(_bits(v1), _bits(v0)), "caches differ"
+    assert torch.isfinite(o1.float()).all()
+    assert torch.equal(_bits(o1), _bits(o0)), "out differs from the two-call result"

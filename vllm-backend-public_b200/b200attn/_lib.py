@@ -49,6 +49,7 @@ SIGNATURES = {
     "b2_decode_plan_create": (vp, [vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, f32, i32, vp, vp, vp, sz, vp]),
     "b2_decode_plan_destroy": (None, [vp]),
     "b2_decode_plan_run": (i32, [vp, vp, vp, vp, vp, i32, i64, i64, i32, vp]),
+    "b2_decode_plan_run_append": (i32, [vp, vp, vp, vp, vp, vp, i64, i64, vp, vp, i32, i64, i64, i32, vp]),
     "b2_paged_decode_simt": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64,
                                    f32, i32, vp, vp, vp]),
     "b2_prefill_attention": (i32, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64,

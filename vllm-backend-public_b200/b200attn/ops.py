@@ -345,6 +345,39 @@ class DecodePlan:
                              qs, os_, num_splits, _stream(self.dev)))
         return out
 
+    def run_append(self, q: torch.Tensor, k_new: torch.Tensor, v_new: torch.Tensor, slot_mapping: torch.Tensor,
+                   block_tables: torch.Tensor, seq_lens: torch.Tensor, out: torch.Tensor,
+                   num_splits: int = 0) -> torch.Tensor:
+        """reshape_and_cache_decode(k_new, v_new, ..., slot_mapping, block_tables, seq_lens) + run(...) in one call
+        (b2_decode_plan_run_append): one launch for the single-pass grid.  k_new / v_new: bf16 [B, Hkv, d] rows (strided
+        views and pinned host memory allowed); slot_mapping int64 [B] and the RESIDENT block_tables int32 [B, max_nb]
+        (updated in place) on the device."""
+        B = q.shape[0]
+        if q.dtype != torch.bfloat16 or out.dtype != torch.bfloat16 or q.shape[1:] != (self.Hq, self.d) \
+                or out.shape != q.shape or q.stride(1) != self.d or out.stride(1) != self.d:
+            raise ValueError(f"q / out must be bf16 [B, {self.Hq}, {self.d}] with contiguous head/dim axes")
+        for name, t in (("k_new", k_new), ("v_new", v_new)):
+            if t.dtype != torch.bfloat16 or t.shape != (B, self.Hkv, self.d) or t.stride(2) != 1 or t.stride(1) != self.d:
+                raise ValueError(f"{name} must be bf16 [B, {self.Hkv}, {self.d}] with contiguous head/dim axes")
+        if slot_mapping.dtype != torch.int64 or slot_mapping.shape != (B,) or not slot_mapping.is_cuda \
+                or not slot_mapping.is_contiguous():
+            raise ValueError("slot_mapping must be a contiguous device int64 [B]")
+        if block_tables.dtype != torch.int32 or block_tables.shape != (B, self.max_nb) or not block_tables.is_cuda \
+                or block_tables.stride(1) != 1 or (B > 1 and block_tables.stride(0) != self.max_nb):
+            raise ValueError(f"block_tables must be a device int32 [B, {self.max_nb}]")
+        if seq_lens.dtype != torch.int32 or seq_lens.shape != (B,) or not seq_lens.is_cuda:
+            raise ValueError("seq_lens must be a device int32 [B]")
+        for name, t in (("q", q), ("out", out), ("k_new", k_new), ("v_new", v_new)):
+            if not t.is_cuda and not t.is_pinned():
+                raise ValueError(f"{name} must be a CUDA tensor or a pinned host tensor (b200attn has no CPU path)")
+        one = self.Hkv * self.d
+        _lib.check(self._lib.b2_decode_plan_run_append(
+            self._h, out.data_ptr(), q.data_ptr(), k_new.data_ptr(), v_new.data_ptr(), slot_mapping.data_ptr(),
+            k_new.stride(0) if B > 1 else one, v_new.stride(0) if B > 1 else one, block_tables.data_ptr(),
+            seq_lens.data_ptr(), B, q.stride(0) if B > 1 else self.Hq * self.d,
+            out.stride(0) if B > 1 else self.Hq * self.d, num_splits, _stream(self.dev)))
+        return out
+
     def close(self) -> None:
         if self._h:
             self._lib.b2_decode_plan_destroy(self._h)

@@ -18,6 +18,8 @@ What run() enqueues (captured once per (B, schedule) in a CUDA graph, then repla
                                   over PCIe itself (the H2D leg, no staging copy)
     b2_decode_plan_run            q likewise; `out` is the PINNED host tensor: result rows leave as 16-byte vector
                                   stores straight into host memory (the D2H leg, no separate copy)
+    (B2_STEP_FUSE_APPEND=1: both as one call, b2_decode_plan_run_append -- one launch for the single-pass grid; same
+    bits, measured no faster on this path, see __init__)
 and then synchronises the stream.  The schedule (single-pass grid or dynamic persistent) is chosen on the host
 from h_seq_lens by b2_paged_decode_plan_splits, as an engine's scheduler would.
 
@@ -26,6 +28,7 @@ Mirrors the per-step work of the engine behind the reference's launch contract
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -70,6 +73,11 @@ class DecodeStep:
         # the schedule choice is a performance heuristic over lengths that grow by one token per step: it is refreshed
         # every `plan_every` steps (and whenever the batch size changes), not recomputed on the critical path of each
         self.plan_every = 8
+        # B2_STEP_FUSE_APPEND=1: the step as ONE call (b2_decode_plan_run_append).  Off by default: measured on this path
+        # (scripts/e2e_append_ab.py, config 2, back-to-back graph replays) 176.9-178.9 us fused vs 176.3-176.4 us for the
+        # two calls with zero-copy inputs, 188.2 vs 188.2 us with the staged copy -- the step's cost over the resident
+        # loop (164 us) is the 787 KB of q|k|v crossing PCIe before the first CTAs can start, not the kernel boundary
+        self.fuse_append = os.environ.get("B2_STEP_FUSE_APPEND", "0") == "1"
         self._plan_cache = (0, 0, 0)            # (B, num_splits, steps left)
 
     # ------------------------------------------------------------------------------------------
@@ -106,8 +114,13 @@ class DecodeStep:
             self.d_qkv.copy_(self.h_qkv, non_blocking=True)
         self.d_meta.copy_(self.h_meta, non_blocking=True)
         q, k, v, bt, sl, slots = self._views(B, zero_copy)
-        ops.reshape_and_cache_decode(k, v, self.k_cache, self.v_cache, slots, bt, sl, self.k_scale, self.v_scale)
-        self.plan_handle.run(q, bt, sl, self.h_out[:B], num_splits)
+        if self.fuse_append:
+            # one call; for the single-pass grid one launch (b2_decode_plan_run_append: the CTA that owns (row, kv head)
+            # writes the row's new K/V and its table entry itself), else the KV write launched in front of the grid
+            self.plan_handle.run_append(q, k, v, slots, bt, sl, self.h_out[:B], num_splits)
+        else:
+            ops.reshape_and_cache_decode(k, v, self.k_cache, self.v_cache, slots, bt, sl, self.k_scale, self.v_scale)
+            self.plan_handle.run(q, bt, sl, self.h_out[:B], num_splits)
 
     def plan(self, B: int) -> int:
         # straight ctypes call on the pinned buffer's address: this runs on the host every step, before the launch

@@ -79,6 +79,7 @@ struct DecodeParams {
     void* k_cache_w;
     void* v_cache_w;
     int64_t k_new_stride, v_new_stride, cache_block_stride, cache_head_stride;
+    int32_t* bt_update;   // resident block tables (b2_decode_plan_run_append): also record the new token's block, or null
 };
 
 template <int BS, bool FP8, int NT, int NSTAGE>
@@ -186,9 +187,13 @@ template <class C, int NSTAGE>
 __device__ __forceinline__ void produce_segment(const CUtensorMap* tmK, const CUtensorMap* tmV,
                                                 const int32_t* __restrict__ bt, int n_blk, int kvh,
                                                 uint32_t ring, uint32_t bar_full, uint32_t bar_empty,
-                                                uint32_t& it, int lane, uint64_t pol, int two_box) {
+                                                uint32_t& it, int lane, uint64_t pol, int two_box,
+                                                int last_blk = -1) {
     const int n_stage = (n_blk + C::BLK_PER_STAGE - 1) / C::BLK_PER_STAGE;
     int cur = (lane < n_blk) ? bt[lane] : 0;            // 32 table entries per batch
+    // fused append over resident tables: the id of the segment's last block comes from the new token's slot, not from
+    // the table entry this very grid is writing (only used with n_blk <= 32)
+    if (last_blk >= 0 && lane == n_blk - 1) cur = last_blk;
     int nxt = (32 + lane < n_blk) ? bt[32 + lane] : 0;  // next batch, prefetched
     for (int st = 0; st < n_stage; ++st, ++it) {
         const uint32_t s = it % NSTAGE;
@@ -622,10 +627,14 @@ __device__ __forceinline__ AppendVec append_load(const DecodeParams& p, int b, i
     return a;
 }
 template <int BS, bool FP8>
-__device__ __forceinline__ void append_store(const DecodeParams& p, const AppendVec& a, int kvh, int lane) {
+__device__ __forceinline__ void append_store(const DecodeParams& p, const AppendVec& a, int b, int seq_len, int kvh, int lane) {
     if (a.slot >= 0) {                                // < 0: padding row, nothing to write
         const int64_t blk = a.slot / BS;
         const int off = (int)(a.slot - blk * BS);
+        // resident tables: the slot names the block of column (seq_len - 1) / BS (as b2_reshape_and_cache_decode; every
+        // kv head's CTA of the row stores the same value)
+        if (p.bt_update && lane == 0 && seq_len > 0 && (seq_len - 1) / BS < p.max_nb)
+            p.bt_update[(int64_t)b * p.max_nb + (seq_len - 1) / BS] = (int32_t)blk;
         const bool is_v = lane >= 16;
         const int c = lane & 15;
         const int64_t dst_elem = blk * p.cache_block_stride + kvh * p.cache_head_stride + (int64_t)off * D + c * 8;
@@ -671,7 +680,7 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
                 p.out[b * p.out_stride + (int64_t)head0 * D + i] = __float2bfloat16(0.f);
         if (p.append && warp == NCW) {                // the KV write does not depend on seq_len (as b2_reshape_and_cache)
             asm volatile("griddepcontrol.wait;" ::: "memory");
-            append_store<BS, FP8>(p, append_load(p, b, kvh, lane), kvh, lane);
+            append_store<BS, FP8>(p, append_load(p, b, kvh, lane), b, seq_len, kvh, lane);
         }
         return;
     }
@@ -704,9 +713,9 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
             const int head = (n_blk - 1) / C::BLK_PER_STAGE * C::BLK_PER_STAGE;
             if (head)
                 produce_segment<C, NSTAGE>(&tmK, &tmV, bt, head, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
-            append_store<BS, FP8>(p, a, kvh, lane);
+            append_store<BS, FP8>(p, a, b, seq_len, kvh, lane);
             produce_segment<C, NSTAGE>(&tmK, &tmV, bt + head, n_blk - head, kvh, ring, bar_full, bar_empty, it, lane, pol,
-                                       p.two_box);
+                                       p.two_box, p.bt_update && a.slot >= 0 ? (int)(a.slot / BS) : -1);
         } else {
             produce_segment<C, NSTAGE>(&tmK, &tmV, bt, n_blk, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
         }
@@ -1601,6 +1610,7 @@ struct AppendArgs {
     void* k_cache;
     void* v_cache;
     int64_t k_token_stride, v_token_stride, cache_block_stride, cache_head_stride;
+    int32_t* bt_update;   // device-resident block tables to keep current (decode-plan form), or null
 };
 
 // The append rides inside the decode grid when exactly one CTA reads a (row, kv head) -- the single-pass grid with all
@@ -1643,6 +1653,7 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
     p.slot_mapping = nullptr;
     p.k_cache_w = p.v_cache_w = nullptr;
     p.k_new_stride = p.v_new_stride = p.cache_block_stride = p.cache_head_stride = 0;
+    p.bt_update = nullptr;
     if (ap) {
         if (append_is_fused(pl)) {
             p.append = 1;
@@ -1655,10 +1666,16 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
             p.v_new_stride = ap->v_token_stride;
             p.cache_block_stride = ap->cache_block_stride;
             p.cache_head_stride = ap->cache_head_stride;
+            p.bt_update = ap->bt_update;
         } else {
-            const int rc = b2_reshape_and_cache(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping, B, g.Hkv,
-                                                D, g.bs, ap->k_token_stride, ap->v_token_stride, ap->cache_block_stride,
-                                                ap->cache_head_stride, g.kv_dtype, g.k_scale, g.v_scale, st);
+            const int rc = ap->bt_update
+                ? b2_reshape_and_cache_decode(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping,
+                                              ap->bt_update, seq_lens, B, g.Hkv, D, g.bs, g.max_nb, ap->k_token_stride,
+                                              ap->v_token_stride, ap->cache_block_stride, ap->cache_head_stride,
+                                              g.kv_dtype, g.k_scale, g.v_scale, st)
+                : b2_reshape_and_cache(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping, B, g.Hkv, D,
+                                       g.bs, ap->k_token_stride, ap->v_token_stride, ap->cache_block_stride,
+                                       ap->cache_head_stride, g.kv_dtype, g.k_scale, g.v_scale, st);
             if (rc != B2_OK) return rc;
         }
     }
@@ -1834,7 +1851,7 @@ extern "C" int b2_paged_decode_append(void* out, const void* q, const void* k_ne
     if (rc != B2_OK) return rc;
     const DecodeGeom g{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
     const AppendArgs ap{k_new, v_new, slot_mapping, k_cache, v_cache, k_token_stride, v_token_stride, cache_block_stride,
-                        cache_head_stride};
+                        cache_head_stride, nullptr};
     return run_decode(g, maps, kn, /*zero_first=*/true, out, q, block_tables, seq_lens, B, q_stride, out_stride, num_splits,
                       static_cast<cudaStream_t>(stream), &ap);
 }
@@ -1918,6 +1935,9 @@ struct b2_decode_plan {
     CacheMaps maps;
     Knobs kn;
     int max_B;
+    void* k_cache;        // for b2_decode_plan_run_append (the step's KV write goes into the caches the plan reads)
+    void* v_cache;
+    int64_t cache_block_stride, cache_head_stride;
 };
 
 extern "C" b2_decode_plan* b2_decode_plan_create(const void* k_cache, const void* v_cache, int max_B, int Hq, int Hkv, int d,
@@ -1947,6 +1967,10 @@ extern "C" b2_decode_plan* b2_decode_plan_create(const void* k_cache, const void
     pl->g = DecodeGeom{Hq, Hkv, bs, max_nb, kv_dtype, scale, k_scale, v_scale, workspace, workspace_bytes};
     pl->kn = kn;
     pl->max_B = max_B;
+    pl->k_cache = const_cast<void*>(k_cache);
+    pl->v_cache = const_cast<void*>(v_cache);
+    pl->cache_block_stride = cache_block_stride;
+    pl->cache_head_stride = cache_head_stride;
     if (make_decode_maps(&pl->maps, k_cache, v_cache, kv_dtype, num_blocks, Hkv, bs, cache_block_stride,
                          cache_head_stride, kn.two_box != 0) != B2_OK) {
         delete pl;
@@ -1983,3 +2007,23 @@ extern "C" B2_API int b2_debug_clear_trace(void) {
     return cudaMemcpyToSymbol(g_trace, zeros, sizeof zeros) == cudaSuccess ? 0 : B2_ECUDA;
 }
 #endif
+
+// The decode step of an engine with RESIDENT block tables in one call: b2_reshape_and_cache_decode (KV write + table
+// entry of the new token) followed by b2_decode_plan_run -- one launch for the single-pass grid (see append_is_fused).
+extern "C" int b2_decode_plan_run_append(b2_decode_plan* pl, void* out, const void* q, const void* k_new, const void* v_new,
+                                         const int64_t* slot_mapping, int64_t k_token_stride, int64_t v_token_stride,
+                                         int32_t* block_tables, const int32_t* seq_lens, int B, int64_t q_stride,
+                                         int64_t out_stride, int num_splits, void* stream) {
+    B2_REQUIRE(pl != nullptr, B2_EINVAL, "decode_plan_run_append: null plan");
+    B2_REQUIRE(B >= 0 && B <= pl->max_B, B2_EINVAL, "decode_plan_run_append: B=%d outside [0, %d]", B, pl->max_B);
+    if (B == 0) return B2_OK;
+    B2_REQUIRE(k_new && v_new && slot_mapping && block_tables, B2_EINVAL, "decode_plan_run_append: null pointer");
+    B2_REQUIRE(b2_aligned16(k_new) && b2_aligned16(v_new) && k_token_stride % 8 == 0 && v_token_stride % 8 == 0, B2_EINVAL,
+               "decode_plan_run_append: k_new / v_new rows must keep 16-byte alignment");
+    B2_REQUIRE(k_token_stride >= (int64_t)pl->g.Hkv * D && v_token_stride >= (int64_t)pl->g.Hkv * D, B2_EINVAL,
+               "decode_plan_run_append: k_new / v_new strides overlap");
+    const AppendArgs ap{k_new, v_new, slot_mapping, pl->k_cache, pl->v_cache, k_token_stride, v_token_stride,
+                        pl->cache_block_stride, pl->cache_head_stride, block_tables};
+    return run_decode(pl->g, pl->maps, pl->kn, /*zero_first=*/false, out, q, block_tables, seq_lens, B, q_stride,
+                      out_stride, num_splits, static_cast<cudaStream_t>(stream), &ap);
+}
