@@ -174,3 +174,28 @@ def test_plan_run_append_resident_tables(cuda, fp8, splits):
     assert torch.equal(_bits(k1), _bits(k0)) and torch.equal(_bits(v1), _bits(v0)), "caches differ"
     assert torch.isfinite(o1.float()).all()
     assert torch.equal(_bits(o1), _bits(o0)), "out differs from the two-call result"
+
+
+def test_append_refused_call_writes_nothing(cuda):
+    """A call that fails its argument checks (workspace too small for a split-K schedule) must not have launched the
+    KV write either: the caches keep their bytes."""
+    c = _case(cuda, [300, 200, 129], 8, 2, 16, False, seed=31)
+    kc, vc = c["kc0"].clone(), c["vc0"].clone()
+    small = torch.zeros(64, dtype=torch.uint8, device=cuda)
+    with pytest.raises(ValueError):
+        b200attn.paged_decode_append(c["q"], c["k_new"], c["v_new"], c["slot_new"], kc, vc, c["bt"], c["seq_lens"],
+                                     workspace=small, num_splits=3)
+    # through the C ABI (the Python wrapper sizes workspaces itself): the library's own refusal
+    import ctypes as C
+    from b200attn import _lib
+    lib = _lib.load()
+    q, bt = c["q"], c["bt"]
+    rc = lib.b2_paged_decode_append(
+        C.c_void_p(torch.empty_like(q).data_ptr()), C.c_void_p(q.data_ptr()), C.c_void_p(c["k_new"].data_ptr()),
+        C.c_void_p(c["v_new"].data_ptr()), C.c_void_p(c["slot_new"].data_ptr()), 2 * 128, 2 * 128,
+        C.c_void_p(kc.data_ptr()), C.c_void_p(vc.data_ptr()), C.c_void_p(bt.data_ptr()), C.c_void_p(c["seq_lens"].data_ptr()),
+        3, 8, 2, 128, 16, bt.shape[1], kc.shape[0], 8 * 128, 8 * 128, kc.stride(0), kc.stride(1), 128 ** -0.5, 0, None, None,
+        C.c_void_p(small.data_ptr()), 64, 3, C.c_void_p(torch.cuda.current_stream(cuda).cuda_stream))
+    assert rc == _lib.B2_ENOMEM, rc
+    torch.cuda.synchronize()
+    assert torch.equal(_bits(kc), _bits(c["kc0"])) and torch.equal(_bits(vc), _bits(c["vc0"])), "a refused call wrote the cache"

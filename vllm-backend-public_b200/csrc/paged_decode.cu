@@ -1667,16 +1667,6 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
             p.cache_block_stride = ap->cache_block_stride;
             p.cache_head_stride = ap->cache_head_stride;
             p.bt_update = ap->bt_update;
-        } else {
-            const int rc = ap->bt_update
-                ? b2_reshape_and_cache_decode(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping,
-                                              ap->bt_update, seq_lens, B, g.Hkv, D, g.bs, g.max_nb, ap->k_token_stride,
-                                              ap->v_token_stride, ap->cache_block_stride, ap->cache_head_stride,
-                                              g.kv_dtype, g.k_scale, g.v_scale, st)
-                : b2_reshape_and_cache(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping, B, g.Hkv, D,
-                                       g.bs, ap->k_token_stride, ap->v_token_stride, ap->cache_block_stride,
-                                       ap->cache_head_stride, g.kv_dtype, g.k_scale, g.v_scale, st);
-            if (rc != B2_OK) return rc;
         }
     }
     p.chunk_tokens = pl.chunk_tokens;
@@ -1698,6 +1688,19 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
         if (header) base += WS_HEADER_BYTES;
         p.ws_o = reinterpret_cast<float*>(base);
         p.ws_lse = p.ws_o + body / sizeof(float) / (D + 1) * D;
+    }
+    if (ap && !p.append) {
+        // a schedule that cuts rows over several CTAs: the KV write goes in front of the grid (after every argument
+        // check above, so a refused call has written nothing)
+        const int rc = ap->bt_update
+            ? b2_reshape_and_cache_decode(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping,
+                                          ap->bt_update, seq_lens, B, g.Hkv, D, g.bs, g.max_nb, ap->k_token_stride,
+                                          ap->v_token_stride, ap->cache_block_stride, ap->cache_head_stride,
+                                          g.kv_dtype, g.k_scale, g.v_scale, st)
+            : b2_reshape_and_cache(ap->k_new, ap->v_new, ap->k_cache, ap->v_cache, ap->slot_mapping, B, g.Hkv, D,
+                                   g.bs, ap->k_token_stride, ap->v_token_stride, ap->cache_block_stride,
+                                   ap->cache_head_stride, g.kv_dtype, g.k_scale, g.v_scale, st);
+        if (rc != B2_OK) return rc;
     }
     if (g.bs == 8) return dispatch_decode<8>(maps.k, maps.v, p, pl, fp8, kn.fp8_ctas, zero_first, st);
     if (g.bs == 16) return dispatch_decode<16>(maps.k, maps.v, p, pl, fp8, kn.fp8_ctas, zero_first, st);
