@@ -458,12 +458,16 @@ def test_decode_step_from_host_buffers(cuda, use_graph, zero_copy):
     assert torch.equal(bits(kc), bits(kc_ref)) and torch.equal(bits(vc), bits(vc_ref))
 
 
+@pytest.mark.parametrize("fuse", [False, True])
 @pytest.mark.parametrize("fp8", [False, True])
-def test_decode_step_resident_tables_follow_the_sequences(cuda, fp8):
+def test_decode_step_resident_tables_follow_the_sequences(cuda, fp8, fuse, monkeypatch):
     """Device-resident block tables: they are uploaded ONCE; then every sequence grows by one token per step across
     several block boundaries, and the only per-step host->device words are seq_lens and slots.  The decode-step KV
     write must keep the resident tables current (b2_reshape_and_cache_decode), checked against the oracle, which
-    is given the host-side tables the block manager would hold."""
+    is given the host-side tables the block manager would hold.  fuse: the step as ONE call, b2_decode_plan_run_append
+    (captured in the step's CUDA graph; for the single-pass grid the owning CTA writes the row and its table entry and
+    must take the new block's id from the slot, never from the poisoned entry)."""
+    monkeypatch.setenv("B2_STEP_FUSE_APPEND", "1" if fuse else "0")
     B, Hq, Hkv, bs, ctx, steps = 5, 8, 2, 16, 70, 40
     inp = R.make_inputs(B, Hq, Hkv, 128, bs, ctx + steps + bs, seed=31, ragged=False, slack_blocks=8)
     lens = torch.tensor([1, 15, 16, 33, 70], dtype=torch.int32)                 # start lengths (tokens already cached)
@@ -503,7 +507,8 @@ def test_decode_step_resident_tables_follow_the_sequences(cuda, fp8):
         else:
             R.reshape_and_cache_ref(k_new, v_new, kc_ref, vc_ref, slots)
         ref = R.paged_decode_ref(q, kc_ref, vc_ref, full_bt, cur, return_f32=True, **okw)
-        assert_close(out, ref, what=f"resident tables step {it} fp8={fp8}")
+        assert_close(out, ref, what=f"resident tables step {it} fp8={fp8} fuse={fuse}")
+    assert step.fuse_append == fuse
     nb1 = (cur.long() + bs - 1) // bs
     dt = step.d_block_tables.cpu()
     for b in range(B):
