@@ -1,4 +1,5 @@
 """Host-side schedule planner (b2_paged_decode_plan_splits): pure host arithmetic, no GPU."""
+import pytest
 import torch
 
 import b200attn
@@ -42,3 +43,15 @@ def test_bad_arguments():
         b200attn.plan_num_splits(torch.tensor([1, 2], dtype=torch.int64), 8, 2)
     with pytest.raises(b200attn.B2Error):
         b200attn.plan_num_splits(torch.tensor([1, 2], dtype=torch.int32), 7, 2)
+
+
+def test_append_fused_rule():
+    """b2_paged_decode_append rides inside the decode grid only where one CTA reads a (row, kv head): the single-pass grid
+    (num_splits = 1) with all q heads of a kv head in one CTA (G <= 16).  Pure host code."""
+    import b200attn
+    assert b200attn.append_is_fused(32, 8, 1) and b200attn.append_is_fused(64, 8, 1) and b200attn.append_is_fused(16, 1, 1)
+    assert not b200attn.append_is_fused(32, 8, 0)        # dynamic persistent: rows are cut into chunks over many CTAs
+    assert not b200attn.append_is_fused(32, 8, 4)        # split-K
+    assert not b200attn.append_is_fused(40, 2, 1)        # G = 20: two head-group CTAs share a kv head
+    with pytest.raises(b200attn.B2Error):
+        b200attn.append_is_fused(30, 8, 1)               # Hq not a multiple of Hkv
