@@ -17,6 +17,14 @@ pytestmark = pytest.mark.gpu
 ATOL, RTOL = 2e-3, 1e-2
 
 
+@pytest.fixture(autouse=True, params=[1, 2], ids=["producer-store", "consumer-store"])
+def append_mode(request, monkeypatch):
+    """Both ways the fused path can store the row (B2_APPEND_MODE, csrc/paged_decode.cu): 1 = the producer warp in front of
+    its last stage (default), 2 = consumer warp 0 at CTA start with an mbarrier hand-over to the producer."""
+    monkeypatch.setenv("B2_APPEND_MODE", str(request.param))
+    return request.param
+
+
 def _case(dev, lens, Hq, Hkv, bs, fp8, seed, pad_rows=()):
     d = 128
     B = len(lens)

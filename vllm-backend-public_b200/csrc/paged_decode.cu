@@ -691,6 +691,8 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
     const uint32_t bar_full = ring + C::RING_BYTES;
     const uint32_t bar_empty = bar_full + NSTAGE * 8;
     float* scratch = reinterpret_cast<float*>(smem_raw + C::RING_BYTES + C::BAR_BYTES);
+    const uint32_t bar_append = bar_empty + NSTAGE * 8;   // the spare slot of the barrier area (append mode 2 only)
+    if (tid == 0) b2::mbar_init(bar_append, 1);            // made visible by the fence + barrier of init_pipeline
     init_pipeline(bar_full, bar_empty, NSTAGE, tid);
 
     uint32_t it = 0;
@@ -709,11 +711,14 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         if (p.append) {
             // fused KV write (single pass: this CTA streams the whole row, the new token sits in its last block): every
             // stage but the last goes out first, then the store, then the stage that holds it
-            const AppendVec a = append_load(p, b, kvh, lane);
+            AppendVec a;
+            if (p.append == 1) a = append_load(p, b, kvh, lane);
+            else a.slot = p.slot_mapping[b];              // mode 2: consumer warp 0 stores; only the slot is needed here
             const int head = (n_blk - 1) / C::BLK_PER_STAGE * C::BLK_PER_STAGE;
             if (head)
                 produce_segment<C, NSTAGE>(&tmK, &tmV, bt, head, kvh, ring, bar_full, bar_empty, it, lane, pol, p.two_box);
-            append_store<BS, FP8>(p, a, b, seq_len, kvh, lane);
+            if (p.append == 1) append_store<BS, FP8>(p, a, b, seq_len, kvh, lane);
+            else b2::mbar_wait(bar_append, 0);            // the row is stored and fenced (long ago, unless the row is short)
             produce_segment<C, NSTAGE>(&tmK, &tmV, bt + head, n_blk - head, kvh, ring, bar_full, bar_empty, it, lane, pol,
                                        p.two_box, p.bt_update && a.slot >= 0 ? (int)(a.slot / BS) : -1);
         } else {
@@ -730,7 +735,16 @@ paged_decode_split_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_
         QFrags<NT> qf;
         // q may be the output of the kernel this grid was launched under (rotary + KV write in the engine)
         asm volatile("griddepcontrol.wait;" ::: "memory");
+        AppendVec a;
+        const bool storer = p.append == 2 && warp == 0;   // warp-uniform
+        if (storer) a = append_load(p, b, kvh, lane);     // in flight under the q loads
         load_q_frags<FP8, NT>(qf, reinterpret_cast<const uint32_t*>(p.q + b * p.q_stride + (int64_t)head0 * D), nheads, lane);
+        if (storer) {
+            // append mode 2: this warp idles until the first stage lands anyway; the store, its fences and the hand-over
+            // to the producer (release on the mbarrier, acquired by its wait in front of the last stage) fit in that gap
+            append_store<BS, FP8>(p, a, b, seq_len, kvh, lane);
+            if (lane == 0) b2::mbar_arrive(bar_append);
+        }
         WarpAcc<NT> acc;
         acc.reset();
         consume_segment<C, FP8, NT, NSTAGE>(acc, qf, n_tok, ring, bar_full, bar_empty, it, sl2, warp, lane);
@@ -1326,9 +1340,13 @@ struct Knobs {
     int static_pct;     // B2_STATIC_PCT: share of the chunks dealt statically
     int fp8_ctas;       // B2_FP8_CTAS: 3 (default) or 2 resident CTAs per SM for the fp8 kernels
     int two_box;        // B2_TWO_BOX=1: force the two-boxes-per-tile bf16 map (the fallback path)
+    int append_mode;    // B2_APPEND_MODE: who stores the fused append's row -- 2 (default) consumer warp 0 at CTA start,
+                        // in the gap before its first stage lands; the producer waits for it on an mbarrier in front of its
+                        // last stage.  1: the producer warp itself, in front of its last stage (A/B: 0.6 us slower per step)
 };
 Knobs read_knobs() {
     Knobs k;
+    k.append_mode = env_int("B2_APPEND_MODE", 2) == 1 ? 1 : 2;
     k.chunk_tokens = env_int("B2_CHUNK_TOKENS", 0);
     int pct = env_int("B2_STATIC_PCT", 85);
     k.static_pct = pct < 0 ? 0 : (pct > 100 ? 100 : pct);
@@ -1656,7 +1674,7 @@ int run_decode(const DecodeGeom& g, const CacheMaps& maps, const Knobs& kn, bool
     p.bt_update = nullptr;
     if (ap) {
         if (append_is_fused(pl)) {
-            p.append = 1;
+            p.append = kn.append_mode;
             p.k_new = static_cast<const __nv_bfloat16*>(ap->k_new);
             p.v_new = static_cast<const __nv_bfloat16*>(ap->v_new);
             p.slot_mapping = ap->slot_mapping;
