@@ -142,8 +142,8 @@ B2_API int b2_paged_decode(void* out, const void* q,
  *   i.e. position seq_lens[b] - 1 of its block table (seq_lens COUNT the new token); slot < 0 skips the write.
  *   The slot must belong to row b alone among the rows of the call (true of every engine: shared prefix blocks are full).
  * With num_splits = 1 (the single-pass grid; b2_paged_decode_plan_splits picks it for long uniform batches) and
- * Hq / Hkv <= 16 it is ONE kernel launch: the CTA that owns (row, kv head) stores the new K/V row itself before it
- * streams the row, and makes the store visible to its own TMA loads (fence.proxy.async) -- the step has no second launch
+ * Hq / Hkv <= 16 it is ONE kernel launch: the CTA that owns (row, kv head) stores the new K/V row itself and issues
+ * the TMA copy of the stage that holds it only once the store is visible to the async proxy (fence.proxy.async) -- the step has no second launch
  * and no kernel boundary.  b2_paged_decode_append_fused tells (1 / 0; negative on bad arguments).  Every other schedule
  * cuts a row over several CTAs: the call then launches the KV write in front of the decode grid (same results). */
 B2_API int b2_paged_decode_append_fused(int Hq, int Hkv, int num_splits);
